@@ -1,0 +1,320 @@
+// crc32c_kernels.cu — batch CRC-32C (Castagnoli) for sm_100a.
+//
+// Replaces butil::crc32c::Extend / Value (reference src/butil/crc32c.cc:379-454,
+// crc32c.h:19-29) for many messages at once.  The reference walks one buffer
+// with a serial 8-bytes-per-instruction chain (crc32c.cc:407-410); a GPU has no
+// CRC instruction, so the work is re-shaped around GF(2) linearity:
+//
+//   * a message is cut into 4 KiB chunks; 4 lanes (a "quad") own one chunk;
+//   * each step the quad reads one 64-byte row (16 B per lane, full 32-byte
+//     sectors) and every lane keeps FOUR independent Horner accumulators, one per
+//     32-bit column of its uint4:  H <- Z64(H) ^ word, where Z64 advances a CRC
+//     register across 64 bytes.  Z64 is applied with 4 table lookups (one per
+//     state byte) — 1 lookup per payload byte, the same cost as slicing, but
+//     with no serial dependency between the 16 lookups of a row;
+//   * the Z64 tables are replicated once per lane ([byte][lane]) in shared
+//     memory (128 KiB), so a warp-wide lookup is bank-conflict free;
+//   * columns, lanes, the ragged tail and (for multi-chunk messages) chunks are
+//     then combined with the shift operators Z4/Z16/Z32 (small tables) and a
+//     GF(2) multiply by x^(8*len) (crc32c_combine_kernel).
+//
+// Register convention is the reference's: l = crc ^ 0xffffffff, one byte step is
+// l = table0[(l ^ b) & 0xff] ^ (l >> 8) (crc32c.cc:390-393), result l ^ 0xffffffff.
+#include "b2c_internal.cuh"
+
+namespace b2c {
+
+static constexpr uint32_t kPolyReflected = 0x82F63B78u;
+
+// ---------------------------------------------------------------------------
+// host-side table construction
+// ---------------------------------------------------------------------------
+namespace {
+
+struct HostTables {
+    uint32_t t0[256];
+    HostTables() {
+        for (uint32_t i = 0; i < 256; i++) {
+            uint32_t c = i;
+            for (int k = 0; k < 8; k++) c = (c >> 1) ^ ((c & 1) ? kPolyReflected : 0);
+            t0[i] = c;
+        }
+    }
+    uint32_t zbytes(uint32_t l, uint32_t k) const {  // advance register across k zero bytes
+        for (uint32_t i = 0; i < k; i++) l = t0[l & 0xff] ^ (l >> 8);
+        return l;
+    }
+};
+
+uint32_t host_mulmod(uint32_t a, uint32_t b) {  // reflected domain: bit 31 is x^0
+    uint32_t p = 0;
+    for (int i = 0; i < 32; i++) {
+        if ((a >> (31 - i)) & 1) p ^= b;
+        b = (b >> 1) ^ ((b & 1) ? kPolyReflected : 0);
+    }
+    return p;
+}
+
+}  // namespace
+
+__constant__ uint32_t c_x2n[64];  // x^(2^j) mod P, reflected
+
+int crc_tables_init(b2c_ctx* ctx) {
+    HostTables ht;
+    std::vector<uint32_t> tabA(4 * 256 * 32);
+    std::vector<uint32_t> small(3 * 4 * 256);
+    const uint32_t dist[3] = {4, 16, 32};
+    for (uint32_t k = 0; k < 4; k++)
+        for (uint32_t b = 0; b < 256; b++) {
+            uint32_t v = ht.zbytes(b << (8 * k), 64);
+            for (uint32_t l = 0; l < 32; l++) tabA[(k * 256 + b) * 32 + l] = v;
+            for (uint32_t d = 0; d < 3; d++) small[(d * 4 + k) * 256 + b] = ht.zbytes(b << (8 * k), dist[d]);
+        }
+    uint32_t x2n[64];
+    x2n[0] = 1u << 30;  // x^1
+    for (int j = 1; j < 64; j++) x2n[j] = host_mulmod(x2n[j - 1], x2n[j - 1]);
+    B2C_CUDA(ctx, cudaMalloc(&ctx->d_crc_tabA, tabA.size() * 4));
+    B2C_CUDA(ctx, cudaMalloc(&ctx->d_crc_small, small.size() * 4));
+    B2C_CUDA(ctx, cudaMemcpy(ctx->d_crc_tabA, tabA.data(), tabA.size() * 4, cudaMemcpyHostToDevice));
+    B2C_CUDA(ctx, cudaMemcpy(ctx->d_crc_small, small.data(), small.size() * 4, cudaMemcpyHostToDevice));
+    B2C_CUDA(ctx, cudaMemcpyToSymbol(c_x2n, x2n, sizeof(x2n)));
+    return B2C_OK;
+}
+
+// ---------------------------------------------------------------------------
+// device code
+// ---------------------------------------------------------------------------
+struct CrcSmem {
+    uint32_t A[4][256][32];  // replicated Z^64 tables: 128 KiB
+    uint32_t S[3][4][256];   // Z^4, Z^16, Z^32: 12 KiB
+};
+
+__device__ __forceinline__ uint32_t apply_A(const CrcSmem& sm, uint32_t x, uint32_t lane) {
+    return sm.A[0][x & 0xff][lane] ^ sm.A[1][(x >> 8) & 0xff][lane] ^ sm.A[2][(x >> 16) & 0xff][lane] ^
+           sm.A[3][x >> 24][lane];
+}
+template <int D>
+__device__ __forceinline__ uint32_t apply_S(const CrcSmem& sm, uint32_t x) {
+    return sm.S[D][0][x & 0xff] ^ sm.S[D][1][(x >> 8) & 0xff] ^ sm.S[D][2][(x >> 16) & 0xff] ^ sm.S[D][3][x >> 24];
+}
+__device__ __forceinline__ uint32_t byte_step(const CrcSmem& sm, uint32_t l, uint32_t b) {
+    return sm.S[0][3][(l ^ b) & 0xff] ^ (l >> 8);  // Z^4 of a top byte == table0
+}
+
+__device__ __forceinline__ uint4 ldg128_stream(const uint8_t* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+// S(l, p[0..L)) computed by the 4 lanes of one quad; result valid on all 4 lanes.
+__device__ uint32_t crc_chunk_quad(const CrcSmem& sm, const uint8_t* p, uint32_t L, uint32_t l, uint32_t lane) {
+    const uint32_t q = lane & 3;
+    const uint32_t qbase = lane & ~3u;
+    const uint32_t qmask = 0xFu << qbase;
+    // head: bytes up to 16-byte alignment
+    uint32_t hb = (16u - (uint32_t)(reinterpret_cast<uintptr_t>(p) & 15)) & 15u;
+    if (hb > L) hb = L;
+    for (uint32_t i = 0; i < hb; i++) l = byte_step(sm, l, p[i]);
+    p += hb;
+    L -= hb;
+    const uint32_t rows = L >> 6;
+    if (rows) {
+        const uint8_t* lp = p + q * 16;
+        uint4 w = ldg128_stream(lp);
+        uint32_t h0 = w.x, h1 = w.y, h2 = w.z, h3 = w.w;
+        if (q == 0) h0 ^= l;
+#pragma unroll 4
+        for (uint32_t it = 1; it < rows; it++) {
+            w = ldg128_stream(lp + (size_t)it * 64);
+            h0 = apply_A(sm, h0, lane) ^ w.x;
+            h1 = apply_A(sm, h1, lane) ^ w.y;
+            h2 = apply_A(sm, h2, lane) ^ w.z;
+            h3 = apply_A(sm, h3, lane) ^ w.w;
+        }
+        // fold the 4 columns of this lane: g = S(0, 16 raw bytes)
+        uint32_t g = apply_S<0>(sm, h0);
+        g = apply_S<0>(sm, g ^ h1);
+        g = apply_S<0>(sm, g ^ h2);
+        g = apply_S<0>(sm, g ^ h3);
+        uint32_t g0 = __shfl_sync(qmask, g, qbase + 0);
+        uint32_t g1 = __shfl_sync(qmask, g, qbase + 1);
+        uint32_t g2 = __shfl_sync(qmask, g, qbase + 2);
+        uint32_t g3 = __shfl_sync(qmask, g, qbase + 3);
+        l = apply_S<2>(sm, apply_S<1>(sm, g0) ^ g1) ^ (apply_S<1>(sm, g2) ^ g3);
+        p += (size_t)rows * 64;
+        L -= rows * 64;
+    }
+    if (L == 0) return l;
+    // ragged tail: L < 64 bytes, p is 16-byte aligned
+    const uint32_t tw = L >> 2, tb = L & 3;
+    const uint32_t a = tw >> 2, r = tw & 3;  // full lanes, words in the partial lane
+    uint4 w = make_uint4(0, 0, 0, 0);
+    if (q * 16 < L) w = ldg128_stream(p + q * 16);
+    uint32_t g = apply_S<0>(sm, w.x);
+    g = apply_S<0>(sm, g ^ w.y);
+    g = apply_S<0>(sm, g ^ w.z);
+    g = apply_S<0>(sm, g ^ w.w);
+    uint32_t g0 = __shfl_sync(qmask, g, qbase + 0);
+    uint32_t g1 = __shfl_sync(qmask, g, qbase + 1);
+    uint32_t g2 = __shfl_sync(qmask, g, qbase + 2);
+    if (a > 0) l = apply_S<1>(sm, l) ^ g0;
+    if (a > 1) l = apply_S<1>(sm, l) ^ g1;
+    if (a > 2) l = apply_S<1>(sm, l) ^ g2;
+    // partial lane `a` finishes: r whole words then tb bytes
+    uint32_t wx = __shfl_sync(qmask, w.x, qbase + a);
+    uint32_t wy = __shfl_sync(qmask, w.y, qbase + a);
+    uint32_t wz = __shfl_sync(qmask, w.z, qbase + a);
+    uint32_t ww = __shfl_sync(qmask, w.w, qbase + a);
+    uint32_t last = wx;
+    if (r > 0) { l = apply_S<0>(sm, l ^ wx); last = wy; }
+    if (r > 1) { l = apply_S<0>(sm, l ^ wy); last = wz; }
+    if (r > 2) { l = apply_S<0>(sm, l ^ wz); last = ww; }
+    for (uint32_t i = 0; i < tb; i++) l = byte_step(sm, l, (last >> (8 * i)) & 0xff);
+    return l;
+}
+
+struct CrcParams {
+    const uint8_t* data;
+    const uint64_t* off;
+    const uint32_t* len;
+    const uint32_t* init;        // nullable
+    const uint32_t* chunk_msg;   // nullable when uniform single chunk
+    const uint32_t* chunk_first; // nullable when uniform single chunk
+    const uint32_t* tabA;
+    const uint32_t* small;
+    uint32_t* rem;               // [n_chunks] raw remainders of multi-chunk messages
+    uint32_t* crc;               // [n]
+    uint32_t n_chunks;
+};
+
+__global__ void __launch_bounds__(1024, 1) crc32c_chunks_kernel(CrcParams P) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    CrcSmem& sm = *reinterpret_cast<CrcSmem*>(smem_raw);
+    {
+        const uint4* srcA = reinterpret_cast<const uint4*>(P.tabA);
+        uint4* dstA = reinterpret_cast<uint4*>(&sm.A[0][0][0]);
+        for (uint32_t i = threadIdx.x; i < sizeof(sm.A) / 16; i += blockDim.x) dstA[i] = srcA[i];
+        const uint4* srcS = reinterpret_cast<const uint4*>(P.small);
+        uint4* dstS = reinterpret_cast<uint4*>(&sm.S[0][0][0]);
+        for (uint32_t i = threadIdx.x; i < sizeof(sm.S) / 16; i += blockDim.x) dstS[i] = srcS[i];
+    }
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t quads_per_cta = blockDim.x >> 2;
+    const uint32_t total_quads = gridDim.x * quads_per_cta;
+    for (uint32_t c = blockIdx.x * quads_per_cta + (threadIdx.x >> 2); c < P.n_chunks; c += total_quads) {
+        uint32_t m = c, k = 0;
+        if (P.chunk_msg) {
+            m = P.chunk_msg[c];
+            k = c - P.chunk_first[m];
+        }
+        const uint32_t len = P.len[m];
+        const uint32_t begin = k * kCrcChunk;
+        const uint32_t L = min(kCrcChunk, len - begin);
+        const bool single = len <= kCrcChunk;
+        uint32_t l = 0;
+        if (k == 0) l = (P.init ? P.init[m] : 0u) ^ 0xffffffffu;
+        l = crc_chunk_quad(sm, P.data + P.off[m] + begin, L, l, lane);
+        if ((lane & 3) == 0) {
+            if (single) P.crc[m] = l ^ 0xffffffffu;
+            else P.rem[c] = l;
+        }
+    }
+}
+
+// GF(2)[x] multiply mod P in the reflected domain (bit 31 is x^0).
+__device__ __forceinline__ uint32_t mulmod(uint32_t a, uint32_t b) {
+    uint32_t p = 0;
+#pragma unroll
+    for (int i = 0; i < 32; i++) {
+        p ^= b & (0u - ((a >> (31 - i)) & 1u));
+        b = (b >> 1) ^ (kPolyReflected & (0u - (b & 1u)));
+    }
+    return p;
+}
+
+// x^(8*bytes) mod P
+__device__ uint32_t xpow_bytes(uint64_t bytes) {
+    uint64_t e = bytes << 3;
+    uint32_t r = 0x80000000u;  // x^0
+    for (int j = 0; e; j++, e >>= 1)
+        if (e & 1) r = mulmod(r, c_x2n[j]);
+    return r;
+}
+
+// One warp per multi-chunk message: message remainder = sum over chunks of
+// rem_k * x^(8 * bytes after chunk k).
+__global__ void crc32c_combine_kernel(const uint32_t* __restrict__ multi_list, uint32_t n_multi,
+                                      const uint32_t* __restrict__ chunk_first, const uint32_t* __restrict__ len,
+                                      const uint32_t* __restrict__ rem, uint32_t* __restrict__ crc) {
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t lane = threadIdx.x & 31;
+    if (warp >= n_multi) return;
+    const uint32_t m = multi_list[warp];
+    const uint32_t first = chunk_first[m];
+    const uint32_t K = chunk_first[m + 1] - first;
+    const uint32_t n = len[m];
+    const uint32_t per = (K + 31) / 32;
+    const uint32_t a = min(K, lane * per), b = min(K, a + per);
+    uint32_t acc = 0;
+    if (a < b) {
+        const uint32_t xch = xpow_bytes(kCrcChunk);
+        acc = rem[first + a];
+        for (uint32_t k = a + 1; k < b; k++) {
+            uint32_t lk = min(kCrcChunk, n - k * kCrcChunk);
+            acc = mulmod(acc, lk == kCrcChunk ? xch : xpow_bytes(lk)) ^ rem[first + k];
+        }
+        uint64_t covered = min((uint64_t)n, (uint64_t)b * kCrcChunk);
+        uint64_t after = (uint64_t)n - covered;
+        if (after) acc = mulmod(acc, xpow_bytes(after));
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) acc ^= __shfl_xor_sync(0xffffffffu, acc, s);
+    if (lane == 0) crc[m] = acc ^ 0xffffffffu;
+}
+
+int launch_crc32c(b2c_ctx* ctx, const Layout& L, const uint8_t* d_data, const uint32_t* d_init, uint32_t* d_crc) {
+    if (L.n == 0) return B2C_OK;
+    if (!ctx->crc_attr_done) {  // per device: a ctx is bound to one
+        B2C_CUDA(ctx, cudaFuncSetAttribute(crc32c_chunks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)sizeof(CrcSmem)));
+        ctx->crc_attr_done = true;
+    }
+    uint32_t* d_rem = nullptr;
+    if (L.n_multi) {
+        int rc = ws_reserve(ctx, ctx->ws_misc, (size_t)L.n_chunks * 4);
+        if (rc) return rc;
+        d_rem = static_cast<uint32_t*>(ctx->ws_misc.p);
+    }
+    CrcParams P;
+    P.data = d_data;
+    P.off = L.d_off;
+    P.len = L.d_len;
+    P.init = d_init;
+    P.chunk_msg = L.all_single_chunk_uniform ? nullptr : L.d_chunk_msg;
+    P.chunk_first = L.all_single_chunk_uniform ? nullptr : L.d_chunk_first;
+    P.tabA = ctx->d_crc_tabA;
+    P.small = ctx->d_crc_small;
+    P.rem = d_rem;
+    P.crc = d_crc;
+    P.n_chunks = L.n_chunks;
+    const uint32_t quads_per_cta = 256;
+    uint32_t grid = (L.n_chunks + quads_per_cta - 1) / quads_per_cta;
+    if (grid > (uint32_t)ctx->num_sms) grid = ctx->num_sms;
+    crc32c_chunks_kernel<<<grid, 1024, sizeof(CrcSmem), ctx->stream>>>(P);
+    ctx->launches++;
+    B2C_CUDA(ctx, cudaGetLastError());
+    if (L.n_multi) {
+        uint32_t blocks = (L.n_multi * 32 + 255) / 256;
+        crc32c_combine_kernel<<<blocks, 256, 0, ctx->stream>>>(L.d_multi_list, L.n_multi, L.d_chunk_first, L.d_len,
+                                                                d_rem, d_crc);
+        ctx->launches++;
+        B2C_CUDA(ctx, cudaGetLastError());
+    }
+    return B2C_OK;
+}
+
+}  // namespace b2c

@@ -1,0 +1,185 @@
+/*
+ * b2c_codec.h — C ABI of the B200 batch payload codec (libb2c.so).
+ *
+ * Drop-in boundary for bRPC's one data-parallel hot path: snappy compress /
+ * decompress and CRC32C over many independent RPC message bodies.  Plain
+ * pointers and sizes only; no C++ or torch types.  Each entry point cites the
+ * reference interface (bRPC 1.4.0, paths relative to the reference root) it
+ * replaces.  INTEGRATION.md shows the bRPC-side binding.
+ *
+ * Results are bit-exact with the reference: compressed bytes equal
+ * butil::snappy::RawCompress, decompressed bytes / accept-reject decisions
+ * equal butil::snappy::Uncompress(Source*,Sink*), CRCs equal
+ * butil::crc32c::Extend.
+ *
+ * Conventions
+ *   - every function returning int returns B2C_OK (0) or a negative B2C_E_*
+ *     infrastructure error; b2c_last_error(ctx) has the text.
+ *   - per-message results live in status arrays: B2C_OK, B2C_CORRUPT (the
+ *     reference would return false for this message) or B2C_TOO_SMALL.
+ *   - a "layout" describes n messages inside one arena: message i occupies
+ *     bytes [off[i], off[i]+len[i]).
+ *   - *_dev entry points take DEVICE pointers and enqueue work on the ctx
+ *     stream; they do not synchronise (call b2c_ctx_sync).  *_batch entry
+ *     points take HOST memory (iovec block lists in, flat buffers out) and
+ *     return when the results are in host memory.
+ *   - thread safety: one ctx may be used by one thread at a time; create one
+ *     ctx per worker thread (or guard it) — all ctxs on a device share it.
+ */
+#ifndef B2C_CODEC_H_
+#define B2C_CODEC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2C_OK 0
+#define B2C_CORRUPT 1   /* malformed snappy stream: reference returns false (snappy.cc:867) */
+#define B2C_TOO_SMALL 2 /* output slot smaller than the stream's uncompressed length */
+
+#define B2C_E_CUDA (-1)     /* CUDA runtime/driver failure (text in b2c_last_error) */
+#define B2C_E_ARG (-2)      /* invalid argument */
+#define B2C_E_NOMEM (-3)    /* host or device allocation failed */
+#define B2C_E_CAPACITY (-4) /* caller-provided output buffer too small */
+#define B2C_E_NODEVICE (-5) /* no usable CUDA device: the codec has no CPU fallback */
+
+typedef struct b2c_ctx b2c_ctx;
+typedef struct b2c_layout b2c_layout;
+
+/* Layout-identical to butil's `struct const_iovec` (src/butil/iobuf.h:40-44);
+ * one entry per IOBuf BlockRef as returned by IOBuf::backing_block(i)
+ * (src/butil/iobuf.cpp:1504-1510). */
+typedef struct b2c_iovec {
+    const void* iov_base;
+    size_t iov_len;
+} b2c_iovec;
+
+/* ---- context ----------------------------------------------------------- */
+
+/* Bind a codec context to CUDA device `device` (streams, lookup tables, pinned
+ * staging, device workspace).  Fails with B2C_E_NODEVICE when there is no GPU.
+ * Replaces nothing in the reference (its codec is stateless); it is the state
+ * behind the handlers registered at src/brpc/global.cpp:389-393. */
+int b2c_ctx_create(int device, b2c_ctx** ctx);
+void b2c_ctx_destroy(b2c_ctx* ctx);
+const char* b2c_last_error(const b2c_ctx* ctx);
+int b2c_ctx_device(const b2c_ctx* ctx);
+/* cudaStream_t of the ctx, as an opaque pointer */
+void* b2c_ctx_stream(b2c_ctx* ctx);
+int b2c_ctx_sync(b2c_ctx* ctx);
+/* Number of kernels this ctx has launched so far (bench.py's gpu_launches). */
+uint64_t b2c_ctx_launch_count(const b2c_ctx* ctx);
+
+/* Device memory / transfer / timing helpers so that hosts without their own
+ * CUDA binding can drive the *_dev entry points. */
+int b2c_dev_alloc(b2c_ctx* ctx, size_t bytes, void** d_ptr);
+int b2c_dev_free(b2c_ctx* ctx, void* d_ptr);
+int b2c_host_alloc_pinned(b2c_ctx* ctx, size_t bytes, void** h_ptr);
+int b2c_host_free_pinned(b2c_ctx* ctx, void* h_ptr);
+int b2c_memcpy_h2d(b2c_ctx* ctx, void* d_dst, const void* h_src, size_t bytes); /* async on ctx stream */
+int b2c_memcpy_d2h(b2c_ctx* ctx, void* h_dst, const void* d_src, size_t bytes); /* async on ctx stream */
+int b2c_memset_dev(b2c_ctx* ctx, void* d_dst, int value, size_t bytes);
+typedef struct b2c_event b2c_event;
+int b2c_event_create(b2c_ctx* ctx, b2c_event** ev);
+void b2c_event_destroy(b2c_event* ev);
+int b2c_event_record(b2c_ctx* ctx, b2c_event* ev);                /* on the ctx stream */
+int b2c_event_elapsed_ms(b2c_event* start, b2c_event* stop, float* ms); /* syncs on stop */
+
+/* ---- pure host helpers ------------------------------------------------- */
+
+/* snappy::MaxCompressedLength — src/butil/third_party/snappy/snappy.cc:55-77 */
+size_t b2c_snappy_max_compressed_length(size_t source_len);
+/* snappy::GetUncompressedLength(const char*, size_t, size_t*) — snappy.cc:235-244
+ * (strict varint, snappy-stubs-internal.h:325-347).  Returns 1/0 like the reference's bool. */
+int b2c_snappy_get_uncompressed_length(const void* compressed, size_t n, uint32_t* result);
+/* SnappyDecompressor::ReadUncompressedLength — snappy.cc:692-711: the lenient
+ * preamble parse that Uncompress(Source*,Sink*) (and so brpc's SnappyDecompress)
+ * uses.  Returns the number of preamble bytes, 0 on failure. */
+int b2c_snappy_read_preamble(const void* compressed, size_t n, uint32_t* result);
+/* butil::crc32c::Mask / Unmask — src/butil/crc32c.h:38-47 */
+uint32_t b2c_crc32c_mask(uint32_t crc);
+uint32_t b2c_crc32c_unmask(uint32_t masked_crc);
+
+/* ---- layouts ----------------------------------------------------------- */
+
+/* Describe n messages in an arena: host arrays off[n] (byte offsets) and len[n].
+ * The arrays are copied; derived work lists (64 KiB snappy fragments —
+ * snappy.cc:887-948 — and CRC chunks) are precomputed and uploaded.  The
+ * reference has no such object: it walks one IOBuf at a time
+ * (IOBufAsSnappySource, src/butil/iobuf.cpp:2062-2090). */
+int b2c_layout_create(b2c_ctx* ctx, uint32_t n, const uint64_t* off, const uint32_t* len,
+                      b2c_layout** layout);
+void b2c_layout_destroy(b2c_layout* layout);
+uint32_t b2c_layout_count(const b2c_layout* layout);
+/* sum of len[] */
+uint64_t b2c_layout_payload_bytes(const b2c_layout* layout);
+/* one past the last arena byte any message touches */
+uint64_t b2c_layout_arena_bytes(const b2c_layout* layout);
+/* sum over messages of MaxCompressedLength(len[i]) + 5: capacity that always
+ * suffices for b2c_snappy_compress_dev's packed output */
+uint64_t b2c_layout_max_compressed_bytes(const b2c_layout* layout);
+
+/* ---- device-resident entry points -------------------------------------- */
+
+/* d_crc[i] = butil::crc32c::Extend(d_init ? d_init[i] : 0, msg_i, len_i)
+ * — src/butil/crc32c.cc:451-454 / crc32c.h:19-29 (Value == Extend(0,...)). */
+int b2c_crc32c_dev(b2c_ctx* ctx, const b2c_layout* layout, const void* d_data,
+                   const uint32_t* d_init, uint32_t* d_crc);
+
+/* For every message: the exact byte stream butil::snappy::Compress(Source*,Sink*)
+ * produces (snappy.cc:875-954; what brpc::policy::SnappyCompress(const IOBuf&,
+ * IOBuf*) appends, src/brpc/policy/snappy_compress.cpp:51-55).  Streams are
+ * packed back to back in d_out; d_out_off[n+1] (device) receives their offsets
+ * (stream i = [d_out_off[i], d_out_off[i+1])).  d_out must hold out_cap >=
+ * b2c_layout_max_compressed_bytes(layout) bytes. */
+int b2c_snappy_compress_dev(b2c_ctx* ctx, const b2c_layout* layout, const void* d_in,
+                            void* d_out, uint64_t out_cap, uint64_t* d_out_off);
+
+/* d_ulen[i] / d_status[i]: lenient preamble of stream i (snappy.cc:692-711);
+ * status B2C_CORRUPT where the reference's ReadUncompressedLength fails. */
+int b2c_snappy_uncompressed_length_dev(b2c_ctx* ctx, const b2c_layout* in_layout, const void* d_in,
+                                       uint32_t* d_ulen, int32_t* d_status);
+
+/* butil::snappy::Uncompress(Source*,Sink*) per message (snappy.cc:1526-1552,
+ * tag loop 716-787; what brpc::policy::SnappyDecompress(const IOBuf&, IOBuf*)
+ * runs, snappy_compress.cpp:57-61).  Stream i is decoded into
+ * d_out + out_layout.off[i]; out_layout.len[i] is the slot capacity.
+ * d_status[i] = B2C_OK iff the reference returns true (then d_ulen[i] bytes were
+ * written), B2C_CORRUPT iff it returns false, B2C_TOO_SMALL when the preamble
+ * asks for more than the slot.  d_ulen may be NULL. */
+int b2c_snappy_decompress_dev(b2c_ctx* ctx, const b2c_layout* in_layout, const void* d_in,
+                              const b2c_layout* out_layout, void* d_out, uint32_t* d_ulen,
+                              int32_t* d_status);
+
+/* ---- host (end-to-end) entry points ------------------------------------- */
+/* Message i is the concatenation of segs[seg_begin[i] .. seg_begin[i+1]) — the
+ * BlockRefs of one IOBuf (src/butil/iobuf.h:74-101).  Inputs are gathered into
+ * pinned staging, moved with async H2D copies, processed, and results copied
+ * back into the caller's flat buffers. */
+
+/* brpc::policy::SnappyCompress(const IOBuf&, IOBuf*) for a batch
+ * (snappy_compress.cpp:51-55).  out_off[n+1]: stream i = out[out_off[i], out_off[i+1]). */
+int b2c_snappy_compress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin,
+                              uint32_t n, void* out, uint64_t out_cap, uint64_t* out_off);
+
+/* brpc::policy::SnappyDecompress(const IOBuf&, IOBuf*) for a batch
+ * (snappy_compress.cpp:57-61).  Decoded message i = out[out_off[i], out_off[i+1]);
+ * status[i] as for b2c_snappy_decompress_dev (a failed message occupies 0 bytes). */
+int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin,
+                                uint32_t n, void* out, uint64_t out_cap, uint64_t* out_off,
+                                int32_t* status);
+
+/* butil::crc32c::Extend for a batch (crc32c.h:19-29); init may be NULL (== Value). */
+int b2c_crc32c_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n,
+                     const uint32_t* init, uint32_t* crc);
+
+/* Bytes the last *_batch call moved over PCIe (bench.py's e2e accounting). */
+void b2c_last_transfer_bytes(const b2c_ctx* ctx, uint64_t* h2d, uint64_t* d2h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2C_CODEC_H_ */

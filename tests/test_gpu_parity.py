@@ -1,0 +1,345 @@
+"""GPU parity tests (run on the B200 box with -m gpu): the CUDA path, called
+through the C ABI (libb2c.so), against the CPU oracle on the same inputs."""
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from tests.util import assert_bytes_equal, pack, pack_tight, slices
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def codec():
+    import brpc_b200
+    c = brpc_b200.Codec(0)
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
+def cpu():
+    return O.best()
+
+
+SIZES = [0, 1, 3, 4, 5, 14, 15, 16, 17, 31, 32, 33, 59, 60, 61, 62, 63, 64, 65, 100, 127, 128, 129, 255, 256, 257, 782,
+         1000, 1023, 1024, 1025, 2047, 2048, 2049, 4095, 4096, 4097, 8160, 8161, 12435, 16384, 32768, 65535, 65536,
+         65537, 70000, 131072, 200000]
+
+
+# ---------------------------------------------------------------- CRC32C
+def test_crc_known_answers(codec, cpu, golden):
+    msgs = [bytes.fromhex(e["in"]) for e in golden["crc"]["rfc3720"]] + [b"123456789", b"hello world", b"a", b"foo", b""]
+    want = [e["crc"] for e in golden["crc"]["rfc3720"]] + [0xE3069283, golden["crc"]["hello_world"],
+                                                            cpu.crc32c(b"a"), cpu.crc32c(b"foo"), 0]
+    arena, off, ln = pack(msgs)
+    got = codec.crc32c(arena, off, ln)
+    assert [int(x) for x in got] == want
+
+
+def test_crc_parity_sweep_with_init_and_misalignment(codec, cpu):
+    rng = np.random.default_rng(3)
+    lens = list(range(0, 200)) + SIZES + [1 << 20, (4 << 20) + 3]
+    msgs = [rng.integers(0, 256, n, dtype=np.uint8).tobytes() for n in lens]
+    for align in (16, 1):
+        arena, off, ln = pack(msgs, align=align)
+        if align == 1:  # also shift the whole arena by 3 bytes
+            arena = np.concatenate([np.zeros(3, np.uint8), arena])
+            off = off + np.uint64(3)
+        init = rng.integers(0, 2**32, len(msgs), dtype=np.uint32)
+        got0 = codec.crc32c(arena, off, ln)
+        got1 = codec.crc32c(arena, off, ln, init=init)
+        for i, m in enumerate(msgs):
+            assert int(got0[i]) == cpu.crc32c(m), (align, i, len(m))
+            assert int(got1[i]) == cpu.crc32c_extend(int(init[i]), m), (align, i, len(m))
+
+
+def test_crc_extend_composition(codec, cpu):
+    # crc32c_unittest.cc:59-62: Extend(Value(A), B) == Value(A||B), on the GPU
+    rng = np.random.default_rng(4)
+    A = [rng.integers(0, 256, n, dtype=np.uint8).tobytes() for n in (6, 100, 5000, 70000)]
+    B = [rng.integers(0, 256, n, dtype=np.uint8).tobytes() for n in (5, 4097, 63, 9000)]
+    a_arena, a_off, a_len = pack(A)
+    b_arena, b_off, b_len = pack(B)
+    ab_arena, ab_off, ab_len = pack([x + y for x, y in zip(A, B)])
+    ca = codec.crc32c(a_arena, a_off, a_len)
+    cab = codec.crc32c(b_arena, b_off, b_len, init=ca)
+    whole = codec.crc32c(ab_arena, ab_off, ab_len)
+    assert (cab == whole).all()
+    assert int(codec.crc32c(*pack([b"hello world"]))[0]) == cpu.crc32c_extend(cpu.crc32c(b"hello "), b"world")
+
+
+def test_crc_c1_shape(codec, cpu):
+    # BASELINE configs[0]: 4096 x 4 KB echo payloads
+    arena, off, ln = O.corpus_batch("words", np.full(4096, 4096, dtype=np.uint32))
+    got = codec.crc32c(arena, off, ln)
+    want, _ = cpu.batch_crc32c(arena, off, ln, threads=8)
+    assert (got == want).all()
+
+
+# ---------------------------------------------------------------- compress
+def _check_compress(codec, cpu, arena, off, ln, label):
+    packed, out_off = codec.compress(arena, off, ln)
+    w_out, w_off, w_len, _ = cpu.batch_compress(arena, off, ln, threads=8)
+    got_len = np.diff(out_off).astype(np.uint32)
+    bad = np.nonzero(got_len != w_len)[0]
+    for i in range(len(ln)):
+        g = packed[int(out_off[i]):int(out_off[i + 1])].tobytes()
+        w = w_out[int(w_off[i]):int(w_off[i]) + int(w_len[i])].tobytes()
+        assert_bytes_equal(g, w, f"{label} msg {i} len {int(ln[i])} (len mismatches: {len(bad)})")
+    return packed, out_off
+
+
+@pytest.mark.parametrize("kind", ["az09", "rand62", "words"])
+def test_compress_parity_sizes(codec, cpu, kind):
+    arena, off, ln = O.corpus_batch(kind, np.array(SIZES + [1 << 20, (1 << 20) + 77], dtype=np.uint32), first_index=5)
+    _check_compress(codec, cpu, arena, off, ln, kind)
+
+
+def test_compress_golden_fixtures(codec, cpu, golden):
+    # committed fixtures generated from the reference's own code (tests/golden/make_golden.py)
+    vec = [e for e in golden["vectors"] if e["n"] <= 70000]
+    msgs = [O.corpus(e["corpus"], e["n"], e["index"]).tobytes() for e in vec]
+    arena, off, ln = pack(msgs)
+    packed, out_off = codec.compress(arena, off, ln)
+    crc = codec.crc32c(arena, off, ln)
+    for i, e in enumerate(vec):
+        z = packed[int(out_off[i]):int(out_off[i + 1])].tobytes()
+        assert len(z) == e["clen"], e
+        assert z[:16].hex() == e["head"], e
+        assert cpu.crc32c(z) == e["ccrc"], e
+        assert int(crc[i]) == e["crc"], e
+        if "z" in e:
+            assert z.hex() == e["z"]
+
+
+def test_compress_low_entropy_and_runs(codec, cpu):
+    rng = np.random.default_rng(9)
+    msgs = [bytes(65536), b"\xff" * 4096, b"ab" * 3000, bytes(300) + O.corpus("rand62", 700, 3).tobytes() + bytes(300)]
+    for t in range(120):
+        n = int(rng.integers(1, 9000 if t % 8 else 70000))
+        msgs.append(rng.integers(0, int(rng.integers(2, 6)), n, dtype=np.uint8).tobytes())
+    for t in range(40):
+        n = int(rng.integers(1, 5000))
+        d = rng.integers(0, 256, n, dtype=np.uint8)
+        if n > 64:
+            a = int(rng.integers(0, n // 2))
+            d[a:a + n // 3] = d[0]  # long run inside random bytes
+        msgs.append(d.tobytes())
+    arena, off, ln = pack(msgs, align=1)  # arbitrary alignment of every message
+    _check_compress(codec, cpu, arena, off, ln, "low-entropy")
+
+
+def test_compress_c1_shape(codec, cpu):
+    for kind in ("words", "az09", "rand62"):
+        arena, off, ln = O.corpus_batch(kind, np.full(4096, 4096, dtype=np.uint32))
+        _check_compress(codec, cpu, arena, off, ln, f"C1 {kind}")
+
+
+def test_compress_c2_shape_sample(codec, cpu):
+    arena, off, ln = O.corpus_batch("words", np.full(65536, 1024, dtype=np.uint32), first_index=1000)
+    _check_compress(codec, cpu, arena, off, ln, "C2 words")
+
+
+def test_compress_c3_shape(codec, cpu):
+    arena, off, ln = O.corpus_batch("words", np.full(16, 1 << 20, dtype=np.uint32), first_index=9)
+    packed, out_off = _check_compress(codec, cpu, arena, off, ln, "C3 words")
+    assert packed[:3].tobytes() == bytes([0x80, 0x80, 0x40])  # varint(1 MiB)
+
+
+def test_compress_empty_batch_and_empty_messages(codec, cpu):
+    packed, out_off = codec.compress(np.zeros(64, np.uint8), np.zeros(0, np.uint64), np.zeros(0, np.uint32))
+    assert len(packed) == 0 and list(out_off) == [0]
+    arena, off, ln = pack([b"", b"", b"x", b""])
+    packed, out_off = codec.compress(arena, off, ln)
+    assert packed.tobytes() == b"\x00" + b"\x00" + b"\x01\x00x" + b"\x00"
+
+
+# ---------------------------------------------------------------- decompress
+def _decompress(codec, streams, caps=None):
+    arena, off, ln = pack_tight(streams)
+    if caps is None:
+        caps = []
+        for s in streams:
+            v = O.port().ulen_lenient(s) if len(s) else None
+            caps.append(v if v is not None and v < (1 << 26) else 0)
+    caps = np.array(caps, dtype=np.uint32)
+    o_off = np.zeros(len(caps), dtype=np.uint64)
+    if len(caps):
+        o_off[1:] = np.cumsum(caps[:-1].astype(np.uint64))
+    out, ulen, status = codec.decompress(arena, off, ln, o_off, caps)
+    return out, o_off, ulen, status
+
+
+@pytest.mark.parametrize("kind", ["az09", "rand62", "words"])
+def test_decompress_roundtrip_sizes(codec, cpu, kind):
+    msgs = [O.corpus(kind, n, 11 + i).tobytes() for i, n in enumerate(SIZES + [1 << 20])]
+    streams = [cpu.compress(m) for m in msgs]
+    out, o_off, ulen, status = _decompress(codec, streams)
+    assert (status == 0).all(), np.nonzero(status)[0]
+    for i, m in enumerate(msgs):
+        assert int(ulen[i]) == len(m)
+        assert_bytes_equal(out[int(o_off[i]):int(o_off[i]) + len(m)].tobytes(), m, f"{kind} msg {i} n={len(m)}")
+
+
+def test_decompress_malformed_known_answers(codec, golden):
+    # SURVEY Appendix B + extras; expected answers recorded from the reference library
+    es = [e for e in golden["malformed"] if e["stream"]]
+    streams = [bytes.fromhex(e["stream"]) for e in es]
+    out, o_off, ulen, status = _decompress(codec, streams)
+    for i, e in enumerate(es):
+        if e["uncompress"]:
+            assert status[i] == 0, e
+            n = len(bytes.fromhex(e["out"]))
+            assert out[int(o_off[i]):int(o_off[i]) + n].tobytes().hex() == e["out"], e
+        else:
+            assert status[i] != 0, e
+
+
+def test_decompress_corrupted_streams_agree_with_oracle(codec, cpu):
+    rng = np.random.default_rng(11)
+    base = [cpu.compress(O.corpus(k, n, i)) for k in ("words", "az09", "rand62") for i, n in enumerate((40, 300, 5000, 70000))]
+    streams = []
+    for t in range(2000):
+        z = bytearray(base[t % len(base)])
+        mode = t % 4
+        if mode == 0:
+            z[int(rng.integers(0, len(z)))] = int(rng.integers(0, 256))
+        elif mode == 1:
+            del z[int(rng.integers(1, len(z))):]
+        elif mode == 2:
+            z += bytes(rng.integers(0, 256, int(rng.integers(1, 6)), dtype=np.uint8))
+        else:
+            for _ in range(3):
+                z[int(rng.integers(0, len(z)))] ^= 1 << int(rng.integers(0, 8))
+        streams.append(bytes(z))
+    out, o_off, ulen, status = _decompress(codec, streams)
+    n_ok = 0
+    for i, s in enumerate(streams):
+        cap = O.port().ulen_lenient(s)
+        if cap is None or cap >= (1 << 26):
+            assert status[i] != 0
+            continue
+        ok, want = cpu.uncompress(s, cap=cap)
+        assert (status[i] == 0) == ok, (i, s[:24].hex(), int(status[i]), ok)
+        if ok:
+            n_ok += 1
+            assert_bytes_equal(out[int(o_off[i]):int(o_off[i]) + len(want)].tobytes(), want, f"corrupted {i}")
+    assert 0 < n_ok < len(streams)
+
+
+def test_decompress_too_small_and_ulen(codec, cpu):
+    streams = [cpu.compress(O.corpus("words", n, n)) for n in (100, 1000, 10000)]
+    out, o_off, ulen, status = _decompress(codec, streams, caps=[100, 999, 20000])
+    assert list(status) == [0, 2, 0] and list(ulen) == [100, 1000, 10000]
+    arena, off, ln = pack_tight(streams + [b"\xff\xff\xff\xff\xff\x01", b""])
+    u, st = codec.uncompressed_lengths(arena, off, ln)
+    assert list(u[:3]) == [100, 1000, 10000] and list(st) == [0, 0, 0, 1, 1]
+
+
+def test_decompress_foreign_encoder_features(codec):
+    # copy-4 tags, offsets beyond 64 KiB and overlapping (RLE) copies — never emitted by the
+    # reference compressor but accepted by its decoder (snappy.h:199-201)
+    lit = bytes(range(256)) * 300  # 76800 bytes
+    def literal(b):
+        n = len(b) - 1
+        return bytes([62 << 2]) + n.to_bytes(3, "little") + b
+    body = literal(lit) + bytes([3 | (63 << 2)]) + (70000).to_bytes(4, "little") + bytes([2 | (63 << 2)]) + (1).to_bytes(2, "little")
+    total = len(lit) + 128
+    pre = bytearray()
+    v = total
+    while v >= 128:
+        pre.append((v & 0x7f) | 0x80)
+        v >>= 7
+    pre.append(v)
+    s = bytes(pre) + body
+    ok, want = O.port().uncompress(s)
+    assert ok
+    out, o_off, ulen, status = _decompress(codec, [s])
+    assert status[0] == 0
+    assert_bytes_equal(out[:total].tobytes(), want, "foreign")
+
+
+# ---------------------------------------------------------------- end-to-end host API
+def test_e2e_iovec_batches(codec, cpu):
+    import brpc_b200
+    rng = np.random.default_rng(21)
+    # C2 shape: 1 KiB bodies cut once at a random place; C3 shape: 1 MiB in 8160-byte blocks
+    arena2, off2, ln2 = O.corpus_batch("words", np.full(20000, 1024, dtype=np.uint32), first_index=77)
+    segs2, sb2 = brpc_b200.make_iovecs(arena2, off2, ln2, cuts=rng.integers(0, 1025, len(ln2)))
+    arena3, off3, ln3 = O.corpus_batch("words", np.array([1 << 20, 12435, 0, 1, (1 << 20) + 5], dtype=np.uint32))
+    segs3, sb3 = brpc_b200.make_iovecs(arena3, off3, ln3, seg_bytes=8160)
+    for arena, off, ln, segs, sb in ((arena2, off2, ln2, segs2, sb2), (arena3, off3, ln3, segs3, sb3)):
+        crc = codec.crc32c_batch(segs, sb)
+        want_crc, _ = cpu.batch_crc32c(arena, off, ln, threads=8)
+        assert (crc == want_crc).all()
+        cap = int(sum(32 + int(l) + int(l) // 6 + 5 for l in ln))
+        out = np.empty(cap, dtype=np.uint8)
+        out_off = codec.compress_batch(segs, sb, out)
+        w_out, w_off, w_len, _ = cpu.batch_compress(arena, off, ln, threads=8)
+        assert (np.diff(out_off).astype(np.uint32) == w_len).all()
+        for i in range(0, len(ln), max(1, len(ln) // 500)):
+            assert_bytes_equal(out[int(out_off[i]):int(out_off[i + 1])].tobytes(),
+                               w_out[int(w_off[i]):int(w_off[i]) + int(w_len[i])].tobytes(), f"e2e msg {i}")
+        # feed the compressed streams back, in 100-byte blocks
+        csegs, csb = brpc_b200.make_iovecs(out, out_off[:-1], np.diff(out_off).astype(np.uint32), seg_bytes=100)
+        back = np.empty(int(ln.astype(np.uint64).sum()) + 64, dtype=np.uint8)
+        b_off, status = codec.decompress_batch(csegs, csb, back)
+        assert (status == 0).all()
+        assert (np.diff(b_off).astype(np.uint32) == ln).all()
+        for i in range(0, len(ln), max(1, len(ln) // 500)):
+            a, b = int(off[i]), int(off[i]) + int(ln[i])
+            assert_bytes_equal(back[int(b_off[i]):int(b_off[i + 1])].tobytes(), arena[a:b].tobytes(), f"e2e back {i}")
+        h2d, d2h = codec.last_transfer_bytes()
+        assert h2d > 0 and d2h > 0
+
+
+def test_e2e_decompress_rejects_like_reference(codec, golden):
+    import brpc_b200
+    es = [e for e in golden["malformed"] if e["stream"]]
+    arena, off, ln = pack_tight([bytes.fromhex(e["stream"]) for e in es])
+    segs, sb = brpc_b200.make_iovecs(arena, off, ln)
+    out = np.empty(1 << 16, dtype=np.uint8)
+    o_off, status = codec.decompress_batch(segs, sb, out)
+    for i, e in enumerate(es):
+        assert (status[i] == 0) == e["uncompress"], e
+        if e["uncompress"]:
+            n = len(bytes.fromhex(e["out"]))
+            assert out[int(o_off[i]):int(o_off[i]) + n].tobytes().hex() == e["out"]
+
+
+# ---------------------------------------------------------------- full-size properties
+def test_c2_full_size_roundtrip_properties(codec, cpu):
+    """BASELINE configs[1] at full size (2^20 x 1 KiB): compress -> decompress round trip,
+    CRC of every decoded body equals CRC of the original, and an oracle check on a sample."""
+    n = 1 << 20
+    arena, off, ln = O.corpus_batch("words", np.full(n, 1024, dtype=np.uint32), first_index=0)
+    lay = codec.layout(off, ln)
+    d_in = codec.to_device(arena)
+    d_crc = codec.alloc(4 * n)
+    codec.crc32c_dev(lay, d_in, d_crc)
+    d_out = codec.alloc(lay.max_compressed_bytes + 64)
+    d_off = codec.alloc(8 * (n + 1))
+    codec.compress_dev(lay, d_in, d_out, d_off)
+    out_off = codec.d2h(d_off, 8 * (n + 1), np.uint64)
+    total = int(out_off[-1])
+    clay = codec.layout(out_off[:-1], np.diff(out_off).astype(np.uint32))
+    d_back = codec.alloc(int(lay.arena_bytes) + 64)
+    d_st = codec.alloc(4 * n)
+    codec.decompress_dev(clay, d_out, lay, d_back, d_st)
+    d_crc2 = codec.alloc(4 * n)
+    codec.crc32c_dev(lay, d_back, d_crc2)
+    st = codec.d2h(d_st, 4 * n, np.int32)
+    c1 = codec.d2h(d_crc, 4 * n, np.uint32)
+    c2 = codec.d2h(d_crc2, 4 * n, np.uint32)
+    assert (st == 0).all()
+    assert (c1 == c2).all()
+    # sample against the oracle: CRCs and compressed bytes of 4096 evenly spaced messages
+    idx = np.arange(0, n, n // 4096)
+    packed = codec.d2h(d_out, total)
+    want_crc, _ = cpu.batch_crc32c(arena, off[idx], ln[idx], threads=8)
+    assert (c1[idx] == want_crc).all()
+    w_out, w_off, w_len, _ = cpu.batch_compress(arena, off[idx], ln[idx], threads=8)
+    for j, i in enumerate(idx):
+        assert_bytes_equal(packed[int(out_off[i]):int(out_off[i + 1])].tobytes(),
+                           w_out[int(w_off[j]):int(w_off[j]) + int(w_len[j])].tobytes(), f"C2 full msg {i}")
