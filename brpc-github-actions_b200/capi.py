@@ -49,6 +49,8 @@ SYMBOLS = {
     "b2c_event_destroy": (None, [_vp]),
     "b2c_event_record": (C.c_int, [_vp, _vp]),
     "b2c_event_elapsed_ms": (C.c_int, [_vp, _vp, C.POINTER(C.c_float)]),
+    "b2c_prof_enable": (C.c_int, [_vp, C.c_int]),
+    "b2c_prof_total_ms": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float), _u32p]),
     "b2c_snappy_max_compressed_length": (C.c_size_t, [C.c_size_t]),
     "b2c_snappy_get_uncompressed_length": (C.c_int, [_vp, C.c_size_t, _u32p]),
     "b2c_snappy_read_preamble": (C.c_int, [_vp, C.c_size_t, _u32p]),
@@ -383,6 +385,14 @@ class Codec:
                                                          out.ctypes.data, out.nbytes, _ptr(out_off, _u64p),
                                                          _ptr(status, _i32p)))
         return out_off, status
+
+    def prof_enable(self, on: bool = True):
+        self._check(self.lib.b2c_prof_enable(self.ctx, 1 if on else 0))
+
+    def prof_total_ms(self, which: int):
+        ms, cnt = C.c_float(0), C.c_uint32(0)
+        self._check(self.lib.b2c_prof_total_ms(self.ctx, which, C.byref(ms), C.byref(cnt)))
+        return float(ms.value), int(cnt.value)
 
     def last_transfer_bytes(self):
         a, b = C.c_uint64(0), C.c_uint64(0)

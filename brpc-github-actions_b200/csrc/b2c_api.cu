@@ -60,6 +60,19 @@ static int pin_reserve(b2c_ctx* ctx, void** p, size_t* cap, size_t bytes) {
     return B2C_OK;
 }
 
+void prof_mark(b2c_ctx* ctx, int which) {
+    if (!ctx->prof_on) return;
+    auto& v = ctx->prof_ev[which];
+    uint32_t& used = ctx->prof_used[which];
+    if (used >= 1024) return;
+    if (used >= v.size()) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        v.push_back(e);
+    }
+    cudaEventRecord(v[used++], ctx->stream);
+}
+
 template <typename T>
 static int upload(b2c_ctx* ctx, T** d, const std::vector<T>& h) {
     *d = nullptr;
@@ -139,6 +152,8 @@ void b2c_ctx_destroy(b2c_ctx* ctx) {
     if (ctx->h_pin_out) cudaFreeHost(ctx->h_pin_out);
     if (ctx->d_crc_tabA) cudaFree(ctx->d_crc_tabA);
     if (ctx->d_crc_small) cudaFree(ctx->d_crc_small);
+    for (auto& v : ctx->prof_ev)
+        for (cudaEvent_t e : v) cudaEventDestroy(e);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
@@ -219,6 +234,29 @@ int b2c_event_elapsed_ms(b2c_event* start, b2c_event* stop, float* ms) {
     if (!start || !stop || !ms) return B2C_E_ARG;
     if (cudaEventSynchronize(stop->ev) != cudaSuccess) return B2C_E_CUDA;
     if (cudaEventElapsedTime(ms, start->ev, stop->ev) != cudaSuccess) return B2C_E_CUDA;
+    return B2C_OK;
+}
+
+int b2c_prof_enable(b2c_ctx* ctx, int on) {
+    if (!ctx) return B2C_E_ARG;
+    B2C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->prof_on = on != 0;
+    for (auto& u : ctx->prof_used) u = 0;
+    return B2C_OK;
+}
+
+int b2c_prof_total_ms(b2c_ctx* ctx, int which, float* total_ms, uint32_t* launches) {
+    if (!ctx || which < 0 || which >= B2C_PROF_COUNT || !total_ms) return B2C_E_ARG;
+    B2C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    float sum = 0;
+    uint32_t pairs = ctx->prof_used[which] / 2;
+    for (uint32_t i = 0; i < pairs; i++) {
+        float ms = 0;
+        B2C_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->prof_ev[which][2 * i], ctx->prof_ev[which][2 * i + 1]));
+        sum += ms;
+    }
+    *total_ms = sum;
+    if (launches) *launches = pairs;
     return B2C_OK;
 }
 

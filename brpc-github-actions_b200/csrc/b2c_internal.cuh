@@ -79,6 +79,10 @@ struct b2c_ctx {
     size_t h_pin_in_cap = 0;
     void* h_pin_out = nullptr;
     size_t h_pin_out_cap = 0;
+    // optional kernel timing (b2c_prof_*)
+    bool prof_on = false;
+    std::vector<cudaEvent_t> prof_ev[B2C_PROF_COUNT];  // start/stop pairs
+    uint32_t prof_used[B2C_PROF_COUNT] = {0, 0, 0, 0};
 };
 
 struct b2c_layout : b2c::Layout {};
@@ -97,6 +101,9 @@ int ws_reserve(b2c_ctx* ctx, DevBuf& b, size_t bytes);
         cudaError_t _e = (call);                                    \
         if (_e != cudaSuccess) return b2c::set_err((ctx), B2C_E_CUDA, #call, _e); \
     } while (0)
+
+// records an event on the ctx stream when profiling is on (start = even slots, stop = odd)
+void prof_mark(b2c_ctx* ctx, int which);
 
 // kernels' host launchers (defined in the .cu files)
 int crc_tables_init(b2c_ctx* ctx);

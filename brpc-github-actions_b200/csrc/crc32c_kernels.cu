@@ -304,7 +304,9 @@ int launch_crc32c(b2c_ctx* ctx, const Layout& L, const uint8_t* d_data, const ui
     const uint32_t quads_per_cta = 256;
     uint32_t grid = (L.n_chunks + quads_per_cta - 1) / quads_per_cta;
     if (grid > (uint32_t)ctx->num_sms) grid = ctx->num_sms;
+    prof_mark(ctx, B2C_PROF_CRC32C);
     crc32c_chunks_kernel<<<grid, 1024, sizeof(CrcSmem), ctx->stream>>>(P);
+    prof_mark(ctx, B2C_PROF_CRC32C);
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
     if (L.n_multi) {

@@ -416,6 +416,7 @@ int launch_compress(b2c_ctx* ctx, const Layout& L, const uint8_t* d_in, uint8_t*
 
     static const uint32_t class_entries[3] = {1024, 4096, 16384};
     static const uint32_t class_warps[3] = {8, 4, 1};
+    prof_mark(ctx, B2C_PROF_COMPRESS);
     for (int c = 0; c < 3; c++) {
         if (!L.n_class[c]) continue;
         CompressParams P;
@@ -437,6 +438,8 @@ int launch_compress(b2c_ctx* ctx, const Layout& L, const uint8_t* d_in, uint8_t*
         ctx->launches++;
         B2C_CUDA(ctx, cudaGetLastError());
     }
+    prof_mark(ctx, B2C_PROF_COMPRESS);
+    prof_mark(ctx, B2C_PROF_PACK);
     snappy_message_sizes_kernel<<<(L.n + 255) / 256, 256, 0, ctx->stream>>>(L.d_len, L.d_frag_first, d_frag_clen,
                                                                              d_frag_rel, d_msg_clen, L.n);
     ctx->launches++;
@@ -447,6 +450,7 @@ int launch_compress(b2c_ctx* ctx, const Layout& L, const uint8_t* d_in, uint8_t*
     const uint32_t blocks = (uint32_t)((warps * 32 + 255) / 256);
     snappy_gather_kernel<<<blocks, 256, 0, ctx->stream>>>(L.d_len, L.d_frag_msg, L.d_frag_slot, d_frag_clen,
                                                           d_frag_rel, d_out_off, scratch, d_out, L.n_frags, L.n);
+    prof_mark(ctx, B2C_PROF_PACK);
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
     return B2C_OK;

@@ -217,6 +217,7 @@ int launch_decompress(b2c_ctx* ctx, const Layout& in, const uint8_t* d_in, const
     if (in.n == 0) return B2C_OK;
     static const uint32_t class_smem[3] = {2048, 8192, 0};
     static const uint32_t class_warps[3] = {8, 4, 8};
+    prof_mark(ctx, B2C_PROF_DECOMPRESS);
     for (int c = 0; c < 3; c++) {
         if (!out.n_dclass[c]) continue;
         DecompressParams P;
@@ -237,6 +238,7 @@ int launch_decompress(b2c_ctx* ctx, const Layout& in, const uint8_t* d_in, const
         ctx->launches++;
         B2C_CUDA(ctx, cudaGetLastError());
     }
+    prof_mark(ctx, B2C_PROF_DECOMPRESS);
     return B2C_OK;
 }
 

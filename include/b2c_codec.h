@@ -88,6 +88,19 @@ void b2c_event_destroy(b2c_event* ev);
 int b2c_event_record(b2c_ctx* ctx, b2c_event* ev);                /* on the ctx stream */
 int b2c_event_elapsed_ms(b2c_event* start, b2c_event* stop, float* ms); /* syncs on stop */
 
+/* Kernel timing for bench.py's roofline line (instrumentation; no counterpart in
+ * the reference).  While enabled, the launchers bracket their dominant kernels
+ * with CUDA events on the ctx stream; b2c_prof_total_ms waits for them and
+ * returns the summed duration and the number of timed launches since the last
+ * enable/reset. */
+#define B2C_PROF_CRC32C 0      /* crc32c_chunks_kernel */
+#define B2C_PROF_COMPRESS 1    /* snappy_compress_fragments_kernel (all size classes) */
+#define B2C_PROF_DECOMPRESS 2  /* snappy_decompress_kernel (all size classes) */
+#define B2C_PROF_PACK 3        /* compress post-pass: sizes + scan + gather */
+#define B2C_PROF_COUNT 4
+int b2c_prof_enable(b2c_ctx* ctx, int on);
+int b2c_prof_total_ms(b2c_ctx* ctx, int which, float* total_ms, uint32_t* launches);
+
 /* ---- pure host helpers ------------------------------------------------- */
 
 /* snappy::MaxCompressedLength — src/butil/third_party/snappy/snappy.cc:55-77 */
