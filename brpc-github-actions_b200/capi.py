@@ -63,6 +63,7 @@ SYMBOLS = {
     "b2c_layout_arena_bytes": (C.c_uint64, [_vp]),
     "b2c_layout_max_compressed_bytes": (C.c_uint64, [_vp]),
     "b2c_crc32c_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    "b2c_crc32c_noalloc_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     "b2c_snappy_compress_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint64, _vp]),
     "b2c_snappy_uncompressed_length_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     "b2c_snappy_decompress_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
@@ -304,6 +305,10 @@ class Codec:
     # ---- device-resident ops ---------------------------------------------
     def crc32c_dev(self, layout: Layout, d_data: DevMem, d_crc: DevMem, d_init: DevMem | None = None):
         self._check(self.lib.b2c_crc32c_dev(self.ctx, layout.h, d_data.ptr, d_init.ptr if d_init else None, d_crc.ptr))
+
+    def crc32c_noalloc_dev(self, layout: Layout, d_data: DevMem, d_crc: DevMem, d_init: DevMem | None = None):
+        self._check(self.lib.b2c_crc32c_noalloc_dev(self.ctx, layout.h, d_data.ptr, d_init.ptr if d_init else None,
+                                                    d_crc.ptr))
 
     def compress_dev(self, layout: Layout, d_in: DevMem, d_out: DevMem, d_out_off: DevMem):
         self._check(self.lib.b2c_snappy_compress_dev(self.ctx, layout.h, d_in.ptr, d_out.ptr, d_out.nbytes,

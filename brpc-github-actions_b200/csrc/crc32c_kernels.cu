@@ -20,6 +20,8 @@
 //
 // Register convention is the reference's: l = crc ^ 0xffffffff, one byte step is
 // l = table0[(l ^ b) & 0xff] ^ (l >> 8) (crc32c.cc:390-393), result l ^ 0xffffffff.
+#include <mutex>
+
 #include "b2c_internal.cuh"
 
 namespace b2c {
@@ -319,4 +321,86 @@ int launch_crc32c(b2c_ctx* ctx, const Layout& L, const uint8_t* d_data, const ui
     return B2C_OK;
 }
 
+// ---------------------------------------------------------------------------
+// Allocation-free variant (b2c_crc32c_noalloc_dev).
+//
+// The chunk kernel needs one 32-bit slot per 4 KiB chunk to park the partial CRCs
+// of multi-chunk messages until the combine kernel folds them.  launch_crc32c
+// takes those slots from a workspace that grows with cudaMalloc; callers that
+// cannot allocate on their call path (see include/b2c_codec.h) get the same slots
+// from this fixed array instead.  Inside host code `g_noalloc_rem` is only a
+// handle for the runtime, not an address a kernel could use, so the real device
+// address is looked up once per device and cached.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) uint32_t g_noalloc_rem[B2C_CRC32C_NOALLOC_MAX_CHUNKS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+uint32_t* g_noalloc_addr[kMaxDevices] = {};  // device address of g_noalloc_rem, per device
+}  // namespace
+
+// First use on a device: resolve the array's address with that device current.
+static int noalloc_scratch(b2c_ctx* ctx, uint32_t** out) {
+    const int dev = ctx->device;
+    if (dev < 0 || dev >= kMaxDevices) return set_err(ctx, B2C_E_ARG, "noalloc: device index out of range", cudaSuccess);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_addr[dev]) {
+        B2C_CUDA(ctx, cudaSetDevice(dev));
+        void* p = nullptr;
+        B2C_CUDA(ctx, cudaGetSymbolAddress(&p, g_noalloc_rem));
+        if (!p) return set_err(ctx, B2C_E_CUDA, "noalloc: cudaGetSymbolAddress returned null", cudaSuccess);
+        g_noalloc_addr[dev] = static_cast<uint32_t*>(p);
+    }
+    *out = g_noalloc_addr[dev];
+    return B2C_OK;
+}
+
 }  // namespace b2c
+
+extern "C" int b2c_crc32c_noalloc_dev(b2c_ctx* ctx, const b2c_layout* layout, const void* d_data,
+                                      const uint32_t* d_init, uint32_t* d_crc) {
+    using namespace b2c;
+    if (!ctx || !layout || !d_crc || (layout->payload && !d_data)) return B2C_E_ARG;
+    const Layout& L = *layout;
+    if (L.n_chunks > B2C_CRC32C_NOALLOC_MAX_CHUNKS)
+        return set_err(ctx, B2C_E_CAPACITY,
+                       "b2c_crc32c_noalloc_dev: layout has more than B2C_CRC32C_NOALLOC_MAX_CHUNKS (2^20) 4 KiB chunks; "
+                       "split the batch or use b2c_crc32c_dev",
+                       cudaSuccess);
+    B2C_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint32_t* d_rem = nullptr;
+    int rc = noalloc_scratch(ctx, &d_rem);
+    if (rc) return rc;
+    if (L.n == 0) return B2C_OK;
+    if (!ctx->crc_attr_done) {
+        B2C_CUDA(ctx, cudaFuncSetAttribute(crc32c_chunks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)sizeof(CrcSmem)));
+        ctx->crc_attr_done = true;
+    }
+    CrcParams P;
+    P.data = static_cast<const uint8_t*>(d_data);
+    P.off = L.d_off;
+    P.len = L.d_len;
+    P.init = d_init;
+    P.chunk_msg = L.all_single_chunk_uniform ? nullptr : L.d_chunk_msg;
+    P.chunk_first = L.all_single_chunk_uniform ? nullptr : L.d_chunk_first;
+    P.tabA = ctx->d_crc_tabA;
+    P.small = ctx->d_crc_small;
+    P.rem = d_rem;  // slot c is written by chunk c before the combine kernel reads it
+    P.crc = d_crc;
+    P.n_chunks = L.n_chunks;
+    uint32_t grid = (L.n_chunks + 255) / 256;
+    if (grid > (uint32_t)ctx->num_sms) grid = ctx->num_sms;
+    crc32c_chunks_kernel<<<grid, 1024, sizeof(CrcSmem), ctx->stream>>>(P);
+    ctx->launches++;
+    B2C_CUDA(ctx, cudaGetLastError());
+    if (L.n_multi) {
+        const uint32_t blocks = (L.n_multi * 32 + 255) / 256;
+        crc32c_combine_kernel<<<blocks, 256, 0, ctx->stream>>>(L.d_multi_list, L.n_multi, L.d_chunk_first, L.d_len,
+                                                                d_rem, d_crc);
+        ctx->launches++;
+        B2C_CUDA(ctx, cudaGetLastError());
+    }
+    return B2C_OK;
+}

@@ -142,6 +142,35 @@ uint64_t b2c_layout_max_compressed_bytes(const b2c_layout* layout);
 int b2c_crc32c_dev(b2c_ctx* ctx, const b2c_layout* layout, const void* d_data,
                    const uint32_t* d_init, uint32_t* d_crc);
 
+/* Same result as b2c_crc32c_dev, for callers that must not allocate device memory
+ * at call time.  No counterpart in the reference (its CRC needs no scratch at all).
+ *
+ * Who needs it: an RPC worker that checksums bodies on the request path cannot
+ * afford a cudaMalloc there — the allocator call serialises the whole device and
+ * every other in-flight batch waits behind it — and a service that handed the rest
+ * of HBM to another engine at start-up has nothing left to allocate from, so a
+ * late workspace growth inside b2c_crc32c_dev would simply fail.  b2c_crc32c_dev
+ * keeps the per-chunk partial CRCs of messages longer than 4 KiB in a workspace it
+ * grows on demand; this variant keeps them in a fixed array that is part of the
+ * library image (4 bytes per 4 KiB chunk, B2C_CRC32C_NOALLOC_MAX_CHUNKS entries =
+ * 4 MiB, resident on every GPU that loads the library until the process exits).
+ *
+ * Limits and rules:
+ *   - layouts with more than B2C_CRC32C_NOALLOC_MAX_CHUNKS chunks (sum over
+ *     messages of max(1, ceil(len/4096))) are refused with B2C_E_CAPACITY;
+ *   - the first call on each device looks up the array's device address; make
+ *     that first call before starting any stream capture on that device;
+ *   - all calls on a device share the one array: two calls whose kernels can
+ *     overlap on the GPU (different contexts or streams) race — serialise them;
+ *   - the array keeps whatever the previous call left; every slot a call reads
+ *     is written earlier in that same call, so nothing has to be cleared;
+ *   - it calls neither cudaMalloc nor cudaFree nor any other allocating routine;
+ *     the layout (created earlier, at set-up time) and the caller's input and
+ *     output buffers are the only device memory it touches besides the array. */
+#define B2C_CRC32C_NOALLOC_MAX_CHUNKS (1u << 20)
+int b2c_crc32c_noalloc_dev(b2c_ctx* ctx, const b2c_layout* layout, const void* d_data,
+                           const uint32_t* d_init, uint32_t* d_crc);
+
 /* For every message: the exact byte stream butil::snappy::Compress(Source*,Sink*)
  * produces (snappy.cc:875-954; what brpc::policy::SnappyCompress(const IOBuf&,
  * IOBuf*) appends, src/brpc/policy/snappy_compress.cpp:51-55).  Streams are
