@@ -2,9 +2,22 @@
 // entry points declared in include/b2c_codec.h.  Everything below the C ABI is
 // CUDA for sm_100a; there is deliberately no CPU codec here: without a usable
 // device b2c_ctx_create fails with B2C_E_NODEVICE.
+//
+// The *_batch (host memory) entry points run a slab pipeline: the batch is cut
+// into slabs of ~32 MiB; host threads gather a slab's IOBuf blocks into pinned
+// staging while the previous slab is on the PCIe bus / in the kernels and the one
+// before that is being copied out, over kPipeLanes streams with private
+// workspaces (replaces the per-fragment gather memcpy of snappy.cc:901-921 and
+// the sink copies of src/butil/iobuf.cpp:2066-2093).
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <new>
 #include <thread>
 
@@ -23,11 +36,11 @@ int set_err(b2c_ctx* ctx, int code, const char* what, cudaError_t e) {
     return code;
 }
 
-int ws_reserve(b2c_ctx* ctx, DevBuf& b, size_t bytes) {
+int ws_reserve(b2c_ctx* ctx, Lane& lane, DevBuf& b, size_t bytes) {
     if (bytes <= b.cap) return B2C_OK;
     if (b.p) {
         // the old buffer may still be in use by queued work
-        B2C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        B2C_CUDA(ctx, cudaStreamSynchronize(lane.stream));
         B2C_CUDA(ctx, cudaFree(b.p));
         b.p = nullptr;
         b.cap = 0;
@@ -42,26 +55,26 @@ int ws_reserve(b2c_ctx* ctx, DevBuf& b, size_t bytes) {
     return B2C_OK;
 }
 
-static int pin_reserve(b2c_ctx* ctx, void** p, size_t* cap, size_t bytes) {
-    if (bytes <= *cap) return B2C_OK;
-    if (*p) {
-        B2C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        B2C_CUDA(ctx, cudaFreeHost(*p));
-        *p = nullptr;
-        *cap = 0;
+static int pin_reserve(b2c_ctx* ctx, Lane& lane, PinBuf& b, size_t bytes) {
+    if (bytes <= b.cap) return B2C_OK;
+    if (b.p) {
+        B2C_CUDA(ctx, cudaStreamSynchronize(lane.stream));
+        B2C_CUDA(ctx, cudaFreeHost(b.p));
+        b.p = nullptr;
+        b.cap = 0;
     }
     size_t want = bytes + bytes / 8 + 4096;
-    cudaError_t e = cudaHostAlloc(p, want, cudaHostAllocDefault);
+    cudaError_t e = cudaHostAlloc(&b.p, want, cudaHostAllocDefault);
     if (e != cudaSuccess) {
-        *p = nullptr;
+        b.p = nullptr;
         return set_err(ctx, B2C_E_NOMEM, "cudaHostAlloc(staging)", e);
     }
-    *cap = want;
+    b.cap = want;
     return B2C_OK;
 }
 
-void prof_mark(b2c_ctx* ctx, int which) {
-    if (!ctx->prof_on) return;
+void prof_mark(b2c_ctx* ctx, Lane& lane, int which) {
+    if (!ctx->prof_on || &lane != &ctx->main) return;
     auto& v = ctx->prof_ev[which];
     uint32_t& used = ctx->prof_used[which];
     if (used >= 1024) return;
@@ -70,40 +83,299 @@ void prof_mark(b2c_ctx* ctx, int which) {
         if (cudaEventCreate(&e) != cudaSuccess) return;
         v.push_back(e);
     }
-    cudaEventRecord(v[used++], ctx->stream);
-}
-
-template <typename T>
-static int upload(b2c_ctx* ctx, T** d, const std::vector<T>& h) {
-    *d = nullptr;
-    size_t bytes = std::max<size_t>(h.size(), 1) * sizeof(T);
-    B2C_CUDA(ctx, cudaMalloc(d, bytes));
-    if (!h.empty()) B2C_CUDA(ctx, cudaMemcpyAsync(*d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
-    return B2C_OK;
-}
-
-// Run fn(t, T) on T host threads (t = 0..T-1).
-template <typename F>
-static void parallel_for(unsigned T, F fn) {
-    if (T <= 1) {
-        fn(0u, 1u);
-        return;
-    }
-    std::vector<std::thread> th;
-    th.reserve(T - 1);
-    for (unsigned t = 1; t < T; t++) th.emplace_back([=] { fn(t, T); });
-    fn(0u, T);
-    for (auto& x : th) x.join();
-}
-
-static unsigned host_threads(uint64_t bytes) {
-    unsigned hw = std::thread::hardware_concurrency();
-    if (hw == 0) hw = 4;
-    unsigned want = (unsigned)std::min<uint64_t>(16, bytes / (4u << 20) + 1);
-    return std::max(1u, std::min(hw, want));
+    cudaEventRecord(v[used++], lane.stream);
 }
 
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+static inline size_t max_clen(size_t n) { return 32 + n + n / 6; }
+
+// ---------------------------------------------------------------------------
+// persistent host thread pool (gather / copy-out memcpy, preamble parsing)
+// ---------------------------------------------------------------------------
+class HostPool {
+public:
+    explicit HostPool(unsigned n) : n_(std::max(1u, n)) {
+        for (unsigned t = 1; t < n_; t++) workers_.emplace_back([this, t] { loop(t); });
+    }
+    ~HostPool() {
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            stop_ = true;
+            gen_++;
+        }
+        cv_.notify_all();
+        for (auto& w : workers_) w.join();
+    }
+    unsigned size() const { return n_; }
+    // run fn(t, T) for t in [0, T) with T = min(size, want)
+    void run(unsigned want, const std::function<void(unsigned, unsigned)>& fn) {
+        unsigned T = std::max(1u, std::min(n_, want));
+        if (T == 1) {
+            fn(0, 1);
+            return;
+        }
+        std::lock_guard<std::mutex> serial(run_mu_);  // one parallel section at a time, process-wide
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            fn_ = &fn;
+            active_ = T;
+            pending_ = T - 1;
+            gen_++;
+        }
+        cv_.notify_all();
+        fn(0, T);
+        std::unique_lock<std::mutex> g(mu_);
+        done_cv_.wait(g, [this] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+
+private:
+    void loop(unsigned t) {
+        uint64_t seen = 0;
+        for (;;) {
+            const std::function<void(unsigned, unsigned)>* fn = nullptr;
+            unsigned T = 0;
+            {
+                std::unique_lock<std::mutex> g(mu_);
+                cv_.wait(g, [&] { return gen_ != seen; });
+                seen = gen_;
+                if (stop_) return;
+                fn = fn_;
+                T = active_;
+            }
+            if (fn && t < T) {
+                (*fn)(t, T);
+                std::lock_guard<std::mutex> g(mu_);
+                if (--pending_ == 0) done_cv_.notify_one();
+            }
+        }
+    }
+    unsigned n_;
+    std::vector<std::thread> workers_;
+    std::mutex mu_, run_mu_;
+    std::condition_variable cv_, done_cv_;
+    const std::function<void(unsigned, unsigned)>* fn_ = nullptr;
+    unsigned active_ = 0, pending_ = 0;
+    uint64_t gen_ = 0;
+    bool stop_ = false;
+};
+
+static std::mutex g_pool_mu;
+static HostPool* g_pool = nullptr;  // one per process, sized on first use
+
+static HostPool& pool(b2c_ctx* ctx) {
+    std::lock_guard<std::mutex> g(g_pool_mu);
+    if (!g_pool) {
+        unsigned n = ctx->host_threads;
+        if (!n) {
+            n = std::thread::hardware_concurrency();
+            if (!n) n = 4;
+            n = std::min(n, 16u);
+        }
+        g_pool = new HostPool(n);
+    }
+    return *g_pool;
+}
+
+static unsigned threads_for(uint64_t bytes) { return (unsigned)std::min<uint64_t>(64, bytes / (1u << 20) + 1); }
+
+// ---------------------------------------------------------------------------
+// LayoutPlan
+// ---------------------------------------------------------------------------
+static inline int frag_class(uint32_t fl) { return fl <= 1024 ? 0 : fl <= 4096 ? 1 : 2; }
+static inline int slot_class(uint32_t cap) { return cap <= 1024 ? 0 : cap <= 8192 ? 1 : 2; }
+
+namespace {
+struct PlanStats {
+    uint64_t payload = 0, arena_end = 0, max_comp = 0, slot_sum = 0, F = 0, C = 0;
+    uint32_t max_len = 0, n_multi = 0, n_class[3] = {0, 0, 0}, n_dclass[3] = {0, 0, 0};
+};
+void plan_range(const uint64_t* off, const uint32_t* len, uint32_t lo, uint32_t hi, PlanStats& st) {
+    const uint64_t full_slot = align_up(max_clen(kFragBytes), 16);
+    for (uint32_t m = lo; m < hi; m++) {
+        const uint32_t l = len[m];
+        st.payload += l;
+        st.arena_end = std::max<uint64_t>(st.arena_end, off[m] + l);
+        st.max_comp += max_clen(l) + 5;
+        st.max_len = std::max(st.max_len, l);
+        const uint32_t nf = l ? (uint32_t)(((uint64_t)l + kFragBytes - 1) / kFragBytes) : 1u;
+        const uint32_t last = l - (nf - 1) * kFragBytes;
+        st.F += nf;
+        st.n_class[2] += nf - 1;
+        st.n_class[frag_class(last)] += 1;
+        st.slot_sum += (uint64_t)(nf - 1) * full_slot + align_up(max_clen(last), 16);
+        const uint32_t nc = l ? (uint32_t)(((uint64_t)l + kCrcChunk - 1) / kCrcChunk) : 1u;
+        st.C += nc;
+        if (nc > 1) st.n_multi++;
+        st.n_dclass[slot_class(l)]++;
+    }
+}
+}  // namespace
+
+void LayoutPlan::plan(uint32_t n_, const uint64_t* off_, const uint32_t* len_, b2c_ctx* par) {
+    n = n_;
+    off = off_;
+    len = len_;
+    v = LayoutView();
+    v.n = n;
+    PlanStats tot;
+    if (par && n >= (1u << 14)) {
+        PlanStats part[64];
+        unsigned used = 1;
+        pool(par).run(threads_for((uint64_t)n * 256), [&](unsigned t, unsigned T) {
+            if (t == 0) used = T;
+            plan_range(off, len, (uint32_t)((uint64_t)n * t / T), (uint32_t)((uint64_t)n * (t + 1) / T), part[t]);
+        });
+        for (unsigned t = 0; t < used; t++) {
+            const PlanStats& p = part[t];
+            tot.payload += p.payload;
+            tot.arena_end = std::max(tot.arena_end, p.arena_end);
+            tot.max_comp += p.max_comp;
+            tot.slot_sum += p.slot_sum;
+            tot.F += p.F;
+            tot.C += p.C;
+            tot.max_len = std::max(tot.max_len, p.max_len);
+            tot.n_multi += p.n_multi;
+            for (int c = 0; c < 3; c++) {
+                tot.n_class[c] += p.n_class[c];
+                tot.n_dclass[c] += p.n_dclass[c];
+            }
+        }
+    } else {
+        plan_range(off, len, 0, n, tot);
+    }
+    v.payload = tot.payload;
+    v.arena_end = tot.arena_end;
+    v.max_comp = tot.max_comp;
+    v.n_multi = tot.n_multi;
+    for (int c = 0; c < 3; c++) {
+        v.n_class[c] = tot.n_class[c];
+        v.n_dclass[c] = tot.n_dclass[c];
+    }
+    const uint64_t slot_sum = tot.slot_sum, F = tot.F, C = tot.C;
+    const uint32_t max_len = tot.max_len;
+    v.n_frags = (uint32_t)F;
+    v.n_chunks = (uint32_t)C;
+    has_frag_arrays = F != n;
+    has_chunk_arrays = C != n;
+    const uint64_t stride = align_up(max_clen(std::min(max_len, kFragBytes)), 16);
+    const bool uniform = F * stride <= 2 * slot_sum + (1u << 20);
+    has_slot_array = !uniform;
+    v.slot_stride = uniform ? stride : 0;
+    v.frag_scratch_bytes = uniform ? F * stride : slot_sum;
+    has_class_lists = (v.n_class[0] != 0) + (v.n_class[1] != 0) + (v.n_class[2] != 0) > 1;
+    has_dclass_lists = (v.n_dclass[0] != 0) + (v.n_dclass[1] != 0) + (v.n_dclass[2] != 0) > 1;
+    size_t o = 0;
+    auto take = [&](size_t bytes) {
+        size_t at = o;
+        o = align_up(o + bytes, 16);
+        return at;
+    };
+    o_off = take((size_t)n * 8);
+    o_slot = has_slot_array ? take(F * 8) : 0;
+    o_len = take((size_t)n * 4);
+    if (has_frag_arrays) {
+        o_frag_msg = take(F * 4);
+        o_frag_first = take(((size_t)n + 1) * 4);
+    }
+    if (has_class_lists)
+        for (int c = 0; c < 3; c++) o_class[c] = take((size_t)v.n_class[c] * 4);
+    if (has_dclass_lists)
+        for (int c = 0; c < 3; c++) o_dclass[c] = take((size_t)v.n_dclass[c] * 4);
+    if (has_chunk_arrays) {
+        o_chunk_msg = take(C * 4);
+        o_chunk_first = take(((size_t)n + 1) * 4);
+        o_multi = take((size_t)v.n_multi * 4);
+    }
+    blob_bytes = std::max<size_t>(o, 16);
+}
+
+void LayoutPlan::fill(uint8_t* blob) const {
+    if (n) {
+        memcpy(blob + o_off, off, (size_t)n * 8);
+        memcpy(blob + o_len, len, (size_t)n * 4);
+    }
+    if (!(has_frag_arrays || has_slot_array || has_class_lists || has_dclass_lists || has_chunk_arrays)) return;
+    uint64_t* slot = has_slot_array ? reinterpret_cast<uint64_t*>(blob + o_slot) : nullptr;
+    uint32_t* frag_msg = has_frag_arrays ? reinterpret_cast<uint32_t*>(blob + o_frag_msg) : nullptr;
+    uint32_t* frag_first = has_frag_arrays ? reinterpret_cast<uint32_t*>(blob + o_frag_first) : nullptr;
+    uint32_t* cls[3] = {nullptr, nullptr, nullptr};
+    uint32_t* dcls[3] = {nullptr, nullptr, nullptr};
+    for (int c = 0; c < 3; c++) {
+        if (has_class_lists) cls[c] = reinterpret_cast<uint32_t*>(blob + o_class[c]);
+        if (has_dclass_lists) dcls[c] = reinterpret_cast<uint32_t*>(blob + o_dclass[c]);
+    }
+    uint32_t* chunk_msg = has_chunk_arrays ? reinterpret_cast<uint32_t*>(blob + o_chunk_msg) : nullptr;
+    uint32_t* chunk_first = has_chunk_arrays ? reinterpret_cast<uint32_t*>(blob + o_chunk_first) : nullptr;
+    uint32_t* multi = has_chunk_arrays ? reinterpret_cast<uint32_t*>(blob + o_multi) : nullptr;
+    const uint64_t full_slot = align_up(max_clen(kFragBytes), 16);
+    uint64_t slot_at = 0;
+    uint32_t f = 0, c = 0, nm = 0, ncls[3] = {0, 0, 0}, ndcls[3] = {0, 0, 0};
+    for (uint32_t m = 0; m < n; m++) {
+        const uint32_t l = len[m];
+        const uint32_t nf = l ? (uint32_t)(((uint64_t)l + kFragBytes - 1) / kFragBytes) : 1u;
+        if (frag_first) frag_first[m] = f;
+        for (uint32_t k = 0; k < nf; k++, f++) {
+            const uint32_t fl = k + 1 < nf ? kFragBytes : l - (nf - 1) * kFragBytes;
+            if (frag_msg) frag_msg[f] = m;
+            if (slot) {
+                slot[f] = slot_at;
+                slot_at += k + 1 < nf ? full_slot : align_up(max_clen(fl), 16);
+            }
+            if (has_class_lists) {
+                int q = frag_class(fl);
+                cls[q][ncls[q]++] = f;
+            }
+        }
+        if (has_dclass_lists) {
+            int q = slot_class(l);
+            dcls[q][ndcls[q]++] = m;
+        }
+        if (chunk_msg) {
+            const uint32_t nc = l ? (uint32_t)(((uint64_t)l + kCrcChunk - 1) / kCrcChunk) : 1u;
+            chunk_first[m] = c;
+            for (uint32_t k = 0; k < nc; k++) chunk_msg[c++] = m;
+            if (nc > 1) multi[nm++] = m;
+        }
+    }
+    if (frag_first) frag_first[n] = f;
+    if (chunk_first) chunk_first[n] = c;
+}
+
+void LayoutPlan::bind(const uint8_t* d, LayoutView* out) const {
+    *out = v;
+    out->d_off = reinterpret_cast<const uint64_t*>(d + o_off);
+    out->d_len = reinterpret_cast<const uint32_t*>(d + o_len);
+    out->d_frag_slot = has_slot_array ? reinterpret_cast<const uint64_t*>(d + o_slot) : nullptr;
+    out->d_frag_msg = has_frag_arrays ? reinterpret_cast<const uint32_t*>(d + o_frag_msg) : nullptr;
+    out->d_frag_first = has_frag_arrays ? reinterpret_cast<const uint32_t*>(d + o_frag_first) : nullptr;
+    for (int c = 0; c < 3; c++) {
+        out->d_class_list[c] = has_class_lists ? reinterpret_cast<const uint32_t*>(d + o_class[c]) : nullptr;
+        out->d_dclass_list[c] = has_dclass_lists ? reinterpret_cast<const uint32_t*>(d + o_dclass[c]) : nullptr;
+    }
+    out->d_chunk_msg = has_chunk_arrays ? reinterpret_cast<const uint32_t*>(d + o_chunk_msg) : nullptr;
+    out->d_chunk_first = has_chunk_arrays ? reinterpret_cast<const uint32_t*>(d + o_chunk_first) : nullptr;
+    out->d_multi_list = has_chunk_arrays ? reinterpret_cast<const uint32_t*>(d + o_multi) : nullptr;
+}
+
+static int lane_create(b2c_ctx* ctx, Lane& l) {
+    B2C_CUDA(ctx, cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
+    B2C_CUDA(ctx, cudaEventCreateWithFlags(&l.ev_meta, cudaEventDisableTiming));
+    B2C_CUDA(ctx, cudaEventCreateWithFlags(&l.ev_done, cudaEventDisableTiming));
+    return B2C_OK;
+}
+
+static void lane_destroy(Lane& l) {
+    if (l.stream) cudaStreamSynchronize(l.stream);
+    for (DevBuf* b : {&l.ws_frag, &l.ws_misc, &l.d_in, &l.d_out})
+        if (b->p) cudaFree(b->p);
+    for (PinBuf* b : {&l.h_in, &l.h_out})
+        if (b->p) cudaFreeHost(b->p);
+    if (l.ev_meta) cudaEventDestroy(l.ev_meta);
+    if (l.ev_done) cudaEventDestroy(l.ev_done);
+    if (l.stream) cudaStreamDestroy(l.stream);
+    l = Lane();
+}
 
 }  // namespace b2c
 
@@ -123,15 +395,24 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     b2c_ctx* ctx = new (std::nothrow) b2c_ctx();
     if (!ctx) return B2C_E_NOMEM;
     ctx->device = device;
+    if (const char* s = getenv("B2C_SLAB_MB")) ctx->slab_bytes = std::max<size_t>(1, (size_t)atol(s)) << 20;
+    if (const char* s = getenv("B2C_HOST_THREADS")) ctx->host_threads = (unsigned)std::max(1L, atol(s));
+    if (const char* s = getenv("B2C_TRACE")) ctx->trace = atoi(s) != 0;
+    if (const char* s = getenv("B2C_SMALL_KERNELS")) ctx->small_kernels = atoi(s) != 0;
+    if (const char* s = getenv("B2C_SMALL_LPW_C")) ctx->small_lpw_compress = atoi(s);
+    if (const char* s = getenv("B2C_SMALL_LPW_D")) ctx->small_lpw_decompress = atoi(s);
     int rc = B2C_OK;
     do {
         if ((e = cudaSetDevice(device)) != cudaSuccess) { rc = set_err(ctx, B2C_E_CUDA, "cudaSetDevice", e); break; }
         cudaDeviceProp prop;
         if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) { rc = set_err(ctx, B2C_E_CUDA, "cudaGetDeviceProperties", e); break; }
         ctx->num_sms = prop.multiProcessorCount;
-        if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = set_err(ctx, B2C_E_CUDA, "cudaStreamCreate", e); break; }
-        if ((e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = set_err(ctx, B2C_E_CUDA, "cudaStreamCreate", e); break; }
-        rc = crc_tables_init(ctx);
+        if ((rc = lane_create(ctx, ctx->main))) break;
+        for (auto& l : ctx->pipe)
+            if ((rc = lane_create(ctx, l))) break;
+        if (rc) break;
+        if ((rc = crc_tables_init(ctx))) break;
+        rc = small_kernels_configure(ctx);
     } while (0);
     if (rc != B2C_OK) {
         fprintf(stderr, "b2c_ctx_create failed: %s\n", ctx->err.c_str());
@@ -145,28 +426,23 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
 void b2c_ctx_destroy(b2c_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    for (DevBuf* b : {&ctx->ws_frag, &ctx->ws_misc, &ctx->ws_io_in, &ctx->ws_io_out})
-        if (b->p) cudaFree(b->p);
-    if (ctx->h_pin_in) cudaFreeHost(ctx->h_pin_in);
-    if (ctx->h_pin_out) cudaFreeHost(ctx->h_pin_out);
+    lane_destroy(ctx->main);
+    for (auto& l : ctx->pipe) lane_destroy(l);
     if (ctx->d_crc_tabA) cudaFree(ctx->d_crc_tabA);
     if (ctx->d_crc_small) cudaFree(ctx->d_crc_small);
     for (auto& v : ctx->prof_ev)
         for (cudaEvent_t e : v) cudaEventDestroy(e);
-    if (ctx->stream) cudaStreamDestroy(ctx->stream);
-    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
 }
 
 const char* b2c_last_error(const b2c_ctx* ctx) { return ctx ? ctx->err.c_str() : "no context"; }
 int b2c_ctx_device(const b2c_ctx* ctx) { return ctx ? ctx->device : -1; }
-void* b2c_ctx_stream(b2c_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+void* b2c_ctx_stream(b2c_ctx* ctx) { return ctx ? (void*)ctx->main.stream : nullptr; }
 uint64_t b2c_ctx_launch_count(const b2c_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
 int b2c_ctx_sync(b2c_ctx* ctx) {
     if (!ctx) return B2C_E_ARG;
-    B2C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    B2C_CUDA(ctx, cudaStreamSynchronize(ctx->main.stream));
     return B2C_OK;
 }
 
@@ -195,17 +471,17 @@ int b2c_host_free_pinned(b2c_ctx* ctx, void* h_ptr) {
 }
 int b2c_memcpy_h2d(b2c_ctx* ctx, void* d_dst, const void* h_src, size_t bytes) {
     if (!ctx) return B2C_E_ARG;
-    B2C_CUDA(ctx, cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    B2C_CUDA(ctx, cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, ctx->main.stream));
     return B2C_OK;
 }
 int b2c_memcpy_d2h(b2c_ctx* ctx, void* h_dst, const void* d_src, size_t bytes) {
     if (!ctx) return B2C_E_ARG;
-    B2C_CUDA(ctx, cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    B2C_CUDA(ctx, cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, ctx->main.stream));
     return B2C_OK;
 }
 int b2c_memset_dev(b2c_ctx* ctx, void* d_dst, int value, size_t bytes) {
     if (!ctx) return B2C_E_ARG;
-    B2C_CUDA(ctx, cudaMemsetAsync(d_dst, value, bytes, ctx->stream));
+    B2C_CUDA(ctx, cudaMemsetAsync(d_dst, value, bytes, ctx->main.stream));
     return B2C_OK;
 }
 int b2c_event_create(b2c_ctx* ctx, b2c_event** ev) {
@@ -227,7 +503,7 @@ void b2c_event_destroy(b2c_event* ev) {
 }
 int b2c_event_record(b2c_ctx* ctx, b2c_event* ev) {
     if (!ctx || !ev) return B2C_E_ARG;
-    B2C_CUDA(ctx, cudaEventRecord(ev->ev, ctx->stream));
+    B2C_CUDA(ctx, cudaEventRecord(ev->ev, ctx->main.stream));
     return B2C_OK;
 }
 int b2c_event_elapsed_ms(b2c_event* start, b2c_event* stop, float* ms) {
@@ -239,7 +515,7 @@ int b2c_event_elapsed_ms(b2c_event* start, b2c_event* stop, float* ms) {
 
 int b2c_prof_enable(b2c_ctx* ctx, int on) {
     if (!ctx) return B2C_E_ARG;
-    B2C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    B2C_CUDA(ctx, cudaStreamSynchronize(ctx->main.stream));
     ctx->prof_on = on != 0;
     for (auto& u : ctx->prof_used) u = 0;
     return B2C_OK;
@@ -247,7 +523,7 @@ int b2c_prof_enable(b2c_ctx* ctx, int on) {
 
 int b2c_prof_total_ms(b2c_ctx* ctx, int which, float* total_ms, uint32_t* launches) {
     if (!ctx || which < 0 || which >= B2C_PROF_COUNT || !total_ms) return B2C_E_ARG;
-    B2C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    B2C_CUDA(ctx, cudaStreamSynchronize(ctx->main.stream));
     float sum = 0;
     uint32_t pairs = ctx->prof_used[which] / 2;
     for (uint32_t i = 0; i < pairs; i++) {
@@ -311,70 +587,22 @@ int b2c_layout_create(b2c_ctx* ctx, uint32_t n, const uint64_t* off, const uint3
     b2c_layout* L = new (std::nothrow) b2c_layout();
     if (!L) return B2C_E_NOMEM;
     L->ctx = ctx;
-    L->n = n;
-    L->h_off.assign(off, off + n);
-    L->h_len.assign(len, len + n);
-    std::vector<uint32_t> frag_msg, frag_first(n + 1), chunk_msg, chunk_first(n + 1), multi;
-    std::vector<uint64_t> frag_slot;
-    std::vector<uint32_t> cls[3], dcls[3];
-    uint64_t slot = 0;
-    bool single = true;
-    for (uint32_t m = 0; m < n; m++) {
-        const uint32_t l = len[m];
-        L->payload += l;
-        L->arena_end = std::max<uint64_t>(L->arena_end, off[m] + l);
-        L->max_comp += b2c_snappy_max_compressed_length(l) + 5;
-        frag_first[m] = (uint32_t)frag_msg.size();
-        for (uint64_t pos = 0; pos < l; pos += kFragBytes) {
-            const uint32_t fl = (uint32_t)std::min<uint64_t>(kFragBytes, l - pos);
-            const uint32_t f = (uint32_t)frag_msg.size();
-            frag_msg.push_back(m);
-            frag_slot.push_back(slot);
-            slot += align_up(b2c_snappy_max_compressed_length(fl), 16);
-            cls[fl <= 1024 ? 0 : fl <= 4096 ? 1 : 2].push_back(f);
-        }
-        chunk_first[m] = (uint32_t)chunk_msg.size();
-        const uint32_t nc = std::max<uint32_t>(1, (uint32_t)(((uint64_t)l + kCrcChunk - 1) / kCrcChunk));
-        for (uint32_t k = 0; k < nc; k++) chunk_msg.push_back(m);
-        if (nc > 1) {
-            multi.push_back(m);
-            single = false;
-        }
-        dcls[l <= 2048 ? 0 : l <= 8192 ? 1 : 2].push_back(m);
+    LayoutPlan plan;
+    plan.plan(n, off, len);
+    std::vector<uint8_t> blob(plan.blob_bytes);
+    plan.fill(blob.data());
+    cudaError_t e = cudaMalloc(&L->d_blob, plan.blob_bytes);
+    if (e != cudaSuccess) {
+        delete L;
+        return set_err(ctx, B2C_E_NOMEM, "cudaMalloc(layout)", e);
     }
-    frag_first[n] = (uint32_t)frag_msg.size();
-    chunk_first[n] = (uint32_t)chunk_msg.size();
-    L->n_frags = (uint32_t)frag_msg.size();
-    L->frag_scratch_bytes = slot;
-    L->n_chunks = (uint32_t)chunk_msg.size();
-    L->n_multi = (uint32_t)multi.size();
-    L->all_single_chunk_uniform = single;
-    int rc = B2C_OK;
-    do {
-        if ((rc = upload(ctx, &L->d_off, L->h_off))) break;
-        if ((rc = upload(ctx, &L->d_len, L->h_len))) break;
-        if ((rc = upload(ctx, &L->d_frag_msg, frag_msg))) break;
-        if ((rc = upload(ctx, &L->d_frag_first, frag_first))) break;
-        if ((rc = upload(ctx, &L->d_frag_slot, frag_slot))) break;
-        if ((rc = upload(ctx, &L->d_chunk_msg, chunk_msg))) break;
-        if ((rc = upload(ctx, &L->d_chunk_first, chunk_first))) break;
-        if ((rc = upload(ctx, &L->d_multi_list, multi))) break;
-        for (int c = 0; c < 3 && rc == B2C_OK; c++) {
-            L->n_class[c] = (uint32_t)cls[c].size();
-            L->n_dclass[c] = (uint32_t)dcls[c].size();
-            if ((rc = upload(ctx, &L->d_class_list[c], cls[c]))) break;
-            if ((rc = upload(ctx, &L->d_dclass_list[c], dcls[c]))) break;
-        }
-    } while (0);
-    if (rc == B2C_OK) {
-        // host vectors above are pageable: make sure the staged copies are done before they die
-        cudaError_t e = cudaStreamSynchronize(ctx->stream);
-        if (e != cudaSuccess) rc = set_err(ctx, B2C_E_CUDA, "layout upload", e);
+    e = cudaMemcpy(L->d_blob, blob.data(), plan.blob_bytes, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        cudaFree(L->d_blob);
+        delete L;
+        return set_err(ctx, B2C_E_CUDA, "layout upload", e);
     }
-    if (rc != B2C_OK) {
-        b2c_layout_destroy(L);
-        return rc;
-    }
+    plan.bind(static_cast<const uint8_t*>(L->d_blob), &L->v);
     *out = L;
     return B2C_OK;
 }
@@ -383,108 +611,165 @@ void b2c_layout_destroy(b2c_layout* L) {
     if (!L) return;
     if (L->ctx) {
         cudaSetDevice(L->ctx->device);
-        cudaStreamSynchronize(L->ctx->stream);
+        cudaStreamSynchronize(L->ctx->main.stream);
     }
-    void* ptrs[] = {L->d_off, L->d_len, L->d_frag_msg, L->d_frag_first, L->d_frag_slot, L->d_chunk_msg,
-                    L->d_chunk_first, L->d_multi_list, L->d_class_list[0], L->d_class_list[1], L->d_class_list[2],
-                    L->d_dclass_list[0], L->d_dclass_list[1], L->d_dclass_list[2]};
-    for (void* p : ptrs)
-        if (p) cudaFree(p);
+    if (L->d_blob) cudaFree(L->d_blob);
     delete L;
 }
 
-uint32_t b2c_layout_count(const b2c_layout* L) { return L ? L->n : 0; }
-uint64_t b2c_layout_payload_bytes(const b2c_layout* L) { return L ? L->payload : 0; }
-uint64_t b2c_layout_arena_bytes(const b2c_layout* L) { return L ? L->arena_end : 0; }
-uint64_t b2c_layout_max_compressed_bytes(const b2c_layout* L) { return L ? L->max_comp : 0; }
+uint32_t b2c_layout_count(const b2c_layout* L) { return L ? L->v.n : 0; }
+uint64_t b2c_layout_payload_bytes(const b2c_layout* L) { return L ? L->v.payload : 0; }
+uint64_t b2c_layout_arena_bytes(const b2c_layout* L) { return L ? L->v.arena_end : 0; }
+uint64_t b2c_layout_max_compressed_bytes(const b2c_layout* L) { return L ? L->v.max_comp : 0; }
 
 // ---------------------------------------------------------------------------
 // device-resident entry points
 // ---------------------------------------------------------------------------
 int b2c_crc32c_dev(b2c_ctx* ctx, const b2c_layout* L, const void* d_data, const uint32_t* d_init, uint32_t* d_crc) {
-    if (!ctx || !L || !d_crc || (L->payload && !d_data)) return B2C_E_ARG;
+    if (!ctx || !L || !d_crc || (L->v.payload && !d_data)) return B2C_E_ARG;
     B2C_CUDA(ctx, cudaSetDevice(ctx->device));
-    return launch_crc32c(ctx, *L, static_cast<const uint8_t*>(d_data), d_init, d_crc);
+    return launch_crc32c(ctx, ctx->main, L->v, static_cast<const uint8_t*>(d_data), d_init, d_crc);
 }
 
 int b2c_snappy_compress_dev(b2c_ctx* ctx, const b2c_layout* L, const void* d_in, void* d_out, uint64_t out_cap,
                             uint64_t* d_out_off) {
-    if (!ctx || !L || !d_out || !d_out_off || (L->payload && !d_in)) return B2C_E_ARG;
+    if (!ctx || !L || !d_out || !d_out_off || (L->v.payload && !d_in)) return B2C_E_ARG;
     B2C_CUDA(ctx, cudaSetDevice(ctx->device));
-    return launch_compress(ctx, *L, static_cast<const uint8_t*>(d_in), static_cast<uint8_t*>(d_out), out_cap,
-                           d_out_off);
+    return launch_compress(ctx, ctx->main, L->v, static_cast<const uint8_t*>(d_in), static_cast<uint8_t*>(d_out),
+                           out_cap, d_out_off);
 }
 
 int b2c_snappy_uncompressed_length_dev(b2c_ctx* ctx, const b2c_layout* L, const void* d_in, uint32_t* d_ulen,
                                        int32_t* d_status) {
     if (!ctx || !L || !d_ulen) return B2C_E_ARG;
     B2C_CUDA(ctx, cudaSetDevice(ctx->device));
-    return launch_ulen(ctx, *L, static_cast<const uint8_t*>(d_in), d_ulen, d_status);
+    return launch_ulen(ctx, ctx->main, L->v, static_cast<const uint8_t*>(d_in), d_ulen, d_status);
 }
 
 int b2c_snappy_decompress_dev(b2c_ctx* ctx, const b2c_layout* in, const void* d_in, const b2c_layout* out,
                               void* d_out, uint32_t* d_ulen, int32_t* d_status) {
     if (!ctx || !in || !out || !d_status) return B2C_E_ARG;
     B2C_CUDA(ctx, cudaSetDevice(ctx->device));
-    return launch_decompress(ctx, *in, static_cast<const uint8_t*>(d_in), *out, static_cast<uint8_t*>(d_out), d_ulen,
-                             d_status);
+    return launch_decompress(ctx, ctx->main, in->v, static_cast<const uint8_t*>(d_in), out->v,
+                             static_cast<uint8_t*>(d_out), d_ulen, d_status);
 }
 
 // ---------------------------------------------------------------------------
-// host (end-to-end) entry points
+// host (end-to-end) entry points: slab pipeline
 // ---------------------------------------------------------------------------
 namespace {
 
-struct Gathered {
-    std::vector<uint64_t> off;  // staging offsets, 16-byte aligned
-    std::vector<uint32_t> len;
-    uint64_t total = 0;         // staging bytes
-    uint64_t payload = 0;
+using Clock = std::chrono::steady_clock;
+inline double secs(Clock::time_point a, Clock::time_point b) { return std::chrono::duration<double>(b - a).count(); }
+
+struct Slab {
+    uint32_t m0, m1;   // message range
+    uint64_t bytes;    // staging bytes of the payload (messages 16-byte aligned)
+    uint64_t payload;  // sum of message lengths
 };
 
-// Sum segment lengths per message and lay the messages out in staging.
-int plan_gather(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, Gathered& g) {
-    g.off.resize(n);
-    g.len.resize(n);
-    uint64_t pos = 0;
-    for (uint32_t i = 0; i < n; i++) {
-        uint64_t l = 0;
-        for (uint32_t s = seg_begin[i]; s < seg_begin[i + 1]; s++) l += segs[s].iov_len;
-        if (l > 0xffffffffull) return set_err(ctx, B2C_E_ARG, "message longer than 4 GiB - 1", cudaSuccess);
-        g.off[i] = pos;
-        g.len[i] = (uint32_t)l;
-        g.payload += l;
-        pos += align_up(l, 16);
+struct BatchPlan {
+    std::vector<uint64_t>& off;  // per message: offset inside its slab's staging
+    std::vector<uint32_t>& len;
+    std::vector<Slab> slabs;
+    uint64_t payload = 0;
+    explicit BatchPlan(b2c_ctx* ctx) : off(ctx->bp_off), len(ctx->bp_len) {}
+};
+
+// Is `p` page-locked host memory CUDA can DMA into directly (cudaHostAlloc / cudaHostRegister)?
+bool is_pinned_host(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
     }
-    g.total = pos;
+    return a.type == cudaMemoryTypeHost;
+}
+
+// Message lengths (parallel), staging offsets and slab cuts (serial prefix).
+int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, BatchPlan& p) {
+    if (p.off.size() < n) p.off.resize(n);
+    if (p.len.size() < n) p.len.resize(n);
+    std::atomic<bool> too_long(false);
+    pool(ctx).run(threads_for((uint64_t)n * 64), [&](unsigned t, unsigned T) {
+        uint32_t lo = (uint32_t)((uint64_t)n * t / T), hi = (uint32_t)((uint64_t)n * (t + 1) / T);
+        for (uint32_t i = lo; i < hi; i++) {
+            uint64_t l = 0;
+            for (uint32_t s = seg_begin[i]; s < seg_begin[i + 1]; s++) l += segs[s].iov_len;
+            if (l > 0xffffffffull) {
+                too_long = true;
+                l = 0;
+            }
+            p.len[i] = (uint32_t)l;
+        }
+    });
+    if (too_long) return set_err(ctx, B2C_E_ARG, "message longer than 4 GiB - 1", cudaSuccess);
+    const uint64_t target = ctx->slab_bytes;
+    const uint32_t max_msgs = 1u << 18;
+    Slab cur = {0, 0, 0, 0};
+    for (uint32_t i = 0; i < n; i++) {
+        const uint64_t a = align_up(p.len[i], 16);
+        if (cur.m1 > cur.m0 && (cur.bytes + a > target || cur.m1 - cur.m0 >= max_msgs)) {
+            p.slabs.push_back(cur);
+            cur = {i, i, 0, 0};
+        }
+        p.off[i] = cur.bytes;
+        cur.bytes += a;
+        cur.payload += p.len[i];
+        cur.m1 = i + 1;
+        p.payload += p.len[i];
+    }
+    if (cur.m1 > cur.m0) p.slabs.push_back(cur);
     return B2C_OK;
 }
 
-// memcpy every segment into pinned staging, split over host threads by message range.
-void run_gather(const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, const Gathered& g, uint8_t* stage) {
-    parallel_for(host_threads(g.payload), [&](unsigned t, unsigned T) {
-        uint32_t lo = (uint32_t)((uint64_t)n * t / T), hi = (uint32_t)((uint64_t)n * (t + 1) / T);
+// memcpy every segment of the slab's messages into pinned staging.
+void gather_slab(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, const BatchPlan& p, const Slab& s,
+                 uint8_t* stage) {
+    const uint32_t cnt = s.m1 - s.m0;
+    pool(ctx).run(threads_for(s.bytes), [&](unsigned t, unsigned T) {
+        uint32_t lo = s.m0 + (uint32_t)((uint64_t)cnt * t / T), hi = s.m0 + (uint32_t)((uint64_t)cnt * (t + 1) / T);
         for (uint32_t i = lo; i < hi; i++) {
-            uint8_t* d = stage + g.off[i];
-            for (uint32_t s = seg_begin[i]; s < seg_begin[i + 1]; s++) {
-                memcpy(d, segs[s].iov_base, segs[s].iov_len);
-                d += segs[s].iov_len;
+            uint8_t* d = stage + p.off[i];
+            for (uint32_t q = seg_begin[i]; q < seg_begin[i + 1]; q++) {
+                memcpy(d, segs[q].iov_base, segs[q].iov_len);
+                d += segs[q].iov_len;
             }
         }
     });
 }
 
-void parallel_copy(void* dst, const void* src, uint64_t bytes) {
-    parallel_for(host_threads(bytes), [&](unsigned t, unsigned T) {
+void parallel_copy(b2c_ctx* ctx, void* dst, const void* src, uint64_t bytes) {
+    if (!bytes) return;
+    pool(ctx).run(threads_for(bytes), [&](unsigned t, unsigned T) {
         uint64_t lo = bytes * t / T, hi = bytes * (t + 1) / T;
         memcpy(static_cast<uint8_t*>(dst) + lo, static_cast<const uint8_t*>(src) + lo, hi - lo);
     });
 }
 
-struct LayoutGuard {
-    b2c_layout* L = nullptr;
-    ~LayoutGuard() { b2c_layout_destroy(L); }
+struct Trace {
+    bool on;
+    const char* what;
+    double plan = 0, gather = 0, layout = 0, submit = 0, wait = 0, copy_out = 0;
+    Clock::time_point t0;
+    Trace(bool on_, const char* w) : on(on_), what(w), t0(Clock::now()) {}
+    void report(size_t slabs, uint64_t payload) {
+        if (!on) return;
+        double total = secs(t0, Clock::now());
+        fprintf(stderr,
+                "[b2c] %s: %.2f ms total, %zu slabs, %.1f MB payload | plan %.2f gather %.2f layout %.2f submit %.2f "
+                "wait %.2f copy-out %.2f ms\n",
+                what, total * 1e3, slabs, payload / 1e6, plan * 1e3, gather * 1e3, layout * 1e3, submit * 1e3,
+                wait * 1e3, copy_out * 1e3);
+    }
 };
+
+#define TIMED(acc, stmt)                       \
+    do {                                       \
+        auto _t = Clock::now();                \
+        stmt;                                  \
+        (acc) += secs(_t, Clock::now());       \
+    } while (0)
 
 }  // namespace
 
@@ -498,36 +783,57 @@ int b2c_crc32c_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_be
     if (!ctx || (n && (!segs || !seg_begin || !crc))) return B2C_E_ARG;
     if (n == 0) return B2C_OK;
     B2C_CUDA(ctx, cudaSetDevice(ctx->device));
-    Gathered g;
-    int rc = plan_gather(ctx, segs, seg_begin, n, g);
+    Trace tr(ctx->trace, "crc32c_batch");
+    BatchPlan bp(ctx);
+    int rc;
+    TIMED(tr.plan, rc = plan_batch(ctx, segs, seg_begin, n, bp));
     if (rc) return rc;
-    const size_t meta = (size_t)n * 4;
-    if ((rc = pin_reserve(ctx, &ctx->h_pin_in, &ctx->h_pin_in_cap, g.total + meta + 64))) return rc;
-    if ((rc = pin_reserve(ctx, &ctx->h_pin_out, &ctx->h_pin_out_cap, meta + 64))) return rc;
-    if ((rc = ws_reserve(ctx, ctx->ws_io_in, g.total + meta + 64))) return rc;
-    if ((rc = ws_reserve(ctx, ctx->ws_io_out, meta + 64))) return rc;
-    uint8_t* stage = static_cast<uint8_t*>(ctx->h_pin_in);
-    run_gather(segs, seg_begin, n, g, stage);
-    uint8_t* d_in = static_cast<uint8_t*>(ctx->ws_io_in.p);
-    uint32_t* d_init = nullptr;
-    uint64_t h2d = g.total;
-    B2C_CUDA(ctx, cudaMemcpyAsync(d_in, stage, g.total, cudaMemcpyHostToDevice, ctx->stream));
-    if (init) {
-        const size_t init_at = align_up(g.total, 16);
-        memcpy(stage + init_at, init, meta);
-        d_init = reinterpret_cast<uint32_t*>(d_in + init_at);
-        B2C_CUDA(ctx, cudaMemcpyAsync(d_init, stage + init_at, meta, cudaMemcpyHostToDevice, ctx->stream));
-        h2d += meta;
+    uint64_t h2d = 0, d2h = 0;
+    const size_t K = bp.slabs.size();
+    auto finish = [&](size_t k) -> int {
+        Lane& lane = ctx->pipe[k % kPipeLanes];
+        const Slab& s = bp.slabs[k];
+        TIMED(tr.wait, B2C_CUDA(ctx, cudaEventSynchronize(lane.ev_done)));
+        TIMED(tr.copy_out, memcpy(crc + s.m0, lane.h_out.p, (size_t)(s.m1 - s.m0) * 4));
+        return B2C_OK;
+    };
+    for (size_t k = 0; k < K; k++) {
+        if (k >= (size_t)kPipeLanes && (rc = finish(k - kPipeLanes))) return rc;
+        Lane& lane = ctx->pipe[k % kPipeLanes];
+        const Slab& s = bp.slabs[k];
+        const uint32_t cnt = s.m1 - s.m0;
+        LayoutPlan lp;
+        TIMED(tr.layout, lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx));
+        const size_t blob_at = align_up(s.bytes, 256);
+        const size_t init_at = align_up(blob_at + lp.blob_bytes, 256);
+        const size_t in_bytes = init_at + (init ? (size_t)cnt * 4 : 0);
+        if ((rc = pin_reserve(ctx, lane, lane.h_in, in_bytes + 64))) return rc;
+        if ((rc = ws_reserve(ctx, lane, lane.d_in, in_bytes + 64))) return rc;
+        if ((rc = pin_reserve(ctx, lane, lane.h_out, (size_t)cnt * 4 + 64))) return rc;
+        if ((rc = ws_reserve(ctx, lane, lane.d_out, (size_t)cnt * 4 + 64))) return rc;
+        uint8_t* stage = static_cast<uint8_t*>(lane.h_in.p);
+        TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, stage));
+        TIMED(tr.layout, lp.fill(stage + blob_at));
+        if (init) memcpy(stage + init_at, init + s.m0, (size_t)cnt * 4);
+        auto ts = Clock::now();
+        uint8_t* d_in = static_cast<uint8_t*>(lane.d_in.p);
+        B2C_CUDA(ctx, cudaMemcpyAsync(d_in, stage, in_bytes, cudaMemcpyHostToDevice, lane.stream));
+        h2d += in_bytes;
+        LayoutView lv;
+        lp.bind(d_in + blob_at, &lv);
+        uint32_t* d_crc = static_cast<uint32_t*>(lane.d_out.p);
+        if ((rc = launch_crc32c(ctx, lane, lv, d_in, init ? reinterpret_cast<uint32_t*>(d_in + init_at) : nullptr, d_crc)))
+            return rc;
+        B2C_CUDA(ctx, cudaMemcpyAsync(lane.h_out.p, d_crc, (size_t)cnt * 4, cudaMemcpyDeviceToHost, lane.stream));
+        d2h += (size_t)cnt * 4;
+        B2C_CUDA(ctx, cudaEventRecord(lane.ev_done, lane.stream));
+        tr.submit += secs(ts, Clock::now());
     }
-    LayoutGuard lg;
-    if ((rc = b2c_layout_create(ctx, n, g.off.data(), g.len.data(), &lg.L))) return rc;
-    uint32_t* d_crc = static_cast<uint32_t*>(ctx->ws_io_out.p);
-    if ((rc = launch_crc32c(ctx, *lg.L, d_in, d_init, d_crc))) return rc;
-    B2C_CUDA(ctx, cudaMemcpyAsync(ctx->h_pin_out, d_crc, meta, cudaMemcpyDeviceToHost, ctx->stream));
-    B2C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    memcpy(crc, ctx->h_pin_out, meta);
-    ctx->last_h2d = h2d + (uint64_t)n * 12;
-    ctx->last_d2h = meta;
+    for (size_t k = K > (size_t)kPipeLanes ? K - kPipeLanes : 0; k < K; k++)
+        if ((rc = finish(k))) return rc;
+    ctx->last_h2d = h2d;
+    ctx->last_d2h = d2h;
+    tr.report(K, bp.payload);
     return B2C_OK;
 }
 
@@ -537,35 +843,92 @@ int b2c_snappy_compress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_
     out_off[0] = 0;
     if (n == 0) return B2C_OK;
     B2C_CUDA(ctx, cudaSetDevice(ctx->device));
-    Gathered g;
-    int rc = plan_gather(ctx, segs, seg_begin, n, g);
+    Trace tr(ctx->trace, "compress_batch");
+    BatchPlan bp(ctx);
+    int rc;
+    TIMED(tr.plan, rc = plan_batch(ctx, segs, seg_begin, n, bp));
     if (rc) return rc;
-    if ((rc = pin_reserve(ctx, &ctx->h_pin_in, &ctx->h_pin_in_cap, g.total + 64))) return rc;
-    if ((rc = ws_reserve(ctx, ctx->ws_io_in, g.total + 64))) return rc;
-    uint8_t* stage = static_cast<uint8_t*>(ctx->h_pin_in);
-    run_gather(segs, seg_begin, n, g, stage);
-    uint8_t* d_in = static_cast<uint8_t*>(ctx->ws_io_in.p);
-    B2C_CUDA(ctx, cudaMemcpyAsync(d_in, stage, g.total, cudaMemcpyHostToDevice, ctx->stream));
-    LayoutGuard lg;
-    if ((rc = b2c_layout_create(ctx, n, g.off.data(), g.len.data(), &lg.L))) return rc;
-    const uint64_t cap = lg.L->max_comp;
-    const size_t off_bytes = ((size_t)n + 1) * 8;
-    if ((rc = ws_reserve(ctx, ctx->ws_io_out, cap + off_bytes + 64))) return rc;
-    uint8_t* d_out = static_cast<uint8_t*>(ctx->ws_io_out.p);
-    uint64_t* d_out_off = reinterpret_cast<uint64_t*>(d_out + align_up(cap, 16));
-    if ((rc = launch_compress(ctx, *lg.L, d_in, d_out, cap, d_out_off))) return rc;
-    if ((rc = pin_reserve(ctx, &ctx->h_pin_out, &ctx->h_pin_out_cap, off_bytes + 64))) return rc;
-    B2C_CUDA(ctx, cudaMemcpyAsync(ctx->h_pin_out, d_out_off, off_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    B2C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    memcpy(out_off, ctx->h_pin_out, off_bytes);
-    const uint64_t total = out_off[n];
-    if (total > out_cap) return set_err(ctx, B2C_E_CAPACITY, "compress_batch: out_cap too small", cudaSuccess);
-    if ((rc = pin_reserve(ctx, &ctx->h_pin_out, &ctx->h_pin_out_cap, total + 64))) return rc;
-    B2C_CUDA(ctx, cudaMemcpyAsync(ctx->h_pin_out, d_out, total, cudaMemcpyDeviceToHost, ctx->stream));
-    B2C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    parallel_copy(out, ctx->h_pin_out, total);
-    ctx->last_h2d = g.total + (uint64_t)n * 12;
-    ctx->last_d2h = total + off_bytes;
+    uint64_t h2d = 0, d2h = 0, out_base = 0;
+    const size_t K = bp.slabs.size();
+    std::vector<uint64_t> slab_total(K, 0), slab_base(K, 0);
+    const bool direct = is_pinned_host(out);  // caller's buffer is page-locked: DMA straight into it
+    uint64_t fetch_base = 0;
+    // stage B: sizes are on the host -> fetch the packed bytes
+    auto fetch = [&](size_t k) -> int {
+        Lane& lane = ctx->pipe[k % kPipeLanes];
+        const Slab& s = bp.slabs[k];
+        const uint32_t cnt = s.m1 - s.m0;
+        TIMED(tr.wait, B2C_CUDA(ctx, cudaEventSynchronize(lane.ev_meta)));
+        const uint64_t* meta = static_cast<const uint64_t*>(lane.h_out.p);
+        const uint64_t total = meta[cnt];
+        slab_total[k] = total;
+        slab_base[k] = fetch_base;
+        if (fetch_base + total > out_cap)
+            return set_err(ctx, B2C_E_CAPACITY, "compress_batch: out_cap too small", cudaSuccess);
+        fetch_base += total;
+        const size_t data_at = align_up(((size_t)cnt + 1) * 8, 256);
+        uint8_t* dst = direct ? static_cast<uint8_t*>(out) + slab_base[k] : static_cast<uint8_t*>(lane.h_out.p) + data_at;
+        B2C_CUDA(ctx, cudaMemcpyAsync(dst, lane.d_out.p, total, cudaMemcpyDeviceToHost, lane.stream));
+        d2h += total;
+        B2C_CUDA(ctx, cudaEventRecord(lane.ev_done, lane.stream));
+        return B2C_OK;
+    };
+    // stage C: packed bytes are on the host -> caller's buffer
+    auto finish = [&](size_t k) -> int {
+        Lane& lane = ctx->pipe[k % kPipeLanes];
+        const Slab& s = bp.slabs[k];
+        const uint32_t cnt = s.m1 - s.m0;
+        TIMED(tr.wait, B2C_CUDA(ctx, cudaEventSynchronize(lane.ev_done)));
+        const uint64_t* meta = static_cast<const uint64_t*>(lane.h_out.p);
+        const size_t data_at = align_up(((size_t)cnt + 1) * 8, 256);
+        auto tc = Clock::now();
+        if (!direct)
+            parallel_copy(ctx, static_cast<uint8_t*>(out) + out_base, static_cast<uint8_t*>(lane.h_out.p) + data_at,
+                          slab_total[k]);
+        for (uint32_t i = 0; i < cnt; i++) out_off[s.m0 + i + 1] = out_base + meta[i + 1];
+        out_base += slab_total[k];
+        tr.copy_out += secs(tc, Clock::now());
+        return B2C_OK;
+    };
+    for (size_t k = 0; k < K + 2; k++) {
+        if (k < K) {
+            Lane& lane = ctx->pipe[k % kPipeLanes];
+            const Slab& s = bp.slabs[k];
+            const uint32_t cnt = s.m1 - s.m0;
+            LayoutPlan lp;
+            TIMED(tr.layout, lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx));
+            const size_t blob_at = align_up(s.bytes, 256);
+            const size_t in_bytes = blob_at + lp.blob_bytes;
+            const uint64_t cap = lp.v.max_comp;
+            const size_t meta_bytes = ((size_t)cnt + 1) * 8;
+            const size_t off_at = align_up(cap, 256);  // device: packed output, then its offsets
+            if ((rc = pin_reserve(ctx, lane, lane.h_in, in_bytes + 64))) return rc;
+            if ((rc = ws_reserve(ctx, lane, lane.d_in, in_bytes + 64))) return rc;
+            if ((rc = ws_reserve(ctx, lane, lane.d_out, off_at + meta_bytes + 64))) return rc;
+            if ((rc = pin_reserve(ctx, lane, lane.h_out, align_up(meta_bytes, 256) + cap + 64))) return rc;
+            uint8_t* stage = static_cast<uint8_t*>(lane.h_in.p);
+            TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, stage));
+            TIMED(tr.layout, lp.fill(stage + blob_at));
+            auto ts = Clock::now();
+            uint8_t* d_in = static_cast<uint8_t*>(lane.d_in.p);
+            B2C_CUDA(ctx, cudaMemcpyAsync(d_in, stage, in_bytes, cudaMemcpyHostToDevice, lane.stream));
+            h2d += in_bytes;
+            LayoutView lv;
+            lp.bind(d_in + blob_at, &lv);
+            uint8_t* d_out = static_cast<uint8_t*>(lane.d_out.p);
+            uint64_t* d_out_off = reinterpret_cast<uint64_t*>(d_out + off_at);
+            if ((rc = launch_compress(ctx, lane, lv, d_in, d_out, cap, d_out_off))) return rc;
+            B2C_CUDA(ctx, cudaMemcpyAsync(lane.h_out.p, d_out_off, meta_bytes, cudaMemcpyDeviceToHost, lane.stream));
+            d2h += meta_bytes;
+            B2C_CUDA(ctx, cudaEventRecord(lane.ev_meta, lane.stream));
+            tr.submit += secs(ts, Clock::now());
+        }
+        if (k >= 1 && k - 1 < K && (rc = fetch(k - 1))) return rc;
+        if (k >= 2 && k - 2 < K && (rc = finish(k - 2))) return rc;
+    }
+    ctx->last_h2d = h2d;
+    ctx->last_d2h = d2h;
+    tr.report(K, bp.payload);
     return B2C_OK;
 }
 
@@ -575,51 +938,111 @@ int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint3
     out_off[0] = 0;
     if (n == 0) return B2C_OK;
     B2C_CUDA(ctx, cudaSetDevice(ctx->device));
-    Gathered g;
-    int rc = plan_gather(ctx, segs, seg_begin, n, g);
+    Trace tr(ctx->trace, "decompress_batch");
+    BatchPlan bp(ctx);
+    int rc;
+    TIMED(tr.plan, rc = plan_batch(ctx, segs, seg_begin, n, bp));
     if (rc) return rc;
-    if ((rc = pin_reserve(ctx, &ctx->h_pin_in, &ctx->h_pin_in_cap, g.total + 64))) return rc;
-    if ((rc = ws_reserve(ctx, ctx->ws_io_in, g.total + 64))) return rc;
-    uint8_t* stage = static_cast<uint8_t*>(ctx->h_pin_in);
-    run_gather(segs, seg_begin, n, g, stage);
-    uint8_t* d_in = static_cast<uint8_t*>(ctx->ws_io_in.p);
-    B2C_CUDA(ctx, cudaMemcpyAsync(d_in, stage, g.total, cudaMemcpyHostToDevice, ctx->stream));
-    // Output slots from the (lenient) preambles.  A stream cannot expand by more than
-    // 64/3 (a 3-byte copy yields at most 64 bytes), so a larger claim is malformed: the
-    // reference would run out of input before producing it (snappy.cc:867).
-    std::vector<uint64_t> o_off(n);
-    std::vector<uint32_t> o_cap(n);
-    uint64_t pos = 0;
-    for (uint32_t i = 0; i < n; i++) {
-        uint32_t ulen = 0;
-        int k = b2c_snappy_read_preamble(stage + g.off[i], g.len[i], &ulen);
-        bool plausible = k > 0 && (uint64_t)ulen <= ((uint64_t)g.len[i] * 64) / 3 + 64;
-        o_off[i] = pos;
-        o_cap[i] = plausible ? ulen : 0;
-        out_off[i] = pos;
-        pos += o_cap[i];
+    uint64_t h2d = 0, d2h = 0, out_base = 0;
+    const size_t K = bp.slabs.size();
+    std::vector<uint64_t> slab_out(K, 0);
+    std::vector<uint64_t>& o_off = ctx->tmp_off;
+    std::vector<uint32_t>& o_cap = ctx->tmp_cap;
+    const bool direct = is_pinned_host(out);  // caller's buffer is page-locked: DMA straight into it
+    auto finish = [&](size_t k) -> int {
+        Lane& lane = ctx->pipe[k % kPipeLanes];
+        const Slab& s = bp.slabs[k];
+        const uint32_t cnt = s.m1 - s.m0;
+        TIMED(tr.wait, B2C_CUDA(ctx, cudaEventSynchronize(lane.ev_done)));
+        auto tc = Clock::now();
+        const uint8_t* h = static_cast<const uint8_t*>(lane.h_out.p);
+        const uint64_t base = out_off[s.m0];
+        if (!direct) parallel_copy(ctx, static_cast<uint8_t*>(out) + base, h, slab_out[k]);
+        const int32_t* st = reinterpret_cast<const int32_t*>(h + align_up(slab_out[k], 256));
+        for (uint32_t i = 0; i < cnt; i++)  // TOO_SMALL can only mean "implausible preamble" here
+            status[s.m0 + i] = st[i] == B2C_TOO_SMALL ? B2C_CORRUPT : st[i];
+        tr.copy_out += secs(tc, Clock::now());
+        return B2C_OK;
+    };
+    for (size_t k = 0; k < K; k++) {
+        if (k >= (size_t)kPipeLanes && (rc = finish(k - kPipeLanes))) return rc;
+        Lane& lane = ctx->pipe[k % kPipeLanes];
+        const Slab& s = bp.slabs[k];
+        const uint32_t cnt = s.m1 - s.m0;
+        LayoutPlan lin;
+        TIMED(tr.layout, lin.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx));
+        if ((rc = pin_reserve(ctx, lane, lane.h_in, align_up(s.bytes, 256) + lin.blob_bytes + (size_t)cnt * 16 + 4096)))
+            return rc;
+        uint8_t* stage = static_cast<uint8_t*>(lane.h_in.p);
+        TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, stage));
+        // Output slots from the (lenient) preambles.  A stream cannot expand by more than 64/3
+        // (a 3-byte copy yields at most 64 bytes), so a larger claim is malformed: the reference
+        // would run out of input before producing it (snappy.cc:867).
+        auto tl = Clock::now();
+        if (o_off.size() < cnt) o_off.resize(cnt);
+        if (o_cap.size() < cnt) o_cap.resize(cnt);
+        pool(ctx).run(threads_for((uint64_t)cnt * 64), [&](unsigned t, unsigned T) {
+            uint32_t lo = (uint32_t)((uint64_t)cnt * t / T), hi = (uint32_t)((uint64_t)cnt * (t + 1) / T);
+            for (uint32_t i = lo; i < hi; i++) {
+                uint32_t ulen = 0;
+                const uint32_t clen = bp.len[s.m0 + i];
+                int kk = b2c_snappy_read_preamble(stage + bp.off[s.m0 + i], clen, &ulen);
+                bool plausible = kk > 0 && (uint64_t)ulen <= ((uint64_t)clen * 64) / 3 + 64;
+                o_cap[i] = plausible ? ulen : 0;
+            }
+        });
+        uint64_t pos = 0;
+        for (uint32_t i = 0; i < cnt; i++) {
+            o_off[i] = pos;
+            out_off[s.m0 + i] = out_base + pos;
+            pos += o_cap[i];
+        }
+        slab_out[k] = pos;
+        if (out_base + pos > out_cap) return set_err(ctx, B2C_E_CAPACITY, "decompress_batch: out_cap too small", cudaSuccess);
+        out_base += pos;
+        out_off[s.m1] = out_base;
+        LayoutPlan lout;
+        lout.plan(cnt, o_off.data(), o_cap.data(), ctx);
+        const size_t blob_in_at = align_up(s.bytes, 256);
+        const size_t blob_out_at = align_up(blob_in_at + lin.blob_bytes, 256);
+        const size_t in_bytes = blob_out_at + lout.blob_bytes;
+        if ((rc = pin_reserve(ctx, lane, lane.h_in, in_bytes + 64))) return rc;  // (already large enough in practice)
+        stage = static_cast<uint8_t*>(lane.h_in.p);
+        lin.fill(stage + blob_in_at);
+        lout.fill(stage + blob_out_at);
+        tr.layout += secs(tl, Clock::now());
+        const size_t st_at = align_up(pos, 256);
+        if ((rc = ws_reserve(ctx, lane, lane.d_in, in_bytes + 64))) return rc;
+        if ((rc = ws_reserve(ctx, lane, lane.d_out, st_at + (size_t)cnt * 4 + 64))) return rc;
+        if ((rc = pin_reserve(ctx, lane, lane.h_out, st_at + (size_t)cnt * 4 + 64))) return rc;
+        auto ts = Clock::now();
+        uint8_t* d_in = static_cast<uint8_t*>(lane.d_in.p);
+        B2C_CUDA(ctx, cudaMemcpyAsync(d_in, stage, in_bytes, cudaMemcpyHostToDevice, lane.stream));
+        h2d += in_bytes;
+        LayoutView vin, vout;
+        lin.bind(d_in + blob_in_at, &vin);
+        lout.bind(d_in + blob_out_at, &vout);
+        uint8_t* d_out = static_cast<uint8_t*>(lane.d_out.p);
+        int32_t* d_status = reinterpret_cast<int32_t*>(d_out + st_at);
+        if ((rc = launch_decompress(ctx, lane, vin, d_in, vout, d_out, nullptr, d_status))) return rc;
+        if (direct) {
+            const uint64_t base = out_off[s.m0];
+            if (pos) B2C_CUDA(ctx, cudaMemcpyAsync(static_cast<uint8_t*>(out) + base, d_out, pos, cudaMemcpyDeviceToHost, lane.stream));
+            B2C_CUDA(ctx, cudaMemcpyAsync(static_cast<uint8_t*>(lane.h_out.p) + st_at, d_status, (size_t)cnt * 4,
+                                          cudaMemcpyDeviceToHost, lane.stream));
+            d2h += pos + (size_t)cnt * 4;
+        } else {
+            B2C_CUDA(ctx, cudaMemcpyAsync(lane.h_out.p, d_out, st_at + (size_t)cnt * 4, cudaMemcpyDeviceToHost, lane.stream));
+            d2h += st_at + (size_t)cnt * 4;
+        }
+        B2C_CUDA(ctx, cudaEventRecord(lane.ev_done, lane.stream));
+        tr.submit += secs(ts, Clock::now());
     }
-    out_off[n] = pos;
-    if (pos > out_cap) return set_err(ctx, B2C_E_CAPACITY, "decompress_batch: out_cap too small", cudaSuccess);
-    LayoutGuard lin, lout;
-    if ((rc = b2c_layout_create(ctx, n, g.off.data(), g.len.data(), &lin.L))) return rc;
-    if ((rc = b2c_layout_create(ctx, n, o_off.data(), o_cap.data(), &lout.L))) return rc;
-    const size_t st_bytes = (size_t)n * 4;
-    if ((rc = ws_reserve(ctx, ctx->ws_io_out, pos + st_bytes + 64))) return rc;
-    uint8_t* d_out = static_cast<uint8_t*>(ctx->ws_io_out.p);
-    int32_t* d_status = reinterpret_cast<int32_t*>(d_out + align_up(pos, 16));
-    if ((rc = launch_decompress(ctx, *lin.L, d_in, *lout.L, d_out, nullptr, d_status))) return rc;
-    if ((rc = pin_reserve(ctx, &ctx->h_pin_out, &ctx->h_pin_out_cap, align_up(pos, 16) + st_bytes + 64))) return rc;
-    uint8_t* h_out = static_cast<uint8_t*>(ctx->h_pin_out);
-    if (pos) B2C_CUDA(ctx, cudaMemcpyAsync(h_out, d_out, pos, cudaMemcpyDeviceToHost, ctx->stream));
-    B2C_CUDA(ctx, cudaMemcpyAsync(h_out + align_up(pos, 16), d_status, st_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    B2C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    if (pos) parallel_copy(out, h_out, pos);
-    memcpy(status, h_out + align_up(pos, 16), st_bytes);
-    for (uint32_t i = 0; i < n; i++)  // TOO_SMALL here only means "implausible preamble"
-        if (status[i] == B2C_TOO_SMALL) status[i] = B2C_CORRUPT;
-    ctx->last_h2d = g.total + (uint64_t)n * 24;
-    ctx->last_d2h = pos + st_bytes;
+    for (size_t k = K > (size_t)kPipeLanes ? K - kPipeLanes : 0; k < K; k++)
+        if ((rc = finish(k))) return rc;
+    ctx->last_h2d = h2d;
+    ctx->last_d2h = d2h;
+    tr.report(K, bp.payload);
     return B2C_OK;
 }
 

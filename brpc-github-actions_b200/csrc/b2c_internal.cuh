@@ -14,46 +14,77 @@ namespace b2c {
 
 constexpr uint32_t kFragBytes = 65536;  // snappy.h:202-203 kBlockSize
 constexpr uint32_t kCrcChunk = 4096;    // bytes per CRC work item (one quad of lanes)
-constexpr int kNumSM_B200 = 148;
+constexpr int kPipeLanes = 3;           // staging slots of the end-to-end pipeline
 
-// ---- device workspace -----------------------------------------------------
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
 };
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
 
-// ---- layout (host + device mirrors) --------------------------------------
-struct Layout {
-    b2c_ctx* ctx = nullptr;
+// One stream with its private workspaces: kernels of different lanes may overlap.
+struct Lane {
+    cudaStream_t stream = nullptr;
+    DevBuf ws_frag;   // fragment scratch slots (compress)
+    DevBuf ws_misc;   // sizes, scans, chunk remainders
+    DevBuf d_in;      // e2e: device input arena (+ layout blob)
+    DevBuf d_out;     // e2e: device output arena (+ result metadata)
+    PinBuf h_in;      // e2e: pinned staging, host -> device
+    PinBuf h_out;     // e2e: pinned staging, device -> host
+    cudaEvent_t ev_meta = nullptr;  // result metadata has reached h_out
+    cudaEvent_t ev_done = nullptr;  // everything of this slab has reached h_out
+};
+
+// What the kernels consume: device pointers of one batch shape.  Arrays that are the
+// identity for this batch are nullptr (fragment f == message f, chunk c == message c, ...).
+struct LayoutView {
     uint32_t n = 0;
-    uint64_t payload = 0;      // sum len
-    uint64_t arena_end = 0;    // max(off+len)
-    uint64_t max_comp = 0;     // sum MaxCompressedLength(len)+5
-    std::vector<uint64_t> h_off;
-    std::vector<uint32_t> h_len;
-    // device copies
-    uint64_t* d_off = nullptr;  // [n]
-    uint32_t* d_len = nullptr;  // [n]
-    // --- snappy fragments (snappy.cc:887-948): fragment f covers message frag_msg[f],
-    //     bytes [65536*k, ...) with k = f - frag_first[frag_msg[f]]
+    uint64_t payload = 0;    // sum len
+    uint64_t arena_end = 0;  // max(off+len)
+    uint64_t max_comp = 0;   // sum MaxCompressedLength(len)+5
+    const uint64_t* d_off = nullptr;  // [n]
+    const uint32_t* d_len = nullptr;  // [n]
+    // snappy fragments (snappy.cc:887-948): message m owns max(1, ceil(len/65536)) fragments
     uint32_t n_frags = 0;
-    uint32_t* d_frag_msg = nullptr;    // [n_frags]
-    uint32_t* d_frag_first = nullptr;  // [n+1]
-    uint64_t* d_frag_slot = nullptr;   // [n_frags] byte offset of the fragment's scratch slot
+    const uint32_t* d_frag_msg = nullptr;    // [n_frags]   null: f == m
+    const uint32_t* d_frag_first = nullptr;  // [n+1]       null: first[m] == m
+    const uint64_t* d_frag_slot = nullptr;   // [n_frags]   null: slot = f * slot_stride
+    uint64_t slot_stride = 0;
     uint64_t frag_scratch_bytes = 0;
-    // fragments grouped by hash-table size class (S: <=1024 entries, M: <=4096, L: <=16384)
+    // fragments by hash-table size class (<=1024 / <=4096 / <=16384 entries); null list: identity
     uint32_t n_class[3] = {0, 0, 0};
-    uint32_t* d_class_list[3] = {nullptr, nullptr, nullptr};
-    // --- decompress classes by slot capacity (this layout used as OUTPUT layout)
+    const uint32_t* d_class_list[3] = {nullptr, nullptr, nullptr};
+    // messages by output-slot capacity class (<=1 KiB / <=8 KiB / larger; layout used as decompress OUTPUT)
     uint32_t n_dclass[3] = {0, 0, 0};
-    uint32_t* d_dclass_list[3] = {nullptr, nullptr, nullptr};
-    // --- crc chunks: chunk c covers message chunk_msg[c]
+    const uint32_t* d_dclass_list[3] = {nullptr, nullptr, nullptr};
+    // crc chunks of kCrcChunk bytes: message m owns max(1, ceil(len/4096)) chunks
     uint32_t n_chunks = 0;
-    uint32_t n_multi = 0;              // messages with more than one chunk
-    uint32_t* d_chunk_msg = nullptr;   // [n_chunks]
-    uint32_t* d_chunk_first = nullptr; // [n+1]
-    uint32_t* d_multi_list = nullptr;  // [n_multi] message ids with >1 chunk
-    bool all_single_chunk_uniform = false;
+    uint32_t n_multi = 0;                      // messages with more than one chunk
+    const uint32_t* d_chunk_msg = nullptr;     // [n_chunks]  null: c == m
+    const uint32_t* d_chunk_first = nullptr;   // [n+1]       null: first[m] == m
+    const uint32_t* d_multi_list = nullptr;    // [n_multi]
+};
+
+// Host-side derivation of a LayoutView's arrays into one contiguous blob.
+struct LayoutPlan {
+    uint32_t n = 0;
+    const uint64_t* off = nullptr;
+    const uint32_t* len = nullptr;
+    LayoutView v;  // counts and scalars filled by plan(); pointers by bind()
+    bool has_frag_arrays = false, has_slot_array = false, has_class_lists = false, has_dclass_lists = false,
+         has_chunk_arrays = false;
+    // blob offsets (bytes)
+    size_t o_off = 0, o_slot = 0, o_len = 0, o_frag_msg = 0, o_frag_first = 0, o_class[3] = {0, 0, 0},
+           o_dclass[3] = {0, 0, 0}, o_chunk_msg = 0, o_chunk_first = 0, o_multi = 0;
+    size_t blob_bytes = 0;
+
+    // `par`: when non-null, large batches are scanned with the ctx's host thread pool
+    void plan(uint32_t n, const uint64_t* off, const uint32_t* len, b2c_ctx* par = nullptr);
+    void fill(uint8_t* blob) const;                           // blob_bytes of host memory
+    void bind(const uint8_t* d_blob, LayoutView* out) const;  // device address of the uploaded blob
 };
 
 }  // namespace b2c
@@ -61,31 +92,34 @@ struct Layout {
 struct b2c_ctx {
     int device = 0;
     int num_sms = 148;
-    cudaStream_t stream = nullptr;
-    cudaStream_t copy_stream = nullptr;
+    b2c::Lane main;                    // *_dev entry points
+    b2c::Lane pipe[b2c::kPipeLanes];   // *_batch entry points (slab pipeline)
     std::string err;
     uint64_t launches = 0;
     bool crc_attr_done = false;
     uint64_t last_h2d = 0, last_d2h = 0;
-    // CRC tables in device memory
     uint32_t* d_crc_tabA = nullptr;   // [4][256][32] replicated Z^64 tables (128 KiB)
     uint32_t* d_crc_small = nullptr;  // [3][4][256]: Z^4, Z^16, Z^32 slice tables (12 KiB)
-    // grow-only device workspace + pinned staging
-    b2c::DevBuf ws_frag;      // fragment scratch slots
-    b2c::DevBuf ws_misc;      // sizes, scans, chunk remainders
-    b2c::DevBuf ws_io_in;     // e2e: device input arena
-    b2c::DevBuf ws_io_out;    // e2e: device output arena
-    void* h_pin_in = nullptr;
-    size_t h_pin_in_cap = 0;
-    void* h_pin_out = nullptr;
-    size_t h_pin_out_cap = 0;
-    // optional kernel timing (b2c_prof_*)
+    // optional kernel timing (b2c_prof_*), main lane only
     bool prof_on = false;
     std::vector<cudaEvent_t> prof_ev[B2C_PROF_COUNT];  // start/stop pairs
     uint32_t prof_used[B2C_PROF_COUNT] = {0, 0, 0, 0};
+    // reusable host arrays of the *_batch entry points (avoid page-faulting fresh vectors per call)
+    std::vector<uint64_t> bp_off, tmp_off;
+    std::vector<uint32_t> bp_len, tmp_cap;
+    bool small_kernels = true;  // B2C_SMALL_KERNELS=0 routes <=1 KiB bodies through the warp kernels
+    int small_lpw_compress = 4, small_lpw_decompress = 8;  // bodies per warp (B2C_SMALL_LPW_C / _D: 4, 8, 16, 32)
+    // tunables (environment: B2C_SLAB_MB, B2C_HOST_THREADS, B2C_TRACE)
+    size_t slab_bytes = 32u << 20;
+    unsigned host_threads = 0;
+    bool trace = false;
 };
 
-struct b2c_layout : b2c::Layout {};
+struct b2c_layout {
+    b2c_ctx* ctx = nullptr;
+    b2c::LayoutView v;
+    void* d_blob = nullptr;
+};
 
 struct b2c_event {
     cudaEvent_t ev = nullptr;
@@ -94,7 +128,7 @@ struct b2c_event {
 namespace b2c {
 
 int set_err(b2c_ctx* ctx, int code, const char* what, cudaError_t e);
-int ws_reserve(b2c_ctx* ctx, DevBuf& b, size_t bytes);
+int ws_reserve(b2c_ctx* ctx, Lane& lane, DevBuf& b, size_t bytes);
 
 #define B2C_CUDA(ctx, call)                                         \
     do {                                                            \
@@ -102,27 +136,34 @@ int ws_reserve(b2c_ctx* ctx, DevBuf& b, size_t bytes);
         if (_e != cudaSuccess) return b2c::set_err((ctx), B2C_E_CUDA, #call, _e); \
     } while (0)
 
-// records an event on the ctx stream when profiling is on (start = even slots, stop = odd)
-void prof_mark(b2c_ctx* ctx, int which);
+// records an event on the main stream when profiling is on (start = even slots, stop = odd)
+void prof_mark(b2c_ctx* ctx, Lane& lane, int which);
 
-// kernels' host launchers (defined in the .cu files)
+// kernels' host launchers (defined in the .cu files); all work goes to lane.stream
 int crc_tables_init(b2c_ctx* ctx);
-int launch_crc32c(b2c_ctx* ctx, const Layout& L, const uint8_t* d_data, const uint32_t* d_init, uint32_t* d_crc);
-int launch_compress(b2c_ctx* ctx, const Layout& L, const uint8_t* d_in, uint8_t* d_out, uint64_t out_cap,
-                    uint64_t* d_out_off);
-int launch_ulen(b2c_ctx* ctx, const Layout& L, const uint8_t* d_in, uint32_t* d_ulen, int32_t* d_status);
-int launch_decompress(b2c_ctx* ctx, const Layout& in, const uint8_t* d_in, const Layout& out, uint8_t* d_out,
-                      uint32_t* d_ulen, int32_t* d_status);
+int launch_crc32c(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_data, const uint32_t* d_init,
+                  uint32_t* d_crc);
+int launch_compress(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint8_t* d_out,
+                    uint64_t out_cap, uint64_t* d_out_off);
+int launch_ulen(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint32_t* d_ulen,
+                int32_t* d_status);
+int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint8_t* d_in, const LayoutView& out,
+                      uint8_t* d_out, uint32_t* d_ulen, int32_t* d_status);
+// thread-per-message kernels for bodies <= 1 KiB (snappy_small.cu)
+int small_kernels_configure(b2c_ctx* ctx);
+int launch_compress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint8_t* scratch,
+                          uint32_t* d_frag_clen);
+int launch_decompress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint8_t* d_in,
+                            const LayoutView& out, uint8_t* d_out, uint32_t* d_ulen, int32_t* d_status);
 // exclusive scan of u32 values into u64 offsets: out[0]=0 ... out[n]=total
-int launch_scan_u32_u64(b2c_ctx* ctx, const uint32_t* d_vals, uint32_t n, uint64_t* d_out, void* d_tmp /* >= 8*(n/1024+2) */);
+int launch_scan_u32_u64(b2c_ctx* ctx, Lane& lane, const uint32_t* d_vals, uint32_t n, uint64_t* d_out,
+                        void* d_tmp /* >= 8*(n/1024+2) */);
 
 }  // namespace b2c
 
 // ---- device helpers ---------------------------------------------------------
 #ifdef __CUDACC__
 namespace b2c {
-
-__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 
 // 4 bytes at arbitrary byte address p (little endian), using aligned word loads.
 __device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {

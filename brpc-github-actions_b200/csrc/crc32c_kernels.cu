@@ -278,7 +278,8 @@ __global__ void crc32c_combine_kernel(const uint32_t* __restrict__ multi_list, u
     if (lane == 0) crc[m] = acc ^ 0xffffffffu;
 }
 
-int launch_crc32c(b2c_ctx* ctx, const Layout& L, const uint8_t* d_data, const uint32_t* d_init, uint32_t* d_crc) {
+int launch_crc32c(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_data, const uint32_t* d_init,
+                  uint32_t* d_crc) {
     if (L.n == 0) return B2C_OK;
     if (!ctx->crc_attr_done) {  // per device: a ctx is bound to one
         B2C_CUDA(ctx, cudaFuncSetAttribute(crc32c_chunks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -287,17 +288,17 @@ int launch_crc32c(b2c_ctx* ctx, const Layout& L, const uint8_t* d_data, const ui
     }
     uint32_t* d_rem = nullptr;
     if (L.n_multi) {
-        int rc = ws_reserve(ctx, ctx->ws_misc, (size_t)L.n_chunks * 4);
+        int rc = ws_reserve(ctx, lane, lane.ws_misc, (size_t)L.n_chunks * 4);
         if (rc) return rc;
-        d_rem = static_cast<uint32_t*>(ctx->ws_misc.p);
+        d_rem = static_cast<uint32_t*>(lane.ws_misc.p);
     }
     CrcParams P;
     P.data = d_data;
     P.off = L.d_off;
     P.len = L.d_len;
     P.init = d_init;
-    P.chunk_msg = L.all_single_chunk_uniform ? nullptr : L.d_chunk_msg;
-    P.chunk_first = L.all_single_chunk_uniform ? nullptr : L.d_chunk_first;
+    P.chunk_msg = L.d_chunk_msg;
+    P.chunk_first = L.d_chunk_first;
     P.tabA = ctx->d_crc_tabA;
     P.small = ctx->d_crc_small;
     P.rem = d_rem;
@@ -306,15 +307,15 @@ int launch_crc32c(b2c_ctx* ctx, const Layout& L, const uint8_t* d_data, const ui
     const uint32_t quads_per_cta = 256;
     uint32_t grid = (L.n_chunks + quads_per_cta - 1) / quads_per_cta;
     if (grid > (uint32_t)ctx->num_sms) grid = ctx->num_sms;
-    prof_mark(ctx, B2C_PROF_CRC32C);
-    crc32c_chunks_kernel<<<grid, 1024, sizeof(CrcSmem), ctx->stream>>>(P);
-    prof_mark(ctx, B2C_PROF_CRC32C);
+    prof_mark(ctx, lane, B2C_PROF_CRC32C);
+    crc32c_chunks_kernel<<<grid, 1024, sizeof(CrcSmem), lane.stream>>>(P);
+    prof_mark(ctx, lane, B2C_PROF_CRC32C);
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
     if (L.n_multi) {
         uint32_t blocks = (L.n_multi * 32 + 255) / 256;
-        crc32c_combine_kernel<<<blocks, 256, 0, ctx->stream>>>(L.d_multi_list, L.n_multi, L.d_chunk_first, L.d_len,
-                                                                d_rem, d_crc);
+        crc32c_combine_kernel<<<blocks, 256, 0, lane.stream>>>(L.d_multi_list, L.n_multi, L.d_chunk_first, L.d_len,
+                                                               d_rem, d_crc);
         ctx->launches++;
         B2C_CUDA(ctx, cudaGetLastError());
     }
@@ -361,8 +362,8 @@ static int noalloc_scratch(b2c_ctx* ctx, uint32_t** out) {
 extern "C" int b2c_crc32c_noalloc_dev(b2c_ctx* ctx, const b2c_layout* layout, const void* d_data,
                                       const uint32_t* d_init, uint32_t* d_crc) {
     using namespace b2c;
-    if (!ctx || !layout || !d_crc || (layout->payload && !d_data)) return B2C_E_ARG;
-    const Layout& L = *layout;
+    if (!ctx || !layout || !d_crc || (layout->v.payload && !d_data)) return B2C_E_ARG;
+    const LayoutView& L = layout->v;
     if (L.n_chunks > B2C_CRC32C_NOALLOC_MAX_CHUNKS)
         return set_err(ctx, B2C_E_CAPACITY,
                        "b2c_crc32c_noalloc_dev: layout has more than B2C_CRC32C_NOALLOC_MAX_CHUNKS (2^20) 4 KiB chunks; "
@@ -383,8 +384,8 @@ extern "C" int b2c_crc32c_noalloc_dev(b2c_ctx* ctx, const b2c_layout* layout, co
     P.off = L.d_off;
     P.len = L.d_len;
     P.init = d_init;
-    P.chunk_msg = L.all_single_chunk_uniform ? nullptr : L.d_chunk_msg;
-    P.chunk_first = L.all_single_chunk_uniform ? nullptr : L.d_chunk_first;
+    P.chunk_msg = L.d_chunk_msg;
+    P.chunk_first = L.d_chunk_first;
     P.tabA = ctx->d_crc_tabA;
     P.small = ctx->d_crc_small;
     P.rem = d_rem;  // slot c is written by chunk c before the combine kernel reads it
@@ -392,12 +393,12 @@ extern "C" int b2c_crc32c_noalloc_dev(b2c_ctx* ctx, const b2c_layout* layout, co
     P.n_chunks = L.n_chunks;
     uint32_t grid = (L.n_chunks + 255) / 256;
     if (grid > (uint32_t)ctx->num_sms) grid = ctx->num_sms;
-    crc32c_chunks_kernel<<<grid, 1024, sizeof(CrcSmem), ctx->stream>>>(P);
+    crc32c_chunks_kernel<<<grid, 1024, sizeof(CrcSmem), ctx->main.stream>>>(P);
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
     if (L.n_multi) {
         const uint32_t blocks = (L.n_multi * 32 + 255) / 256;
-        crc32c_combine_kernel<<<blocks, 256, 0, ctx->stream>>>(L.d_multi_list, L.n_multi, L.d_chunk_first, L.d_len,
+        crc32c_combine_kernel<<<blocks, 256, 0, ctx->main.stream>>>(L.d_multi_list, L.n_multi, L.d_chunk_first, L.d_len,
                                                                 d_rem, d_crc);
         ctx->launches++;
         B2C_CUDA(ctx, cudaGetLastError());

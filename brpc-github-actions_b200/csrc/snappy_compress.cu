@@ -221,10 +221,11 @@ struct CompressParams {
     const uint8_t* in;
     const uint64_t* off;
     const uint32_t* len;
-    const uint32_t* frag_list;   // fragments of this size class
-    const uint32_t* frag_msg;
-    const uint32_t* frag_first;
-    const uint64_t* frag_slot;
+    const uint32_t* frag_list;   // fragments of this size class (null: identity)
+    const uint32_t* frag_msg;    // null: fragment f belongs to message f
+    const uint32_t* frag_first;  // null: first fragment of message m is m
+    const uint64_t* frag_slot;   // null: slot = f * slot_stride
+    uint64_t slot_stride;
     uint8_t* scratch;
     uint32_t* frag_clen;
     uint32_t n_list;
@@ -238,9 +239,9 @@ __global__ void __launch_bounds__(256) snappy_compress_fragments_kernel(Compress
     const uint32_t w = blockIdx.x * (blockDim.x >> 5) + wib;
     if (w >= P.n_list) return;
     uint16_t* table = reinterpret_cast<uint16_t*>(smem_raw) + (size_t)wib * P.table_entries;
-    const uint32_t f = P.frag_list[w];
-    const uint32_t m = P.frag_msg[f];
-    const uint32_t k = f - P.frag_first[m];
+    const uint32_t f = P.frag_list ? P.frag_list[w] : w;
+    const uint32_t m = P.frag_msg ? P.frag_msg[f] : f;
+    const uint32_t k = P.frag_first ? f - P.frag_first[m] : 0u;
     const uint32_t mlen = P.len[m];
     const uint32_t n = min(kFragBytes, mlen - k * kFragBytes);
     // GetHashTable sizing, snappy.cc:253-256
@@ -252,7 +253,7 @@ __global__ void __launch_bounds__(256) snappy_compress_fragments_kernel(Compress
     }
     __syncwarp();
     const uint8_t* in = P.in + P.off[m] + (size_t)k * kFragBytes;
-    uint8_t* out = P.scratch + P.frag_slot[f];
+    uint8_t* out = P.scratch + (P.frag_slot ? P.frag_slot[f] : (uint64_t)f * P.slot_stride);
     const uint32_t clen = compress_fragment_warp(in, n, out, table, tsize, lane);
     if (lane == 0) P.frag_clen[f] = clen;
 }
@@ -265,7 +266,8 @@ __global__ void snappy_message_sizes_kernel(const uint32_t* __restrict__ len, co
     const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
     if (m >= n) return;
     uint32_t acc = varint_len(len[m]);
-    for (uint32_t f = frag_first[m]; f < frag_first[m + 1]; f++) {
+    const uint32_t f0 = frag_first ? frag_first[m] : m, f1 = frag_first ? frag_first[m + 1] : m + 1;
+    for (uint32_t f = f0; f < f1; f++) {
         frag_rel[f] = acc;
         acc += frag_clen[f];
     }
@@ -274,15 +276,17 @@ __global__ void snappy_message_sizes_kernel(const uint32_t* __restrict__ len, co
 
 // one warp per message preamble + one warp per fragment body
 __global__ void snappy_gather_kernel(const uint32_t* __restrict__ len, const uint32_t* __restrict__ frag_msg,
-                                     const uint64_t* __restrict__ frag_slot, const uint32_t* __restrict__ frag_clen,
+                                     const uint64_t* __restrict__ frag_slot, uint64_t slot_stride,
+                                     const uint32_t* __restrict__ frag_clen,
                                      const uint32_t* __restrict__ frag_rel, const uint64_t* __restrict__ out_off,
                                      const uint8_t* __restrict__ scratch, uint8_t* __restrict__ out, uint32_t n_frags,
                                      uint32_t n_msgs) {
     const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31;
     if (w < n_frags) {
-        const uint32_t m = frag_msg[w];
-        warp_copy_bytes(out + out_off[m] + frag_rel[w], scratch + frag_slot[w], frag_clen[w], lane);
+        const uint32_t m = frag_msg ? frag_msg[w] : w;
+        const uint64_t slot = frag_slot ? frag_slot[w] : (uint64_t)w * slot_stride;
+        warp_copy_bytes(out + out_off[m] + frag_rel[w], scratch + slot, frag_clen[w], lane);
     } else if (w - n_frags < (n_msgs + 31) / 32) {
         // preambles: one lane per message (Varint::Encode32, snappy-stubs-internal.h:349-375)
         const uint32_t m = (w - n_frags) * 32 + lane;
@@ -377,48 +381,52 @@ __global__ void scan_apply_kernel(const uint32_t* __restrict__ v, uint32_t n, co
     }
 }
 
-int launch_scan_u32_u64(b2c_ctx* ctx, const uint32_t* d_vals, uint32_t n, uint64_t* d_out, void* d_tmp) {
+int launch_scan_u32_u64(b2c_ctx* ctx, Lane& lane, const uint32_t* d_vals, uint32_t n, uint64_t* d_out, void* d_tmp) {
     if (n == 0) {
-        B2C_CUDA(ctx, cudaMemsetAsync(d_out, 0, 8, ctx->stream));
+        B2C_CUDA(ctx, cudaMemsetAsync(d_out, 0, 8, lane.stream));
         return B2C_OK;
     }
     const uint32_t nblocks = (n + kScanBlock - 1) / kScanBlock;
     uint64_t* sums = static_cast<uint64_t*>(d_tmp);
-    scan_block_sums_kernel<<<nblocks, 256, 0, ctx->stream>>>(d_vals, n, sums);
-    scan_sums_kernel<<<1, 1024, 0, ctx->stream>>>(sums, nblocks);
-    scan_apply_kernel<<<nblocks, 256, 0, ctx->stream>>>(d_vals, n, sums, d_out);
+    scan_block_sums_kernel<<<nblocks, 256, 0, lane.stream>>>(d_vals, n, sums);
+    scan_sums_kernel<<<1, 1024, 0, lane.stream>>>(sums, nblocks);
+    scan_apply_kernel<<<nblocks, 256, 0, lane.stream>>>(d_vals, n, sums, d_out);
     ctx->launches += 3;
     B2C_CUDA(ctx, cudaGetLastError());
     return B2C_OK;
 }
 
 // ---------------------------------------------------------------------------
-int launch_compress(b2c_ctx* ctx, const Layout& L, const uint8_t* d_in, uint8_t* d_out, uint64_t out_cap,
-                    uint64_t* d_out_off) {
+int launch_compress(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint8_t* d_out,
+                    uint64_t out_cap, uint64_t* d_out_off) {
     if (out_cap < L.max_comp) return set_err(ctx, B2C_E_CAPACITY, "compress output capacity", cudaSuccess);
     if (L.n == 0) {
-        B2C_CUDA(ctx, cudaMemsetAsync(d_out_off, 0, 8, ctx->stream));
+        B2C_CUDA(ctx, cudaMemsetAsync(d_out_off, 0, 8, lane.stream));
         return B2C_OK;
     }
-    int rc = ws_reserve(ctx, ctx->ws_frag, L.frag_scratch_bytes + 64);
+    int rc = ws_reserve(ctx, lane, lane.ws_frag, L.frag_scratch_bytes + 64);
     if (rc) return rc;
     // misc workspace: frag_clen[F] | frag_rel[F] | msg_clen[n] | scan tmp
     const size_t F = L.n_frags, n = L.n;
     const size_t scan_tmp = ((n + kScanBlock - 1) / kScanBlock + 2) * 8;
     const size_t need = (2 * F + n) * 4 + 16 + scan_tmp;
-    rc = ws_reserve(ctx, ctx->ws_misc, need);
+    rc = ws_reserve(ctx, lane, lane.ws_misc, need);
     if (rc) return rc;
-    uint32_t* d_frag_clen = static_cast<uint32_t*>(ctx->ws_misc.p);
+    uint32_t* d_frag_clen = static_cast<uint32_t*>(lane.ws_misc.p);
     uint32_t* d_frag_rel = d_frag_clen + F;
     uint32_t* d_msg_clen = d_frag_rel + F;
     void* d_scan_tmp = reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(d_msg_clen + n) + 15) & ~uintptr_t(15));
-    uint8_t* scratch = static_cast<uint8_t*>(ctx->ws_frag.p);
+    uint8_t* scratch = static_cast<uint8_t*>(lane.ws_frag.p);
 
     static const uint32_t class_entries[3] = {1024, 4096, 16384};
     static const uint32_t class_warps[3] = {8, 4, 1};
-    prof_mark(ctx, B2C_PROF_COMPRESS);
+    prof_mark(ctx, lane, B2C_PROF_COMPRESS);
     for (int c = 0; c < 3; c++) {
         if (!L.n_class[c]) continue;
+        if (c == 0 && ctx->small_kernels) {  // bodies <= 1 KiB: one lane per fragment
+            if ((rc = launch_compress_small(ctx, lane, L, d_in, scratch, d_frag_clen))) return rc;
+            continue;
+        }
         CompressParams P;
         P.in = d_in;
         P.off = L.d_off;
@@ -427,6 +435,7 @@ int launch_compress(b2c_ctx* ctx, const Layout& L, const uint8_t* d_in, uint8_t*
         P.frag_msg = L.d_frag_msg;
         P.frag_first = L.d_frag_first;
         P.frag_slot = L.d_frag_slot;
+        P.slot_stride = L.slot_stride;
         P.scratch = scratch;
         P.frag_clen = d_frag_clen;
         P.n_list = L.n_class[c];
@@ -434,23 +443,24 @@ int launch_compress(b2c_ctx* ctx, const Layout& L, const uint8_t* d_in, uint8_t*
         const uint32_t wpb = class_warps[c];
         const uint32_t blocks = (P.n_list + wpb - 1) / wpb;
         const size_t smem = (size_t)wpb * class_entries[c] * 2;
-        snappy_compress_fragments_kernel<<<blocks, wpb * 32, smem, ctx->stream>>>(P);
+        snappy_compress_fragments_kernel<<<blocks, wpb * 32, smem, lane.stream>>>(P);
         ctx->launches++;
         B2C_CUDA(ctx, cudaGetLastError());
     }
-    prof_mark(ctx, B2C_PROF_COMPRESS);
-    prof_mark(ctx, B2C_PROF_PACK);
-    snappy_message_sizes_kernel<<<(L.n + 255) / 256, 256, 0, ctx->stream>>>(L.d_len, L.d_frag_first, d_frag_clen,
-                                                                             d_frag_rel, d_msg_clen, L.n);
+    prof_mark(ctx, lane, B2C_PROF_COMPRESS);
+    prof_mark(ctx, lane, B2C_PROF_PACK);
+    snappy_message_sizes_kernel<<<(L.n + 255) / 256, 256, 0, lane.stream>>>(L.d_len, L.d_frag_first, d_frag_clen,
+                                                                            d_frag_rel, d_msg_clen, L.n);
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
-    rc = launch_scan_u32_u64(ctx, d_msg_clen, L.n, d_out_off, d_scan_tmp);
+    rc = launch_scan_u32_u64(ctx, lane, d_msg_clen, L.n, d_out_off, d_scan_tmp);
     if (rc) return rc;
     const uint64_t warps = (uint64_t)L.n_frags + (L.n + 31) / 32;
     const uint32_t blocks = (uint32_t)((warps * 32 + 255) / 256);
-    snappy_gather_kernel<<<blocks, 256, 0, ctx->stream>>>(L.d_len, L.d_frag_msg, L.d_frag_slot, d_frag_clen,
-                                                          d_frag_rel, d_out_off, scratch, d_out, L.n_frags, L.n);
-    prof_mark(ctx, B2C_PROF_PACK);
+    snappy_gather_kernel<<<blocks, 256, 0, lane.stream>>>(L.d_len, L.d_frag_msg, L.d_frag_slot, L.slot_stride,
+                                                         d_frag_clen, d_frag_rel, d_out_off, scratch, d_out,
+                                                         L.n_frags, L.n);
+    prof_mark(ctx, lane, B2C_PROF_PACK);
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
     return B2C_OK;

@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(256) snappy_decompress_kernel(DecompressParams
     const uint32_t wib = threadIdx.x >> 5;
     const uint32_t w = blockIdx.x * (blockDim.x >> 5) + wib;
     if (w >= P.n_list) return;
-    const uint32_t m = P.list[w];
+    const uint32_t m = P.list ? P.list[w] : w;
     const uint8_t* in = P.in + P.in_off[m];
     const uint32_t n = P.in_len[m];
     uint8_t* gout = P.out + P.out_off[m];
@@ -203,23 +203,29 @@ __global__ void snappy_ulen_kernel(const uint8_t* __restrict__ in, const uint64_
     if (status) status[m] = k ? B2C_OK : B2C_CORRUPT;
 }
 
-int launch_ulen(b2c_ctx* ctx, const Layout& L, const uint8_t* d_in, uint32_t* d_ulen, int32_t* d_status) {
+int launch_ulen(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint32_t* d_ulen,
+                int32_t* d_status) {
     if (L.n == 0) return B2C_OK;
-    snappy_ulen_kernel<<<(L.n + 255) / 256, 256, 0, ctx->stream>>>(d_in, L.d_off, L.d_len, L.n, d_ulen, d_status);
+    snappy_ulen_kernel<<<(L.n + 255) / 256, 256, 0, lane.stream>>>(d_in, L.d_off, L.d_len, L.n, d_ulen, d_status);
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
     return B2C_OK;
 }
 
-int launch_decompress(b2c_ctx* ctx, const Layout& in, const uint8_t* d_in, const Layout& out, uint8_t* d_out,
-                      uint32_t* d_ulen, int32_t* d_status) {
+int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint8_t* d_in, const LayoutView& out,
+                      uint8_t* d_out, uint32_t* d_ulen, int32_t* d_status) {
     if (in.n != out.n) return set_err(ctx, B2C_E_ARG, "decompress: layouts differ in message count", cudaSuccess);
     if (in.n == 0) return B2C_OK;
-    static const uint32_t class_smem[3] = {2048, 8192, 0};
+    static const uint32_t class_smem[3] = {1024, 8192, 0};
     static const uint32_t class_warps[3] = {8, 4, 8};
-    prof_mark(ctx, B2C_PROF_DECOMPRESS);
+    prof_mark(ctx, lane, B2C_PROF_DECOMPRESS);
     for (int c = 0; c < 3; c++) {
         if (!out.n_dclass[c]) continue;
+        if (c == 0 && ctx->small_kernels) {  // slots <= 1 KiB: one lane per stream
+            int rc = launch_decompress_small(ctx, lane, in, d_in, out, d_out, d_ulen, d_status);
+            if (rc) return rc;
+            continue;
+        }
         DecompressParams P;
         P.in = d_in;
         P.in_off = in.d_off;
@@ -234,11 +240,11 @@ int launch_decompress(b2c_ctx* ctx, const Layout& in, const uint8_t* d_in, const
         P.smem_per_warp = class_smem[c];
         const uint32_t wpb = class_warps[c];
         const uint32_t blocks = (P.n_list + wpb - 1) / wpb;
-        snappy_decompress_kernel<<<blocks, wpb * 32, (size_t)wpb * class_smem[c], ctx->stream>>>(P);
+        snappy_decompress_kernel<<<blocks, wpb * 32, (size_t)wpb * class_smem[c], lane.stream>>>(P);
         ctx->launches++;
         B2C_CUDA(ctx, cudaGetLastError());
     }
-    prof_mark(ctx, B2C_PROF_DECOMPRESS);
+    prof_mark(ctx, lane, B2C_PROF_DECOMPRESS);
     return B2C_OK;
 }
 

@@ -276,6 +276,11 @@ def test_e2e_iovec_batches(codec, cpu):
         cap = int(sum(32 + int(l) + int(l) // 6 + 5 for l in ln))
         out = np.empty(cap, dtype=np.uint8)
         out_off = codec.compress_batch(segs, sb, out)
+        # same call with a page-locked result buffer (the library then DMAs straight into it)
+        out_p = codec.pinned(cap)
+        out_off_p = codec.compress_batch(segs, sb, out_p)
+        assert (out_off_p == out_off).all()
+        assert out_p[:int(out_off[-1])].tobytes() == out[:int(out_off[-1])].tobytes()
         w_out, w_off, w_len, _ = cpu.batch_compress(arena, off, ln, threads=8)
         assert (np.diff(out_off).astype(np.uint32) == w_len).all()
         for i in range(0, len(ln), max(1, len(ln) // 500)):
@@ -286,6 +291,10 @@ def test_e2e_iovec_batches(codec, cpu):
         back = np.empty(int(ln.astype(np.uint64).sum()) + 64, dtype=np.uint8)
         b_off, status = codec.decompress_batch(csegs, csb, back)
         assert (status == 0).all()
+        back_p = codec.pinned(len(back))
+        b_off_p, status_p = codec.decompress_batch(csegs, csb, back_p)
+        assert (b_off_p == b_off).all() and (status_p == 0).all()
+        assert back_p[:int(b_off[-1])].tobytes() == back[:int(b_off[-1])].tobytes()
         assert (np.diff(b_off).astype(np.uint32) == ln).all()
         for i in range(0, len(ln), max(1, len(ln) // 500)):
             a, b = int(off[i]), int(off[i]) + int(ln[i])
