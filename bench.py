@@ -226,10 +226,7 @@ def run_ours(args, rank, local_rank, world):
     codec.prof_enable(False)
     clocks = sampler.stop() if sampler else None
     if dist is not None:
-        import torch
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+        ms = brpc_b200.sharding.max_over_ranks(ms, device="cuda")  # device time, max over ranks
         dist.barrier()
 
     # ---- end to end through the host-buffer ABI (iovec block lists, PCIe inside) ----
@@ -272,10 +269,7 @@ def run_ours(args, rank, local_rank, world):
         e2e_step()
     e2e_s = time.perf_counter() - t0
     if dist is not None:
-        import torch
-        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
+        e2e_s = brpc_b200.sharding.max_over_ranks(e2e_s, device="cuda")
     assert h_back[:payload].tobytes()[:4096] == b"".join(
         arena[int(off[i]):int(off[i]) + int(ln[i])].tobytes() for i in range(4))
 

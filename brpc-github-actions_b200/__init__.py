@@ -7,3 +7,4 @@ around that ABI.
 from .nvcc_build import build  # noqa: F401
 from .capi import (B2CError, Codec, CORRUPT, OK, TOO_SMALL, SYMBOLS, lib_path, load,  # noqa: F401
                    make_iovecs)
+from . import sharding  # noqa: F401,E402

@@ -9,6 +9,7 @@
 // before that is being copied out, over kPipeLanes streams with private
 // workspaces (replaces the per-fragment gather memcpy of snappy.cc:901-921 and
 // the sink copies of src/butil/iobuf.cpp:2066-2093).
+#include <emmintrin.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -55,20 +56,19 @@ int ws_reserve(b2c_ctx* ctx, Lane& lane, DevBuf& b, size_t bytes) {
     return B2C_OK;
 }
 
-static int pin_reserve(b2c_ctx* ctx, Lane& lane, PinBuf& b, size_t bytes) {
+// Grow-only pinned buffer; the first `keep` bytes survive a growth.
+static int pin_reserve(b2c_ctx* ctx, Lane& lane, PinBuf& b, size_t bytes, size_t keep = 0) {
     if (bytes <= b.cap) return B2C_OK;
+    size_t want = bytes + bytes / 8 + 4096;
+    void* fresh = nullptr;
+    cudaError_t e = cudaHostAlloc(&fresh, want, cudaHostAllocDefault);
+    if (e != cudaSuccess) return set_err(ctx, B2C_E_NOMEM, "cudaHostAlloc(staging)", e);
     if (b.p) {
         B2C_CUDA(ctx, cudaStreamSynchronize(lane.stream));
+        if (keep) memcpy(fresh, b.p, std::min(keep, b.cap));
         B2C_CUDA(ctx, cudaFreeHost(b.p));
-        b.p = nullptr;
-        b.cap = 0;
     }
-    size_t want = bytes + bytes / 8 + 4096;
-    cudaError_t e = cudaHostAlloc(&b.p, want, cudaHostAllocDefault);
-    if (e != cudaSuccess) {
-        b.p = nullptr;
-        return set_err(ctx, B2C_E_NOMEM, "cudaHostAlloc(staging)", e);
-    }
+    b.p = fresh;
     b.cap = want;
     return B2C_OK;
 }
@@ -398,6 +398,7 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     if (const char* s = getenv("B2C_SLAB_MB")) ctx->slab_bytes = std::max<size_t>(1, (size_t)atol(s)) << 20;
     if (const char* s = getenv("B2C_HOST_THREADS")) ctx->host_threads = (unsigned)std::max(1L, atol(s));
     if (const char* s = getenv("B2C_TRACE")) ctx->trace = atoi(s) != 0;
+    if (const char* s = getenv("B2C_NT_GATHER")) ctx->nt_gather = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL_KERNELS")) ctx->small_kernels = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL_LPW_C")) ctx->small_lpw_compress = atoi(s);
     if (const char* s = getenv("B2C_SMALL_LPW_D")) ctx->small_lpw_decompress = atoi(s);
@@ -723,19 +724,68 @@ int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, u
     return B2C_OK;
 }
 
-// memcpy every segment of the slab's messages into pinned staging.
+// Copy with non-temporal stores: staging is written once by the CPU and then only read by the
+// DMA engine, so bypassing the cache saves the read-for-ownership of every destination line.
+inline void copy_stream(uint8_t* dst, const uint8_t* src, size_t n) {
+    if (n < 256) {
+        memcpy(dst, src, n);
+        return;
+    }
+    // whole 64-byte destination lines only: a partially written write-combining buffer is costly
+    size_t head = (64 - (reinterpret_cast<uintptr_t>(dst) & 63)) & 63;
+    if (head) {
+        memcpy(dst, src, head);
+        dst += head;
+        src += head;
+        n -= head;
+    }
+    size_t blocks = n / 64;
+    for (size_t i = 0; i < blocks; i++) {
+        __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src));
+        __m128i b = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + 16));
+        __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + 32));
+        __m128i d = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + 48));
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst), a);
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst + 16), b);
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst + 32), c);
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst + 48), d);
+        src += 64;
+        dst += 64;
+    }
+    n -= blocks * 64;
+    if (n) memcpy(dst, src, n);
+}
+
+// memcpy every segment of the slab's messages into pinned staging.  When `caps` is given the
+// messages are snappy streams: the thread that just copied a stream also reads its (lenient)
+// preamble while the bytes are still in its cache and records the plausible output size
+// (0 = malformed or impossible claim; a stream cannot expand more than 64/3 times, snappy.cc:867).
 void gather_slab(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, const BatchPlan& p, const Slab& s,
-                 uint8_t* stage) {
+                 uint8_t* stage, uint32_t* caps = nullptr) {
     const uint32_t cnt = s.m1 - s.m0;
+    const bool stream = ctx->nt_gather;
     pool(ctx).run(threads_for(s.bytes), [&](unsigned t, unsigned T) {
         uint32_t lo = s.m0 + (uint32_t)((uint64_t)cnt * t / T), hi = s.m0 + (uint32_t)((uint64_t)cnt * (t + 1) / T);
         for (uint32_t i = lo; i < hi; i++) {
             uint8_t* d = stage + p.off[i];
+            if (caps) {
+                uint8_t head[5];
+                size_t got = 0;
+                for (uint32_t q = seg_begin[i]; q < seg_begin[i + 1] && got < 5; q++)
+                    for (size_t j = 0; j < segs[q].iov_len && got < 5; j++)
+                        head[got++] = static_cast<const uint8_t*>(segs[q].iov_base)[j];
+                uint32_t ulen = 0;
+                const int kk = b2c_snappy_read_preamble(head, got, &ulen);
+                const bool plausible = kk > 0 && (uint64_t)ulen <= ((uint64_t)p.len[i] * 64) / 3 + 64;
+                caps[i - s.m0] = plausible ? ulen : 0;
+            }
             for (uint32_t q = seg_begin[i]; q < seg_begin[i + 1]; q++) {
-                memcpy(d, segs[q].iov_base, segs[q].iov_len);
+                if (stream) copy_stream(d, static_cast<const uint8_t*>(segs[q].iov_base), segs[q].iov_len);
+                else memcpy(d, segs[q].iov_base, segs[q].iov_len);
                 d += segs[q].iov_len;
             }
         }
+        if (stream) _mm_sfence();
     });
 }
 
@@ -974,23 +1024,11 @@ int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint3
         if ((rc = pin_reserve(ctx, lane, lane.h_in, align_up(s.bytes, 256) + lin.blob_bytes + (size_t)cnt * 16 + 4096)))
             return rc;
         uint8_t* stage = static_cast<uint8_t*>(lane.h_in.p);
-        TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, stage));
-        // Output slots from the (lenient) preambles.  A stream cannot expand by more than 64/3
-        // (a 3-byte copy yields at most 64 bytes), so a larger claim is malformed: the reference
-        // would run out of input before producing it (snappy.cc:867).
-        auto tl = Clock::now();
         if (o_off.size() < cnt) o_off.resize(cnt);
         if (o_cap.size() < cnt) o_cap.resize(cnt);
-        pool(ctx).run(threads_for((uint64_t)cnt * 64), [&](unsigned t, unsigned T) {
-            uint32_t lo = (uint32_t)((uint64_t)cnt * t / T), hi = (uint32_t)((uint64_t)cnt * (t + 1) / T);
-            for (uint32_t i = lo; i < hi; i++) {
-                uint32_t ulen = 0;
-                const uint32_t clen = bp.len[s.m0 + i];
-                int kk = b2c_snappy_read_preamble(stage + bp.off[s.m0 + i], clen, &ulen);
-                bool plausible = kk > 0 && (uint64_t)ulen <= ((uint64_t)clen * 64) / 3 + 64;
-                o_cap[i] = plausible ? ulen : 0;
-            }
-        });
+        // output slot sizes come from the (lenient) preambles, read by the gathering threads
+        TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, stage, o_cap.data()));
+        auto tl = Clock::now();
         uint64_t pos = 0;
         for (uint32_t i = 0; i < cnt; i++) {
             o_off[i] = pos;
@@ -1006,7 +1044,7 @@ int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint3
         const size_t blob_in_at = align_up(s.bytes, 256);
         const size_t blob_out_at = align_up(blob_in_at + lin.blob_bytes, 256);
         const size_t in_bytes = blob_out_at + lout.blob_bytes;
-        if ((rc = pin_reserve(ctx, lane, lane.h_in, in_bytes + 64))) return rc;  // (already large enough in practice)
+        if ((rc = pin_reserve(ctx, lane, lane.h_in, in_bytes + 64, s.bytes))) return rc;  // keeps the gathered slab
         stage = static_cast<uint8_t*>(lane.h_in.p);
         lin.fill(stage + blob_in_at);
         lout.fill(stage + blob_out_at);

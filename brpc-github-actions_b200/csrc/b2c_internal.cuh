@@ -113,6 +113,7 @@ struct b2c_ctx {
     size_t slab_bytes = 32u << 20;
     unsigned host_threads = 0;
     bool trace = false;
+    bool nt_gather = true;  // B2C_NT_GATHER=0: plain memcpy into staging
 };
 
 struct b2c_layout {

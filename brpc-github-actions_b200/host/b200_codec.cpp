@@ -1,0 +1,203 @@
+// b200_codec.cpp — see b200_codec.hpp.  Thin C++ over the C ABI; all arithmetic is in libb2c.so.
+#include "b200_codec.hpp"
+
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <stdexcept>
+
+namespace b200 {
+
+namespace {
+[[noreturn]] void fail(b2c_ctx* ctx, const char* what, int rc) {
+    std::string msg = std::string("b200 codec: ") + what + " failed with " + std::to_string(rc);
+    if (ctx) msg += std::string(": ") + b2c_last_error(ctx);
+    throw std::runtime_error(msg);
+}
+
+struct Flat {  // segs + seg_begin for a batch of block lists
+    std::vector<b2c_iovec> segs;
+    std::vector<uint32_t> begin;
+    explicit Flat(const std::vector<BlockList>& in) {
+        begin.reserve(in.size() + 1);
+        begin.push_back(0);
+        for (const BlockList& b : in) {
+            segs.insert(segs.end(), b.begin(), b.end());
+            begin.push_back((uint32_t)segs.size());
+        }
+    }
+};
+
+size_t total_bytes(const BlockList& b) {
+    size_t n = 0;
+    for (const b2c_iovec& v : b) n += v.iov_len;
+    return n;
+}
+}  // namespace
+
+Context::Context(int device) : ctx_(nullptr) {
+    int rc = b2c_ctx_create(device, &ctx_);
+    if (rc != B2C_OK) fail(nullptr, "b2c_ctx_create (no usable CUDA device? there is no CPU fallback)", rc);
+}
+Context::~Context() { b2c_ctx_destroy(ctx_); }
+
+Context& Context::local() {
+    static thread_local Context* c = nullptr;
+    if (!c) {
+        const char* d = getenv("B200_DEVICE");
+        c = new Context(d ? atoi(d) : 0);
+    }
+    return *c;
+}
+
+namespace policy {
+
+void SnappyCompressBatch(const std::vector<BlockList>& in, std::vector<std::string>* out) {
+    b2c_ctx* ctx = Context::local().get();
+    const uint32_t n = (uint32_t)in.size();
+    out->assign(n, std::string());
+    if (!n) return;
+    Flat f(in);
+    uint64_t cap = 0;
+    for (const BlockList& b : in) cap += b2c_snappy_max_compressed_length(total_bytes(b)) + 5;
+    std::vector<char> buf(cap);
+    std::vector<uint64_t> off(n + 1);
+    int rc = b2c_snappy_compress_batch(ctx, f.segs.data(), f.begin.data(), n, buf.data(), cap, off.data());
+    if (rc != B2C_OK) fail(ctx, "b2c_snappy_compress_batch", rc);
+    for (uint32_t i = 0; i < n; i++) (*out)[i].assign(buf.data() + off[i], off[i + 1] - off[i]);
+}
+
+void SnappyDecompressBatch(const std::vector<BlockList>& in, std::vector<std::string>* out, std::vector<bool>* ok) {
+    b2c_ctx* ctx = Context::local().get();
+    const uint32_t n = (uint32_t)in.size();
+    out->assign(n, std::string());
+    ok->assign(n, false);
+    if (!n) return;
+    Flat f(in);
+    // capacity: a stream expands at most 64/3 times; the library sizes every slot from its preamble
+    uint64_t cap = 64;
+    for (const BlockList& b : in) cap += total_bytes(b) * 64 / 3 + 64;
+    // sum of the claimed lengths is usually far smaller: read the preambles first
+    uint64_t claimed = 0;
+    for (const BlockList& b : in) {
+        uint8_t head[5];
+        size_t got = 0;
+        for (const b2c_iovec& v : b)
+            for (size_t j = 0; j < v.iov_len && got < 5; j++) head[got++] = static_cast<const uint8_t*>(v.iov_base)[j];
+        uint32_t ulen = 0;
+        if (b2c_snappy_read_preamble(head, got, &ulen)) claimed += ulen;
+    }
+    cap = std::min<uint64_t>(cap, claimed + 64);
+    std::vector<char> buf(cap);
+    std::vector<uint64_t> off(n + 1);
+    std::vector<int32_t> st(n);
+    int rc = b2c_snappy_decompress_batch(ctx, f.segs.data(), f.begin.data(), n, buf.data(), cap, off.data(), st.data());
+    if (rc != B2C_OK) fail(ctx, "b2c_snappy_decompress_batch", rc);
+    for (uint32_t i = 0; i < n; i++) {
+        (*ok)[i] = st[i] == B2C_OK;
+        if ((*ok)[i]) (*out)[i].assign(buf.data() + off[i], off[i + 1] - off[i]);
+    }
+}
+
+void Crc32cBatch(const std::vector<BlockList>& in, const uint32_t* init, std::vector<uint32_t>* crc) {
+    b2c_ctx* ctx = Context::local().get();
+    const uint32_t n = (uint32_t)in.size();
+    crc->assign(n, 0);
+    if (!n) return;
+    Flat f(in);
+    int rc = b2c_crc32c_batch(ctx, f.segs.data(), f.begin.data(), n, init, crc->data());
+    if (rc != B2C_OK) fail(ctx, "b2c_crc32c_batch", rc);
+}
+
+bool SnappyCompress(const BlockList& in, std::string* out) {
+    std::vector<std::string> r;
+    SnappyCompressBatch({in}, &r);
+    out->append(r[0]);
+    return !r[0].empty();  // the reference returns `written`, which is never 0 (snappy_compress.cpp:51-55)
+}
+
+bool SnappyDecompress(const BlockList& in, std::string* out) {
+    std::vector<std::string> r;
+    std::vector<bool> ok;
+    SnappyDecompressBatch({in}, &r, &ok);
+    if (!ok[0]) return false;
+    out->append(r[0]);
+    return true;
+}
+
+}  // namespace policy
+
+namespace snappy {
+
+size_t MaxCompressedLength(size_t n) { return b2c_snappy_max_compressed_length(n); }
+
+bool GetUncompressedLength(const char* compressed, size_t n, size_t* result) {
+    uint32_t v = 0;
+    if (!b2c_snappy_get_uncompressed_length(compressed, n, &v)) return false;
+    *result = v;
+    return true;
+}
+
+void RawCompress(const char* input, size_t n, char* compressed, size_t* compressed_length) {
+    b2c_ctx* ctx = Context::local().get();
+    b2c_iovec seg = {input, n};
+    const uint32_t begin[2] = {0, 1};
+    uint64_t off[2] = {0, 0};
+    int rc = b2c_snappy_compress_batch(ctx, &seg, begin, 1, compressed, MaxCompressedLength(n) + 5, off);
+    if (rc != B2C_OK) fail(ctx, "b2c_snappy_compress_batch", rc);
+    *compressed_length = off[1];
+}
+
+size_t Compress(const char* input, size_t n, std::string* output) {
+    std::vector<char> buf(MaxCompressedLength(n) + 5);
+    size_t clen = 0;
+    RawCompress(input, n, buf.data(), &clen);
+    output->assign(buf.data(), clen);
+    return clen;
+}
+
+bool RawUncompress(const char* compressed, size_t n, char* uncompressed) {
+    b2c_ctx* ctx = Context::local().get();
+    uint32_t ulen = 0;
+    if (!b2c_snappy_read_preamble(compressed, n, &ulen)) return false;  // lenient, as RawUncompress(Source*) does
+    b2c_iovec seg = {compressed, n};
+    const uint32_t begin[2] = {0, 1};
+    uint64_t off[2];
+    int32_t st = 0;
+    int rc = b2c_snappy_decompress_batch(ctx, &seg, begin, 1, uncompressed, ulen, off, &st);
+    if (rc != B2C_OK) fail(ctx, "b2c_snappy_decompress_batch", rc);
+    return st == B2C_OK;
+}
+
+bool Uncompress(const char* compressed, size_t n, std::string* uncompressed) {
+    size_t ulen = 0;
+    if (!GetUncompressedLength(compressed, n, &ulen)) return false;  // strict, snappy.cc:1227-1239
+    if (ulen > (uint64_t)n * 64 / 3 + 64) return false;              // cannot be a valid stream (see b2c_api.cu)
+    uncompressed->resize(ulen);
+    return RawUncompress(compressed, n, ulen ? &(*uncompressed)[0] : nullptr);
+}
+
+bool IsValidCompressedBuffer(const char* compressed, size_t n) {
+    uint32_t ulen = 0;
+    if (!b2c_snappy_read_preamble(compressed, n, &ulen)) return false;
+    if (ulen > (uint64_t)n * 64 / 3 + 64) return false;
+    std::vector<char> tmp(ulen ? ulen : 1);
+    return RawUncompress(compressed, n, tmp.data());
+}
+
+}  // namespace snappy
+
+namespace crc32c {
+uint32_t Extend(uint32_t init_crc, const char* data, size_t n) {
+    b2c_ctx* ctx = Context::local().get();
+    b2c_iovec seg = {data, n};
+    const uint32_t begin[2] = {0, 1};
+    uint32_t crc = 0;
+    int rc = b2c_crc32c_batch(ctx, &seg, begin, 1, &init_crc, &crc);
+    if (rc != B2C_OK) fail(ctx, "b2c_crc32c_batch", rc);
+    return crc;
+}
+}  // namespace crc32c
+
+}  // namespace b200

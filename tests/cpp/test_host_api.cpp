@@ -1,0 +1,199 @@
+// test_host_api.cpp — the reference's own unit tests for this path, re-pointed at the GPU
+// codec through the C++ host mirror (b200_codec.hpp):
+//   test/crc32c_unittest.cc:18-70                      -> crc_*
+//   test/brpc_snappy_compress_unittest.cpp:97-104      -> snappy_iobuf
+//   test/brpc_snappy_compress_unittest.cpp:137-164     -> snappy_test
+//   test/brpc_snappy_compress_unittest.cpp:166-234     -> throughput shapes (round trip + bytes vs oracle)
+//   test/brpc_snappy_compress_unittest.cpp:236-255     -> mass_snappy_iobuf
+// plus byte-for-byte comparison of every compressed stream with the CPU oracle.
+// Exit code 0 = all passed.  (TEST INFRASTRUCTURE: links oracle/libb2oracle.so as the checker.)
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "b200_codec.hpp"
+#include "b2o.h"
+
+static int g_fail = 0;
+#define CHECK(cond)                                                         \
+    do {                                                                    \
+        if (!(cond)) {                                                      \
+            fprintf(stderr, "FAIL %s:%d: %s\n", __FILE__, __LINE__, #cond); \
+            g_fail++;                                                       \
+        }                                                                   \
+    } while (0)
+
+using b200::BlockList;
+
+static BlockList blocks_of(const std::string& s, size_t block) {
+    BlockList b;
+    for (size_t p = 0; p < s.size(); p += block) b.push_back({s.data() + p, std::min(block, s.size() - p)});
+    if (s.empty()) b.push_back({s.data(), 0});
+    return b;
+}
+
+static std::string oracle_compress(const std::string& s) {
+    std::string z(b2o_snappy_max_compressed_length(s.size()), '\0');
+    size_t k = b2o_snappy_compress(reinterpret_cast<const uint8_t*>(s.data()), s.size(), reinterpret_cast<uint8_t*>(&z[0]));
+    z.resize(k);
+    return z;
+}
+
+static std::string pattern_az09(int len) {  // brpc_snappy_compress_unittest.cpp:110-117
+    std::string t;
+    for (int j = 0; j < len;) {
+        for (int i = 0; i < 26 && j < len; i++, j++) t.push_back('a' + i);
+        for (int i = 0; i < 10 && j < len; i++, j++) t.push_back('0' + i);
+    }
+    return t;
+}
+
+static void crc_standard_results() {  // CRC.StandardResults, rfc3720 section B.4
+    using namespace b200::crc32c;
+    char buf[32];
+    memset(buf, 0, sizeof(buf));
+    CHECK(0x8a9136aaU == Value(buf, sizeof(buf)));
+    memset(buf, 0xff, sizeof(buf));
+    CHECK(0x62a8ab43U == Value(buf, sizeof(buf)));
+    for (int i = 0; i < 32; i++) buf[i] = i;
+    CHECK(0x46dd794eU == Value(buf, sizeof(buf)));
+    for (int i = 0; i < 32; i++) buf[i] = 31 - i;
+    CHECK(0x113fdb5cU == Value(buf, sizeof(buf)));
+    unsigned char data[48] = {
+        0x01, 0xc0, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00,
+        0x14, 0x00, 0x00, 0x00, 0x00, 0x00, 0x04, 0x00, 0x00, 0x00, 0x00, 0x14, 0x00, 0x00, 0x00, 0x18,
+        0x28, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x02, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00,
+    };
+    CHECK(0xd9963a56 == Value(reinterpret_cast<char*>(data), sizeof(data)));
+}
+
+static void crc_values_extend_mask() {  // CRC.Values / Extend / Mask
+    using namespace b200::crc32c;
+    CHECK(Value("a", 1) != Value("foo", 3));
+    CHECK(Value("hello world", 11) == Extend(Value("hello ", 6), "world", 5));
+    uint32_t crc = Value("foo", 3);
+    CHECK(crc != Mask(crc));
+    CHECK(crc != Mask(Mask(crc)));
+    CHECK(crc == Unmask(Mask(crc)));
+    CHECK(crc == Unmask(Unmask(Mask(Mask(crc)))));
+}
+
+static void snappy_iobuf() {  // test_compress_method.snappy_iobuf
+    const std::string test = "this is a test";
+    std::string output_buf, check_buf;
+    CHECK(b200::policy::SnappyCompress(blocks_of(test, 8192), &output_buf));
+    CHECK(output_buf == oracle_compress(test));
+    CHECK(b200::policy::SnappyDecompress(blocks_of(output_buf, 8192), &check_buf));
+    CHECK(check_buf == test);
+}
+
+static void snappy_test() {  // test_compress_method.snappy_test: string API, concatenated streams
+    std::string text = pattern_az09(200);
+    std::string output, append_string;
+    CHECK(b200::snappy::Compress(text.data(), text.size(), &output));
+    CHECK(output == oracle_compress(text));
+    size_t com_len1 = output.size();
+    const char* s_text = "123456";
+    CHECK(b200::snappy::Compress(s_text, strlen(s_text), &append_string));
+    output.append(append_string);
+    std::string uncompress_str, uncompress_str_t;
+    CHECK(b200::snappy::Uncompress(output.data(), com_len1, &uncompress_str));
+    CHECK(uncompress_str == text);
+    CHECK(b200::snappy::Uncompress(append_string.data(), append_string.size(), &uncompress_str_t));
+    CHECK(uncompress_str_t == s_text);
+    // the concatenation as a whole is NOT one valid stream (trailing bytes): reference returns false
+    std::string whole;
+    CHECK(!b200::snappy::Uncompress(output.data(), output.size(), &whole));
+    CHECK(!b200::snappy::IsValidCompressedBuffer(output.data(), output.size()));
+    CHECK(b200::snappy::IsValidCompressedBuffer(output.data(), com_len1));
+}
+
+static void throughput_shapes() {  // throughput_compare / throughput_compare_complete_random shapes
+    const char str_table[] = "abcdefghijklmnopqrstuvwxyzABCDEFGHIJKLMNOPQRSTUVWXYZ0123456789";
+    int len_subs[] = {128, 1024, 16 * 1024, 32 * 1024, 512 * 1024};
+    srand(1);
+    for (int len : len_subs) {
+        std::string dup = pattern_az09(len), rnd;
+        for (int j = 0; j < len; j++) rnd.push_back(str_table[rand() % 62]);
+        for (const std::string* text : {&dup, &rnd}) {
+            std::string z, back;
+            CHECK(b200::policy::SnappyCompress(blocks_of(*text, 8160), &z));  // 8160-byte IOBuf payload blocks
+            CHECK(z == oracle_compress(*text));
+            size_t ulen = 0;
+            CHECK(b200::snappy::GetUncompressedLength(z.data(), z.size(), &ulen) && ulen == text->size());
+            CHECK(b200::policy::SnappyDecompress(blocks_of(z, 100), &back));
+            CHECK(back == *text);
+            CHECK(b200::crc32c::Value(text->data(), text->size()) ==
+                  b2o_crc32c_value(reinterpret_cast<const uint8_t*>(text->data()), text->size()));
+        }
+    }
+}
+
+static void mass_snappy_iobuf() {  // test_compress_method.mass_snappy_iobuf
+    std::string text;
+    for (int j = 0; j < 782;)
+        for (int i = 0; i < 26 && j < 782; i++, j++) text.push_back('a' + i);
+    std::string output_buf;
+    CHECK(b200::policy::SnappyCompress(blocks_of(text, 8192), &output_buf));
+    CHECK(output_buf == oracle_compress(text));
+    size_t decompress_length = 0;
+    CHECK(b200::snappy::GetUncompressedLength(output_buf.data(), output_buf.size(), &decompress_length));
+    std::vector<char> output(decompress_length);
+    CHECK(b200::snappy::RawUncompress(output_buf.data(), output_buf.size(), output.data()));
+    CHECK(std::string(output.data(), output.size()) == text);
+}
+
+static void batch_calls() {
+    std::vector<std::string> bodies;
+    for (int i = 0; i < 300; i++) {
+        std::string s((size_t)(i * 37 % 5000), '\0');
+        b2o_corpus_fill(B2O_WORDS, i, reinterpret_cast<uint8_t*>(&s[0]), s.size());
+        bodies.push_back(s);
+    }
+    std::vector<BlockList> in;
+    for (const std::string& s : bodies) in.push_back(blocks_of(s, 1000));
+    std::vector<std::string> z, back;
+    std::vector<bool> ok;
+    std::vector<uint32_t> crc;
+    b200::policy::SnappyCompressBatch(in, &z);
+    b200::policy::Crc32cBatch(in, nullptr, &crc);
+    std::vector<BlockList> zin;
+    for (const std::string& s : z) zin.push_back(blocks_of(s, 64));
+    b200::policy::SnappyDecompressBatch(zin, &back, &ok);
+    for (size_t i = 0; i < bodies.size(); i++) {
+        CHECK(z[i] == oracle_compress(bodies[i]));
+        CHECK(ok[i] && back[i] == bodies[i]);
+        CHECK(crc[i] == b2o_crc32c_value(reinterpret_cast<const uint8_t*>(bodies[i].data()), bodies[i].size()));
+    }
+    // a malformed stream in the middle of a batch fails alone
+    std::string bad = z[5];
+    bad[bad.size() / 2] ^= 0x55;
+    bad.resize(bad.size() - 1);
+    zin[5] = blocks_of(bad, 64);
+    b200::policy::SnappyDecompressBatch(zin, &back, &ok);
+    uint32_t ulen = 0;
+    std::vector<uint8_t> tmp(5000);
+    int want = b2o_snappy_uncompress(reinterpret_cast<const uint8_t*>(bad.data()), bad.size(), tmp.data(), tmp.size(), &ulen);
+    CHECK(ok[5] == (want != 0));
+    CHECK(ok[4] && ok[6] && back[6] == bodies[6]);
+}
+
+int main() {
+    crc_standard_results();
+    crc_values_extend_mask();
+    snappy_iobuf();
+    snappy_test();
+    throughput_shapes();
+    mass_snappy_iobuf();
+    batch_calls();
+    if (g_fail) {
+        fprintf(stderr, "%d check(s) failed\n", g_fail);
+        return 1;
+    }
+    printf("host api: all checks passed\n");
+    return 0;
+}

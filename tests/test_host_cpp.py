@@ -1,0 +1,41 @@
+"""The C++ host mirror (brpc-github-actions_b200/host) over libb2c.so: compile it with g++ and,
+on a GPU box, run the reference's own unit tests re-pointed at it (tests/cpp/test_host_api.cpp)."""
+import os
+import shutil
+import subprocess
+
+import pytest
+
+import brpc_b200
+from oracle import oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "brpc-github-actions_b200")
+BIN = os.path.join(ROOT, "tests", "cpp", "test_host_api.bin")
+
+
+def _build():
+    O.port()  # makes sure oracle/libb2oracle.so exists
+    brpc_b200.load()
+    cxx = shutil.which("g++")
+    if cxx is None:
+        if os.path.exists(BIN):
+            return BIN
+        pytest.skip("no g++ and no prebuilt test binary")
+    cmd = [cxx, "-std=c++17", "-O1", "-Wall", "-I", os.path.join(ROOT, "include"), "-I", os.path.join(PKG, "host"),
+           "-I", os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests", "cpp", "test_host_api.cpp"),
+           os.path.join(PKG, "host", "b200_codec.cpp"), "-L", PKG, "-lb2c", "-L", os.path.join(ROOT, "oracle"),
+           "-lb2oracle", f"-Wl,-rpath,{PKG}", f"-Wl,-rpath,{os.path.join(ROOT, 'oracle')}", "-lpthread", "-o", BIN]
+    subprocess.run(cmd, check=True)
+    return BIN
+
+
+def test_host_mirror_compiles_and_links():
+    assert os.path.exists(_build())
+
+
+@pytest.mark.gpu
+def test_reference_unit_tests_on_the_gpu_codec():
+    r = subprocess.run([_build()], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "all checks passed" in r.stdout
