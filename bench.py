@@ -102,18 +102,49 @@ def dist_env():
     return int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
 
 
-def make_batch(rank: int, n_msgs: int):
+WORKLOADS = {
+    "c1": "C1: 4096 x 4 KiB echo payloads",
+    "c2": "C2: 2^20 x 1 KiB small RPC bodies",
+    "c3": "C3: 256 x 1 MiB bodies (16 x 64 KiB snappy fragments each)",
+    "c4": "C4: lognormal 64 B - 4 MiB payload mix (scaled to --bytes)",
+    "c5": "C5: 64 KiB fragments as independent bodies (scaled to --bytes)",
+}
+
+
+def workload_lengths(args) -> np.ndarray:
+    w = args.workload
+    if w == "c1":
+        return np.full(4096, 4096, dtype=np.uint32)
+    if w == "c2":
+        return np.full(args.messages, MSG_BYTES, dtype=np.uint32)
+    if w == "c3":
+        return np.full(256, 1 << 20, dtype=np.uint32)
+    if w == "c5":
+        return np.full(max(1, args.bytes // 65536), 65536, dtype=np.uint32)
+    rng = np.random.default_rng(2024)  # c4: SURVEY.md 8(d)
+    out, total = [], 0
+    while total < args.bytes:
+        x = np.clip(np.round(np.exp(rng.normal(np.log(16384), 2.0, 65536))), 64, 4 << 20).astype(np.uint32)
+        out.append(x)
+        total += int(x.sum())
+    x = np.concatenate(out)
+    return x[: int(np.searchsorted(np.cumsum(x.astype(np.uint64)), args.bytes)) + 1]
+
+
+def make_batch(rank: int, args):
     from oracle import oracle as O
-    lengths = np.full(n_msgs, MSG_BYTES, dtype=np.uint32)
-    return O.corpus_batch(CORPUS, lengths, first_index=rank * n_msgs)
+    lengths = workload_lengths(args)
+    return O.corpus_batch(args.corpus, lengths, first_index=rank * len(lengths))
 
 
-def config_dict(world: int, n_msgs: int):
-    return {"workload": f"C2: {n_msgs} x {MSG_BYTES} B RPC bodies per GPU ({n_msgs * MSG_BYTES / 2**30:.2f} GiB), "
-                        f"corpus={CORPUS}; step = crc32c + snappy compress + snappy decompress",
-            "corpus": CORPUS, "messages_per_gpu": n_msgs, "message_bytes": MSG_BYTES,
+def config_dict(world: int, args, ln: np.ndarray):
+    payload = int(ln.astype(np.uint64).sum())
+    return {"workload": f"{WORKLOADS[args.workload]}: {len(ln)} bodies, {payload / 2**30:.2f} GiB per GPU, "
+                        f"corpus={args.corpus}; step = crc32c + snappy compress + snappy decompress",
+            "corpus": args.corpus, "messages_per_gpu": int(len(ln)), "payload_bytes_per_gpu": payload,
             "sharding": f"{world} independent batch(es), one per GPU, no collective",
-            "l2": "inputs (1 GiB per GPU) larger than the 126 MB L2; no flush needed"}
+            "l2": ("inputs larger than the 126 MB L2; no flush needed" if payload > 200e6 else
+                   "inputs SMALLER than L2 (the reference's CPU-sized case): numbers are L2-resident")}
 
 
 # --------------------------------------------------------------------------- reference arm
@@ -123,8 +154,8 @@ def run_reference(args, rank, world):
     from oracle import oracle as O
     cpu = O.best()
     cores = os.cpu_count() or 1
-    n_msgs = args.messages
-    arena, off, ln = make_batch(0, n_msgs)
+    arena, off, ln = make_batch(0, args)
+    n_msgs = len(ln)
     payload = int(ln.astype(np.uint64).sum())
 
     def step():
@@ -143,9 +174,9 @@ def run_reference(args, rank, world):
     line = {"metric": METRIC, "impl": "reference", "value": gbs, "unit": "GB/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": config_dict(world, n_msgs),
+            "config": config_dict(world, args, ln),
             "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": cpu.kind,
-                             "sample": f"full batch: {n_msgs} x {MSG_BYTES} B per step, {args.steps} steps, "
+                             "sample": f"full batch: {n_msgs} bodies, {payload} B per step, {args.steps} steps, "
                                        f"static split over {cores} threads (RawCompress/RawUncompress/crc32c::Value)"},
             "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -163,9 +194,9 @@ def run_ours(args, rank, local_rank, world):
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    n_msgs = args.messages
     codec = brpc_b200.Codec(local_rank)
-    arena, off, ln = make_batch(rank, n_msgs)
+    arena, off, ln = make_batch(rank, args)
+    n_msgs = len(ln)
     payload = int(ln.astype(np.uint64).sum())
     lay = codec.layout(off, ln)
     d_in = codec.to_device(arena)
@@ -231,7 +262,10 @@ def run_ours(args, rank, local_rank, world):
 
     # ---- end to end through the host-buffer ABI (iovec block lists, PCIe inside) ----
     rng = np.random.default_rng(2024 + rank)
-    segs, seg_begin = brpc_b200.make_iovecs(arena, off, ln, cuts=rng.integers(0, MSG_BYTES + 1, n_msgs))
+    if args.workload == "c2":  # 1-2 blocks per body at a seeded random cut
+        segs, seg_begin = brpc_b200.make_iovecs(arena, off, ln, cuts=rng.integers(0, MSG_BYTES + 1, n_msgs))
+    else:  # IOBuf's default blocks: 8192 bytes minus the 32-byte header
+        segs, seg_begin = brpc_b200.make_iovecs(arena, off, ln, seg_bytes=8160)
     # result buffers are page-locked (b2c_host_alloc_pinned), as the bRPC shim's output blocks would be, so the
     # library DMAs results straight into them; the INPUT blocks stay ordinary pageable memory like IOBuf blocks
     h_comp = codec.pinned(int(lay.max_compressed_bytes))
@@ -270,8 +304,8 @@ def run_ours(args, rank, local_rank, world):
     e2e_s = time.perf_counter() - t0
     if dist is not None:
         e2e_s = brpc_b200.sharding.max_over_ranks(e2e_s, device="cuda")
-    assert h_back[:payload].tobytes()[:4096] == b"".join(
-        arena[int(off[i]):int(off[i]) + int(ln[i])].tobytes() for i in range(4))
+    first = b"".join(arena[int(off[i]):int(off[i]) + int(ln[i])].tobytes() for i in range(min(4, n_msgs)))
+    assert h_back[:len(first)].tobytes() == first
 
     if rank == 0:
         hbm_peak, peak_src = read_peaks()
@@ -296,20 +330,20 @@ def run_ours(args, rank, local_rank, world):
             "metric": METRIC, "value": payload * world * args.steps / (ms * 1e-3) / 1e9, "unit": "GB/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": config_dict(world, n_msgs), "clocks": clocks,
+            "config": config_dict(world, args, ln), "clocks": clocks,
             "e2e": {"value": payload * world * e2e_steps / e2e_s / 1e9, "unit": "GB/s",
                     "h2d_bytes_per_step": int(bytes_h2d), "d2h_bytes_per_step": int(bytes_d2h), "steps": e2e_steps,
                     "path": "b2c_crc32c_batch + b2c_snappy_compress_batch + b2c_snappy_decompress_batch; inputs = pageable host "
                             "iovecs (1-2 blocks per body), outputs = page-locked host buffers"},
             "gpu_launches": int(launches),
-            "roofline": {"kernel": "snappy_compress_small_kernel", "bound": "hbm", "achieved": achieved,
+            "roofline": {"kernel": "snappy_compress_small_kernel" if int(ln.max()) <= 1024 else "snappy_compress_*_kernel (all size classes of the batch)", "bound": "hbm", "achieved": achieved,
                          "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
                          "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                          "note": "byte-exact greedy LZ77 is a serial dependency chain per fragment: latency/issue bound, "
                                  "not HBM bound (see DESIGN.md)"},
             "ops": per_op, "compression_ratio": comp_bytes / payload,
             "cpu_baseline": {"value": cpu_gbs, "unit": "GB/s", "cores": cores, "kind": cpu.kind,
-                             "sample": f"full batch ({n_msgs} x {MSG_BYTES} B) x {reps} passes of crc32c + RawCompress + "
+                             "sample": f"full batch ({n_msgs} bodies, {payload} B) x {reps} passes of crc32c + RawCompress + "
                                        f"RawUncompress, static split over {cores} threads"},
         }
         print(json.dumps(line), flush=True)
@@ -324,7 +358,10 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--messages", type=int, default=N_MSGS, help="messages per GPU (default: the C2 workload)")
+    ap.add_argument("--messages", type=int, default=N_MSGS, help="bodies per GPU for --workload c2")
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS), help="default c2 = BASELINE configs[1]")
+    ap.add_argument("--corpus", default=CORPUS, choices=["words", "az09", "rand62"])
+    ap.add_argument("--bytes", type=int, default=1 << 30, help="payload per GPU for --workload c4 / c5")
     args = ap.parse_args()
     if args.impl == "ours":
         args.warmup = max(args.warmup, 3)  # timing rule: at least 3 warm-up steps

@@ -398,6 +398,10 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     if (const char* s = getenv("B2C_SLAB_MB")) ctx->slab_bytes = std::max<size_t>(1, (size_t)atol(s)) << 20;
     if (const char* s = getenv("B2C_HOST_THREADS")) ctx->host_threads = (unsigned)std::max(1L, atol(s));
     if (const char* s = getenv("B2C_TRACE")) ctx->trace = atoi(s) != 0;
+    if (const char* s = getenv("B2C_BATCH_DECODE")) ctx->batch_decode = atoi(s) != 0;
+    if (const char* s = getenv("B2C_RING_DECODE")) ctx->ring_decode = atoi(s) != 0;
+    if (const char* s = getenv("B2C_BLOCK_DECODE")) ctx->block_decode = atoi(s) != 0;
+    if (const char* s = getenv("B2C_BATCH_DECODE_SMALL")) ctx->batch_decode_small = atoi(s) != 0;
     if (const char* s = getenv("B2C_NT_GATHER")) ctx->nt_gather = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL_KERNELS")) ctx->small_kernels = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL_LPW_C")) ctx->small_lpw_compress = atoi(s);

@@ -113,6 +113,11 @@ struct b2c_ctx {
     size_t slab_bytes = 32u << 20;
     unsigned host_threads = 0;
     bool trace = false;
+    bool ring_decode = false;        // B2C_RING_DECODE=1: unsplittable large slots decode through a 64 KiB smem ring
+    bool block_decode = true;        // B2C_BLOCK_DECODE=0: never split large streams into 64 KiB blocks
+    bool ring_attr_done = false;
+    bool batch_decode = true;        // B2C_BATCH_DECODE=0: one tag per step in the warp decoder
+    bool batch_decode_small = false; // B2C_BATCH_DECODE_SMALL=1: <=1 KiB slots use the warp batch decoder, not one lane per stream
     bool nt_gather = true;  // B2C_NT_GATHER=0: plain memcpy into staging
 };
 

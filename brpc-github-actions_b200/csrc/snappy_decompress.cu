@@ -121,6 +121,317 @@ __device__ int decode_message_warp(const uint8_t* __restrict__ in, const uint32_
     }
 }
 
+// ---------------------------------------------------------------------------
+// Batched decoder: up to 32 tags per step.
+//
+// The serial part of DecompressAllTags (snappy.cc:731-784) is only "where does the next
+// tag start"; everything else is independent per tag.  Per step the warp
+//   1. keeps a 256-byte window of the stream in shared memory and lets every lane compute,
+//      for 8 byte positions each, where the next tag would start IF a tag started there;
+//   2. follows that jump table from the current position for up to 32 hops (a chain of
+//      broadcast shared-memory loads, ~5 instructions per tag), handing tag t to lane t;
+//   3. decodes the 32 tags in parallel, takes a warp prefix sum of their output lengths to
+//      place them, and checks every reject condition of the reference at once;
+//   4. moves the literals (no dependencies), then the copies in rounds: a copy runs as soon
+//      as its source lies entirely before the output position of the first copy that has not
+//      run yet (back-references inside the batch resolve in shared memory / L1).
+// ---------------------------------------------------------------------------
+constexpr uint32_t kWin = 256;
+struct BatchScratch {
+    uint32_t win32[kWin / 4 + 4];  // stream bytes [wbase, wbase + 256) + 16 bytes of padding
+    uint16_t jmp[kWin];            // next tag position (window-relative, saturated) if a tag starts here
+};
+static_assert(sizeof(BatchScratch) <= 1024, "BatchScratch must fit its 1 KiB slot");
+
+__device__ __forceinline__ uint64_t warp_incl_scan_u64(uint64_t v, uint32_t lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t lo = __shfl_up_sync(kFull, (uint32_t)v, d);
+        uint32_t hi = __shfl_up_sync(kFull, (uint32_t)(v >> 32), d);
+        if (lane >= (uint32_t)d) v += ((uint64_t)hi << 32) | lo;
+    }
+    return v;
+}
+
+// Output policies of the batched decoder.
+// LinearOut: the whole output is addressable at base[p] (a per-warp shared-memory buffer for
+// small slots, or the final HBM slot).
+struct LinearOut {
+    static constexpr bool kMovesData = true;
+    uint8_t* base;
+    __device__ __forceinline__ void on_tag(bool, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {}
+    __device__ __forceinline__ uint8_t ld(uint32_t p) const { return base[p]; }
+    __device__ __forceinline__ void st(uint32_t p, uint8_t v) { base[p] = v; }
+    __device__ __forceinline__ void begin_batch(uint32_t, uint32_t, uint32_t) {}
+    __device__ __forceinline__ bool takes_direct(uint32_t) const { return false; }
+    __device__ __forceinline__ void direct_literal(const uint8_t*, uint32_t, uint32_t, uint32_t) {}
+    __device__ __forceinline__ void finish(uint32_t, uint32_t) {}
+};
+
+// RingOut: large outputs.  The most recent 64 KiB of output live in a shared-memory ring
+// (byte p at ring[p & 0xffff]) so that back-references — which the reference compressor keeps
+// inside one 64 KiB block (snappy.h:193-203) — resolve at shared-memory latency; older bytes
+// are read back from HBM, where the ring is flushed in 16-byte stores as it fills.
+struct RingOut {
+    static constexpr bool kMovesData = true;
+    __device__ __forceinline__ void on_tag(bool, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {}
+    uint8_t* ring;      // 65536 bytes of shared memory
+    uint8_t* gout;      // final slot in HBM
+    uint32_t flushed;   // every byte below this is in HBM
+    uint32_t ring_lo;   // no byte below this is in the ring
+    uint32_t bound;     // during a batch: bytes >= bound are read from the ring
+    __device__ __forceinline__ uint8_t ld(uint32_t p) const { return p >= bound ? ring[p & 0xffffu] : gout[p]; }
+    __device__ __forceinline__ void st(uint32_t p, uint8_t v) { ring[p & 0xffffu] = v; }
+    __device__ void flush_to(uint32_t upto, uint32_t lane) {  // warp-cooperative
+        uint32_t a = flushed;
+        if (upto <= a) return;
+        if ((reinterpret_cast<uintptr_t>(gout) & 15) == 0) {
+            uint32_t head = min(upto - a, (16u - (a & 15u)) & 15u);
+            if (lane < head) gout[a + lane] = ring[(a + lane) & 0xffffu];
+            a += head;
+            const uint32_t vecs = (upto - a) >> 4;
+            for (uint32_t i = lane; i < vecs; i += 32) {
+                const uint32_t q = a + 16 * i;
+                *reinterpret_cast<uint4*>(gout + q) = *reinterpret_cast<const uint4*>(ring + (q & 0xffffu));
+            }
+            a += vecs << 4;
+        }
+        for (uint32_t q = a + lane; q < upto; q += 32) gout[q] = ring[q & 0xffffu];
+        flushed = upto;
+        __syncwarp();
+    }
+    // called before a batch that writes [produced, batch_end)
+    __device__ __forceinline__ void begin_batch(uint32_t produced, uint32_t batch_end, uint32_t lane) {
+        if (batch_end - flushed > 49152u) flush_to(produced, lane);  // keeps flushed >= batch_end - 65536
+        const uint32_t lo64 = batch_end > 65536u ? batch_end - 65536u : 0u;
+        bound = max(ring_lo, lo64);
+    }
+    // a literal too long for the ring goes straight from the stream to HBM
+    __device__ __forceinline__ bool takes_direct(uint32_t len) const { return len > 8192u; }
+    __device__ void direct_literal(const uint8_t* src, uint32_t produced, uint32_t len, uint32_t lane) {
+        flush_to(produced, lane);
+        uint8_t* dst = gout + produced;
+        for (uint32_t i = lane; i < len; i += 32) dst[i] = src[i];
+        __syncwarp();
+        flushed = produced + len;
+        ring_lo = produced + len;
+    }
+    __device__ __forceinline__ void finish(uint32_t produced, uint32_t lane) { flush_to(produced, lane); }
+};
+
+// ScanOut: moves no data.  It runs the batched decoder's parse + validation only and records,
+// for every 64 KiB output boundary, the stream offset of the tag that starts there — the
+// fragment boundaries the raw snappy format does not mark (format_description.txt:18-25).
+// A stream is "splittable" when no element straddles such a boundary and no copy reaches back
+// across one (always true for the reference compressor, which never matches across its 64 KiB
+// blocks, snappy.h:193-203); its blocks can then be decoded independently, one warp each.
+struct ScanOut {
+    static constexpr bool kMovesData = false;
+    uint32_t* blk_ip;  // [nblk] stream offset where output block k starts
+    uint32_t nblk;
+    uint32_t bad;      // per-lane: something prevents splitting
+    __device__ __forceinline__ void on_tag(bool act, uint32_t at, uint32_t out_pos, uint32_t len, uint32_t kind,
+                                           uint32_t offset) {
+        if (!act) return;
+        const uint32_t k0 = out_pos >> 16;
+        if (len && ((out_pos + len - 1) >> 16) != k0) bad = 1;
+        if ((out_pos & 0xffffu) == 0 && k0 > 0 && k0 < nblk) blk_ip[k0] = at;
+        if (kind != 0 && offset > (out_pos & 0xffffu)) bad = 1;
+    }
+    __device__ __forceinline__ uint8_t ld(uint32_t) const { return 0; }
+    __device__ __forceinline__ void st(uint32_t, uint8_t) {}
+    __device__ __forceinline__ void begin_batch(uint32_t, uint32_t, uint32_t) {}
+    __device__ __forceinline__ bool takes_direct(uint32_t) const { return false; }
+    __device__ __forceinline__ void direct_literal(const uint8_t*, uint32_t, uint32_t, uint32_t) {}
+    __device__ __forceinline__ void finish(uint32_t, uint32_t) {}
+};
+
+template <class Out>
+__device__ int decode_message_batched(const uint8_t* __restrict__ in, const uint32_t n, uint32_t ip, Out& out,
+                                      const uint32_t expected, const uint32_t lane, BatchScratch& sc) {
+    const uint8_t* win = reinterpret_cast<const uint8_t*>(sc.win32);
+    uint32_t produced = 0;
+    uint32_t wbase = 0;
+    bool have_window = false;
+    for (;;) {
+        if (ip == n) {  // clean eof, snappy.cc:867
+            if (produced != expected) return B2C_CORRUPT;
+            out.finish(produced, lane);
+            return B2C_OK;
+        }
+        if (!have_window || ip - wbase + 5 > kWin) {
+            // ---- 1. refill the window at ip and rebuild the jump table
+            __syncwarp();
+            wbase = ip;
+            have_window = true;
+#pragma unroll
+            for (uint32_t r = 0; r < 2; r++) {
+                const uint32_t wi = lane + 32 * r;
+                const uint32_t at = wbase + 4 * wi;
+                sc.win32[wi] = at < n ? ld32u(in + at) : 0u;
+            }
+            if (lane < 4) sc.win32[kWin / 4 + lane] = 0u;
+            __syncwarp();
+#pragma unroll
+            for (uint32_t j = 0; j < 8; j++) {
+                const uint32_t p = lane * 8 + j;
+                const uint32_t c = win[p];
+                const uint32_t kind = c & 3;
+                uint64_t L;
+                if (kind == 0) {
+                    const uint32_t l = c >> 2;
+                    if (l < 60) {
+                        L = l + 2;
+                    } else {
+                        const uint32_t ex = l - 59;
+                        uint32_t val = win[p + 1] | (win[p + 2] << 8) | (win[p + 3] << 16) | ((uint32_t)win[p + 4] << 24);
+                        if (ex < 4) val &= (1u << (8 * ex)) - 1u;
+                        L = (uint64_t)1 + ex + (uint32_t)(val + 1u);  // len wraps to 0 like the reference
+                    }
+                } else {
+                    L = kind == 1 ? 2 : kind == 2 ? 3 : 5;
+                }
+                const uint64_t to = p + L;
+                sc.jmp[p] = (uint16_t)(to > 0xFFFFu ? 0xFFFFu : to);
+            }
+            __syncwarp();
+        }
+        // ---- 2. follow the chain: tag t of this batch goes to lane t
+        uint32_t cur = ip - wbase, my_pos = 0, count = 0;
+        for (uint32_t t = 0; t < 32; t++) {
+            if (cur + 5 > kWin) break;       // tag might not be fully inside the window: next batch reloads
+            if (wbase + cur >= n) break;     // end of stream (or an overrun the owning lane reports)
+            const uint32_t nxt = sc.jmp[cur];
+            if (nxt - cur > 1030u) {         // a literal of more than 1 KiB: it gets a batch of its own,
+                if (t == 0) {                // so that one batch never outgrows the output ring
+                    if (lane == 0) my_pos = cur;
+                    count = 1;
+                }
+                break;
+            }
+            if (lane == t) my_pos = cur;
+            count = t + 1;
+            cur = nxt;
+        }
+        // ---- 3. decode in parallel
+        const bool act = lane < count;
+        uint32_t kind = 0, len = 0, offset = 0, lit_src = 0, adv = 0;
+        bool fail = false;
+        if (act) {
+            const uint32_t p = my_pos, at = wbase + p;
+            const uint32_t c = win[p];
+            kind = c & 3;
+            const uint32_t extra = kind == 0 ? (c >= 0xf0 ? (c >> 2) - 59 : 0) : kind == 1 ? 1 : kind == 2 ? 2 : 4;
+            if (n - at < extra + 1) fail = true;  // tag cut short
+            uint32_t trailer = win[p + 1] | (win[p + 2] << 8) | (win[p + 3] << 16) | ((uint32_t)win[p + 4] << 24);
+            if (extra < 4) trailer &= (1u << (8 * extra)) - 1u;
+            adv = 1 + extra;
+            if (kind == 0) {
+                len = (c >> 2) + 1;
+                if (len >= 61) len = trailer + 1u;
+                lit_src = at + 1 + extra;
+                if (!fail && n - lit_src < len) fail = true;  // premature end of input
+                if (!fail) adv += len;
+            } else if (kind == 1) {
+                len = ((c >> 2) & 7) + 4;
+                offset = ((c >> 5) << 8) | (trailer & 0xff);
+            } else {
+                len = (c >> 2) + 1;
+                offset = trailer;
+            }
+            if (len > expected) {  // cannot fit whatever came before it
+                fail = true;
+                len = 0;
+            }
+        }
+        const uint64_t incl = warp_incl_scan_u64(act ? len : 0u, lane);
+        const uint64_t pos64 = (uint64_t)produced + incl - len;
+        if (act && !fail) {
+            if (pos64 + len > expected) fail = true;                       // output overrun
+            else if (kind != 0 && (offset == 0 || offset > pos64)) fail = true;  // snappy.cc:1200-1202
+        }
+        if (__any_sync(kFull, fail)) return B2C_CORRUPT;
+        const uint32_t out_pos = (uint32_t)pos64;
+        const uint32_t batch_end = __shfl_sync(kFull, (uint32_t)(pos64 + len), count - 1);
+        // a literal too long for the output policy's buffer is moved on its own (it is the whole batch)
+        const uint32_t kind0 = __shfl_sync(kFull, kind, 0), len0 = __shfl_sync(kFull, len, 0);
+        if (Out::kMovesData && count == 1 && kind0 == 0 && out.takes_direct(len0)) {
+            const uint32_t l0 = len0, s0 = __shfl_sync(kFull, lit_src, 0);
+            out.direct_literal(in + s0, produced, l0, lane);
+            produced += l0;
+            ip = s0 + l0;
+            continue;
+        }
+        out.on_tag(act, wbase + my_pos, out_pos, len, kind, offset);
+        if (!Out::kMovesData) {  // validation / boundary scan only
+            produced = batch_end;
+            ip = __shfl_sync(kFull, wbase + my_pos + adv, count - 1);
+            continue;
+        }
+        out.begin_batch(produced, batch_end, lane);
+        // ---- 4a. literals: short ones per lane, long ones by the whole warp
+        const bool is_lit = act && kind == 0;
+        if (is_lit && len <= 32) {
+            const uint8_t* src = in + lit_src;
+            for (uint32_t i = 0; i < len; i++) out.st(out_pos + i, src[i]);
+        }
+        uint32_t longs = __ballot_sync(kFull, is_lit && len > 32);
+        while (longs) {
+            const uint32_t l = __ffs(longs) - 1;
+            longs &= longs - 1;
+            const uint32_t s0 = __shfl_sync(kFull, lit_src, l), d0 = __shfl_sync(kFull, out_pos, l),
+                           ln = __shfl_sync(kFull, len, l);
+            const uint8_t* src = in + s0;
+            for (uint32_t i = lane; i < ln; i += 32) out.st(d0 + i, src[i]);
+        }
+        __syncwarp();
+        // ---- 4b. copies
+        const bool is_copy = act && kind != 0;
+        uint32_t pending = __ballot_sync(kFull, is_copy);
+        const uint32_t src_pos = out_pos - offset;                         // meaningful for copies
+        const uint32_t src_end = offset >= len ? src_pos + len : out_pos;  // bytes read lie in [src_pos, src_end)
+        if (__any_sync(kFull, is_copy && len > 16)) {
+            // long copies (runs, repeated records): one tag at a time, 32 bytes per instruction
+            while (pending) {
+                const uint32_t l = __ffs(pending) - 1;
+                pending &= pending - 1;
+                const uint32_t d0 = __shfl_sync(kFull, out_pos, l), s0 = __shfl_sync(kFull, src_pos, l),
+                               ln = __shfl_sync(kFull, len, l), of = __shfl_sync(kFull, offset, l);
+                uint8_t v0 = 0, v1 = 0;
+                const uint32_t i0 = lane, i1 = lane + 32;
+                if (i0 < ln) v0 = out.ld(s0 + (of >= ln ? i0 : i0 % of));
+                if (i1 < ln) v1 = out.ld(s0 + (of >= ln ? i1 : i1 % of));
+                if (i0 < ln) out.st(d0 + i0, v0);
+                if (i1 < ln) out.st(d0 + i1, v1);
+                __syncwarp();
+            }
+        } else {
+            // short copies: one lane per tag, in dependency rounds — a copy runs once its source lies
+            // entirely below the output position of the first copy that has not run yet
+            while (pending) {
+                const uint32_t first = __ffs(pending) - 1;
+                const uint32_t frontier = __shfl_sync(kFull, out_pos, first);
+                const bool ready = ((pending >> lane) & 1u) && (lane == first || src_end <= frontier);
+                if (ready) {
+                    if (offset >= len) {
+                        for (uint32_t i = 0; i < len; i++) out.st(out_pos + i, out.ld(src_pos + i));
+                    } else {  // pattern of `offset` bytes repeated, as IncrementalCopy (snappy.cc:98-103)
+                        uint32_t j = 0;
+                        for (uint32_t i = 0; i < len; i++) {
+                            out.st(out_pos + i, out.ld(src_pos + j));
+                            if (++j == offset) j = 0;
+                        }
+                    }
+                }
+                pending &= ~__ballot_sync(kFull, ready);
+                __syncwarp();
+            }
+        }
+        produced = batch_end;
+        ip = __shfl_sync(kFull, wbase + my_pos + adv, count - 1);
+    }
+}
+
 struct DecompressParams {
     const uint8_t* in;
     const uint64_t* in_off;
@@ -133,7 +444,84 @@ struct DecompressParams {
     int32_t* status;
     uint32_t n_list;
     uint32_t smem_per_warp;  // 0: decode straight into global memory
+    uint32_t batched;        // 1: 32 tags per step (decode_message_batched), 0: one tag per step
+    uint32_t ring;           // 1: large slots decode through a 64 KiB shared-memory ring (one warp per CTA)
+    // block-parallel decoding of large streams (class 2 only; null otherwise)
+    const uint32_t* out_frag_first;  // output layout: first 64 KiB block of message m
+    const uint32_t* out_frag_msg;    // output layout: message of block f
+    uint32_t* blk_ip;                // [output blocks] stream offset of each block's first tag
+    uint32_t* mode;                  // [n] kModeWhole / kModeBlocks / kModeDone
+    uint32_t* ulen_tmp;              // [n] uncompressed lengths for the block kernel
+    uint32_t n_blocks;
 };
+
+enum : uint32_t { kModeWhole = 0, kModeBlocks = 1, kModeDone = 2 };
+
+// Pass 1 for large slots: validate the stream and find its 64 KiB block boundaries.
+__global__ void __launch_bounds__(256) snappy_scan_kernel(DecompressParams P) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t wib = threadIdx.x >> 5;
+    const uint32_t w = blockIdx.x * (blockDim.x >> 5) + wib;
+    if (w >= P.n_list) return;
+    const uint32_t m = P.list ? P.list[w] : w;
+    const uint32_t cap = P.out_cap[m];
+    if (cap <= kFragBytes) {  // single block: nothing to split
+        if (lane == 0) P.mode[m] = kModeWhole;
+        return;
+    }
+    const uint8_t* in = P.in + P.in_off[m];
+    const uint32_t n = P.in_len[m];
+    uint32_t expected = 0;
+    const uint32_t k = read_preamble(in, n, &expected);
+    int st = B2C_OK;
+    uint32_t mode = kModeDone;
+    if (k == 0) {
+        st = B2C_CORRUPT;
+    } else if (expected > cap) {
+        st = B2C_TOO_SMALL;
+    } else if (expected <= kFragBytes) {
+        mode = kModeWhole;
+    } else {
+        const uint32_t f0 = P.out_frag_first[m];
+        ScanOut so{P.blk_ip + f0, (expected + kFragBytes - 1) / kFragBytes, 0u};
+        if (lane == 0) P.blk_ip[f0] = k;
+        BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * 1024);
+        st = decode_message_batched(in, n, k, so, expected, lane, sc);
+        if (st == B2C_OK) mode = __any_sync(kFull, so.bad) ? kModeWhole : kModeBlocks;
+    }
+    if (lane == 0) {
+        P.mode[m] = mode;
+        P.ulen_tmp[m] = expected;
+        if (mode != kModeWhole) {
+            P.status[m] = st;
+            if (P.ulen) P.ulen[m] = expected;
+        }
+    }
+}
+
+// Pass 2 for large slots: every 64 KiB block of a splittable stream is decoded by its own warp.
+__global__ void __launch_bounds__(256) snappy_decompress_blocks_kernel(DecompressParams P) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t wib = threadIdx.x >> 5;
+    const uint32_t f = blockIdx.x * (blockDim.x >> 5) + wib;
+    if (f >= P.n_blocks) return;
+    const uint32_t m = P.out_frag_msg[f];
+    if (P.mode[m] != kModeBlocks) return;
+    const uint32_t kblk = f - P.out_frag_first[m];
+    const uint32_t expected = P.ulen_tmp[m];
+    const uint32_t begin = kblk * kFragBytes;
+    if (begin >= expected) return;
+    const uint32_t block_len = min(kFragBytes, expected - begin);
+    const uint32_t ip0 = P.blk_ip[f];
+    const uint32_t ip1 = begin + kFragBytes < expected ? P.blk_ip[f + 1] : P.in_len[m];
+    LinearOut lo{P.out + P.out_off[m] + begin};
+    BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * 1024);
+    const int st = decode_message_batched(P.in + P.in_off[m], ip1, ip0, lo, block_len, lane, sc);
+    if (st != B2C_OK && lane == 0) atomicMax(reinterpret_cast<int*>(&P.status[m]), st);
+}
+
 
 __global__ void __launch_bounds__(256) snappy_decompress_kernel(DecompressParams P) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -142,6 +530,7 @@ __global__ void __launch_bounds__(256) snappy_decompress_kernel(DecompressParams
     const uint32_t w = blockIdx.x * (blockDim.x >> 5) + wib;
     if (w >= P.n_list) return;
     const uint32_t m = P.list ? P.list[w] : w;
+    if (P.mode && P.mode[m] != kModeWhole) return;  // decoded block-parallel, or already rejected by the scan
     const uint8_t* in = P.in + P.in_off[m];
     const uint32_t n = P.in_len[m];
     uint8_t* gout = P.out + P.out_off[m];
@@ -154,8 +543,11 @@ __global__ void __launch_bounds__(256) snappy_decompress_kernel(DecompressParams
     } else if (expected > cap) {
         st = B2C_TOO_SMALL;
     } else if (P.smem_per_warp && expected <= P.smem_per_warp) {
-        uint8_t* sbuf = smem_raw + (size_t)wib * P.smem_per_warp;
-        st = decode_message_warp(in, n, k, sbuf, expected, lane);
+        uint8_t* sbuf = smem_raw + (size_t)wib * (P.smem_per_warp + 1024);
+        BatchScratch& sc = *reinterpret_cast<BatchScratch*>(sbuf + P.smem_per_warp);
+        LinearOut lo{sbuf};
+        st = P.batched ? decode_message_batched(in, n, k, lo, expected, lane, sc)
+                       : decode_message_warp(in, n, k, sbuf, expected, lane);
         __syncwarp();
         if (st == B2C_OK) {
             // flush: bytes to 16-byte alignment of the destination, then 16-byte stores
@@ -184,7 +576,16 @@ __global__ void __launch_bounds__(256) snappy_decompress_kernel(DecompressParams
             if (lane < expected - done) gout[done + lane] = sbuf[done + lane];
         }
     } else {
-        st = decode_message_warp(in, n, k, gout, expected, lane);
+        BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * (P.smem_per_warp + 1024) + P.smem_per_warp);
+        if (P.ring) {
+            RingOut ro{smem_raw + (size_t)wib * (65536 + 1024), gout, 0u, 0u, 0u};
+            BatchScratch& rsc = *reinterpret_cast<BatchScratch*>(ro.ring + 65536);
+            st = decode_message_batched(in, n, k, ro, expected, lane, rsc);
+        } else {
+            LinearOut lo{gout};
+            st = P.batched ? decode_message_batched(in, n, k, lo, expected, lane, sc)
+                           : decode_message_warp(in, n, k, gout, expected, lane);
+        }
     }
     if (lane == 0) {
         P.status[m] = st;
@@ -221,7 +622,7 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
     prof_mark(ctx, lane, B2C_PROF_DECOMPRESS);
     for (int c = 0; c < 3; c++) {
         if (!out.n_dclass[c]) continue;
-        if (c == 0 && ctx->small_kernels) {  // slots <= 1 KiB: one lane per stream
+        if (c == 0 && ctx->small_kernels && !ctx->batch_decode_small) {  // slots <= 1 KiB: one lane per stream
             int rc = launch_decompress_small(ctx, lane, in, d_in, out, d_out, d_ulen, d_status);
             if (rc) return rc;
             continue;
@@ -238,9 +639,46 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
         P.status = d_status;
         P.n_list = out.n_dclass[c];
         P.smem_per_warp = class_smem[c];
-        const uint32_t wpb = class_warps[c];
+        P.out_frag_first = nullptr;
+        P.out_frag_msg = nullptr;
+        P.blk_ip = nullptr;
+        P.mode = nullptr;
+        P.ulen_tmp = nullptr;
+        P.n_blocks = 0;
+        P.batched = ctx->batch_decode ? 1u : 0u;
+        if (c == 2 && ctx->batch_decode && ctx->block_decode && out.d_frag_msg) {
+            // large slots: scan for block boundaries, decode splittable streams one warp per 64 KiB block
+            int rc = ws_reserve(ctx, lane, lane.ws_misc, ((size_t)out.n_frags + 2 * (size_t)out.n + 16) * 4);
+            if (rc) return rc;
+            P.out_frag_first = out.d_frag_first;
+            P.out_frag_msg = out.d_frag_msg;
+            P.blk_ip = static_cast<uint32_t*>(lane.ws_misc.p);
+            P.mode = P.blk_ip + out.n_frags + 1;
+            P.ulen_tmp = P.mode + out.n;
+            P.n_blocks = out.n_frags;
+            // only large-slot messages get a mode from the scan; everything else must read as "whole"
+            B2C_CUDA(ctx, cudaMemsetAsync(P.mode, 0, (size_t)out.n * 4, lane.stream));
+            const uint32_t sblocks = (P.n_list + 7) / 8;
+            snappy_scan_kernel<<<sblocks, 256, 8 * 1024, lane.stream>>>(P);
+            const uint32_t bblocks = (P.n_blocks + 7) / 8;
+            snappy_decompress_blocks_kernel<<<bblocks, 256, 8 * 1024, lane.stream>>>(P);
+            ctx->launches += 2;
+            B2C_CUDA(ctx, cudaGetLastError());
+        }
+        P.ring = (c == 2 && ctx->batch_decode && ctx->ring_decode) ? 1u : 0u;
+        uint32_t wpb = class_warps[c];
+        size_t smem = (size_t)wpb * (class_smem[c] + 1024);
+        if (P.ring) {
+            wpb = 1;
+            smem = 65536 + 1024;
+            if (!ctx->ring_attr_done) {
+                B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_decompress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                   (int)smem));
+                ctx->ring_attr_done = true;
+            }
+        }
         const uint32_t blocks = (P.n_list + wpb - 1) / wpb;
-        snappy_decompress_kernel<<<blocks, wpb * 32, (size_t)wpb * class_smem[c], lane.stream>>>(P);
+        snappy_decompress_kernel<<<blocks, wpb * 32, smem, lane.stream>>>(P);
         ctx->launches++;
         B2C_CUDA(ctx, cudaGetLastError());
     }
