@@ -13,7 +13,7 @@ import numpy as np
 
 from . import nvcc_build as _build
 
-OK, CORRUPT, TOO_SMALL = 0, 1, 2
+OK, CORRUPT, TOO_SMALL, CRC_MISMATCH = 0, 1, 2, 3
 E_CUDA, E_ARG, E_NOMEM, E_CAPACITY, E_NODEVICE = -1, -2, -3, -4, -5
 
 _u8p = C.POINTER(C.c_uint8)
@@ -67,6 +67,8 @@ SYMBOLS = {
     "b2c_snappy_compress_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint64, _vp]),
     "b2c_snappy_uncompressed_length_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     "b2c_snappy_decompress_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b2c_snappy_validate_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    "b2c_snappy_decompress_verify_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b2c_snappy_compress_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _vp, C.c_uint64, _u64p]),
     "b2c_snappy_decompress_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _vp, C.c_uint64, _u64p, _i32p]),
     "b2c_crc32c_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _u32p, _u32p]),
@@ -322,6 +324,34 @@ class Codec:
                        d_ulen: DevMem | None = None):
         self._check(self.lib.b2c_snappy_decompress_dev(self.ctx, in_layout.h, d_in.ptr, out_layout.h, d_out.ptr,
                                                        d_ulen.ptr if d_ulen else None, d_status.ptr))
+
+    def validate_dev(self, layout: Layout, d_in: DevMem, d_status: DevMem, d_ulen: DevMem | None = None):
+        self._check(self.lib.b2c_snappy_validate_dev(self.ctx, layout.h, d_in.ptr, d_ulen.ptr if d_ulen else None,
+                                                     d_status.ptr))
+
+    def decompress_verify_dev(self, in_layout: Layout, d_in: DevMem, out_layout: Layout, d_out: DevMem,
+                              d_masked_crc: DevMem, d_status: DevMem, d_ulen: DevMem | None = None):
+        self._check(self.lib.b2c_snappy_decompress_verify_dev(self.ctx, in_layout.h, d_in.ptr, out_layout.h, d_out.ptr,
+                                                              d_masked_crc.ptr, d_ulen.ptr if d_ulen else None,
+                                                              d_status.ptr))
+
+    def validate(self, arena: np.ndarray, off, length):
+        lin = self.layout(off, length)
+        d = self.to_device(arena)
+        ds = self.alloc(4 * max(lin.n, 1))
+        du = self.alloc(4 * max(lin.n, 1))
+        self.validate_dev(lin, d, ds, du)
+        return self.d2h(ds, 4 * lin.n, np.int32), self.d2h(du, 4 * lin.n, np.uint32)
+
+    def decompress_verify(self, arena: np.ndarray, off, length, out_off, out_cap, masked_crc):
+        lin = self.layout(off, length)
+        lout = self.layout(out_off, out_cap)
+        d = self.to_device(arena)
+        do = self.alloc(int(lout.arena_bytes) + 64)
+        ds = self.alloc(4 * max(lin.n, 1))
+        dm = self.to_device(np.ascontiguousarray(masked_crc, dtype=np.uint32))
+        self.decompress_verify_dev(lin, d, lout, do, dm, ds)
+        return self.d2h(do, int(lout.arena_bytes)), self.d2h(ds, 4 * lin.n, np.int32)
 
     # ---- convenience: numpy in, numpy out, through the device-resident ABI ----
     def crc32c(self, arena: np.ndarray, off, length, init=None) -> np.ndarray:

@@ -367,7 +367,7 @@ static int lane_create(b2c_ctx* ctx, Lane& l) {
 
 static void lane_destroy(Lane& l) {
     if (l.stream) cudaStreamSynchronize(l.stream);
-    for (DevBuf* b : {&l.ws_frag, &l.ws_misc, &l.d_in, &l.d_out})
+    for (DevBuf* b : {&l.ws_frag, &l.ws_misc, &l.ws_tab, &l.d_in, &l.d_out})
         if (b->p) cudaFree(b->p);
     for (PinBuf* b : {&l.h_in, &l.h_out})
         if (b->p) cudaFreeHost(b->p);
@@ -403,6 +403,7 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     if (const char* s = getenv("B2C_BLOCK_DECODE")) ctx->block_decode = atoi(s) != 0;
     if (const char* s = getenv("B2C_BATCH_DECODE_SMALL")) ctx->batch_decode_small = atoi(s) != 0;
     if (const char* s = getenv("B2C_NT_GATHER")) ctx->nt_gather = atoi(s) != 0;
+    if (const char* s = getenv("B2C_GTAB_WPS")) ctx->gtab_warps_per_sm = atoi(s);
     if (const char* s = getenv("B2C_SMALL_KERNELS")) ctx->small_kernels = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL_LPW_C")) ctx->small_lpw_compress = atoi(s);
     if (const char* s = getenv("B2C_SMALL_LPW_D")) ctx->small_lpw_decompress = atoi(s);
@@ -657,6 +658,21 @@ int b2c_snappy_decompress_dev(b2c_ctx* ctx, const b2c_layout* in, const void* d_
     B2C_CUDA(ctx, cudaSetDevice(ctx->device));
     return launch_decompress(ctx, ctx->main, in->v, static_cast<const uint8_t*>(d_in), out->v,
                              static_cast<uint8_t*>(d_out), d_ulen, d_status);
+}
+
+int b2c_snappy_validate_dev(b2c_ctx* ctx, const b2c_layout* L, const void* d_in, uint32_t* d_ulen, int32_t* d_status) {
+    if (!ctx || !L || !d_status) return B2C_E_ARG;
+    B2C_CUDA(ctx, cudaSetDevice(ctx->device));
+    return launch_validate(ctx, ctx->main, L->v, static_cast<const uint8_t*>(d_in), d_ulen, d_status);
+}
+
+int b2c_snappy_decompress_verify_dev(b2c_ctx* ctx, const b2c_layout* in, const void* d_in, const b2c_layout* out,
+                                     void* d_out, const uint32_t* d_masked_crc, uint32_t* d_ulen, int32_t* d_status) {
+    if (!ctx || !in || !out || !d_status || !d_masked_crc) return B2C_E_ARG;
+    if (in->v.n != out->v.n) return set_err(ctx, B2C_E_ARG, "decompress_verify: layouts differ in message count", cudaSuccess);
+    B2C_CUDA(ctx, cudaSetDevice(ctx->device));
+    return launch_decompress_verify(ctx, ctx->main, in->v, static_cast<const uint8_t*>(d_in), out->v,
+                                    static_cast<uint8_t*>(d_out), d_masked_crc, d_ulen, d_status);
 }
 
 // ---------------------------------------------------------------------------

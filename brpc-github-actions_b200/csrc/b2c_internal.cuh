@@ -30,6 +30,7 @@ struct Lane {
     cudaStream_t stream = nullptr;
     DevBuf ws_frag;   // fragment scratch slots (compress)
     DevBuf ws_misc;   // sizes, scans, chunk remainders
+    DevBuf ws_tab;    // hash tables of the 64 KiB-fragment compressor (one 32 KiB table per resident warp)
     DevBuf d_in;      // e2e: device input arena (+ layout blob)
     DevBuf d_out;     // e2e: device output arena (+ result metadata)
     PinBuf h_in;      // e2e: pinned staging, host -> device
@@ -107,6 +108,7 @@ struct b2c_ctx {
     // reusable host arrays of the *_batch entry points (avoid page-faulting fresh vectors per call)
     std::vector<uint64_t> bp_off, tmp_off;
     std::vector<uint32_t> bp_len, tmp_cap;
+    int gtab_warps_per_sm = 16;  // B2C_GTAB_WPS: resident warps per SM of the HBM-table compressor (0 = shared-memory tables); 16 keeps all tables L2-resident
     bool small_kernels = true;  // B2C_SMALL_KERNELS=0 routes <=1 KiB bodies through the warp kernels
     int small_lpw_compress = 4, small_lpw_decompress = 8;  // bodies per warp (B2C_SMALL_LPW_C / _D: 4, 8, 16, 32)
     // tunables (environment: B2C_SLAB_MB, B2C_HOST_THREADS, B2C_TRACE)
@@ -155,6 +157,11 @@ int launch_ulen(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_
                 int32_t* d_status);
 int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint8_t* d_in, const LayoutView& out,
                       uint8_t* d_out, uint32_t* d_ulen, int32_t* d_status);
+int launch_validate(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint32_t* d_ulen,
+                    int32_t* d_status);
+int launch_decompress_verify(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint8_t* d_in,
+                             const LayoutView& out, uint8_t* d_out, const uint32_t* d_masked_crc, uint32_t* d_ulen,
+                             int32_t* d_status);
 // thread-per-message kernels for bodies <= 1 KiB (snappy_small.cu)
 int small_kernels_configure(b2c_ctx* ctx);
 int launch_compress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint8_t* scratch,

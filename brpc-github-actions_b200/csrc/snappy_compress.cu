@@ -22,6 +22,8 @@
 // Fragment outputs land in per-fragment scratch slots; a second pass sizes the
 // messages, a device scan places them, and a gather kernel writes
 // varint32(N) || fragments back to back (snappy.cc:878-881).
+#include <algorithm>
+
 #include "b2c_internal.cuh"
 
 namespace b2c {
@@ -258,6 +260,37 @@ __global__ void __launch_bounds__(256) snappy_compress_fragments_kernel(Compress
     if (lane == 0) P.frag_clen[f] = clen;
 }
 
+// Same algorithm with the hash table in HBM/L2 instead of shared memory: used for 64 KiB
+// fragments, whose 32 KiB tables allow only 6 resident warps per SM in shared memory.  There the
+// warp spends its time waiting on dependent loads of the INPUT (L2 latency), so giving up the
+// table's shared-memory latency for 5-10x more resident warps is the better trade (measured on
+// C5/words: 82 ms -> see DESIGN.md).  Persistent warps, one private 32 KiB table each.
+__global__ void __launch_bounds__(256) snappy_compress_fragments_gtab_kernel(CompressParams P, uint16_t* gtab) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const uint32_t total = gridDim.x * (blockDim.x >> 5);
+    uint16_t* table = gtab + (size_t)gw * 16384;
+    for (uint32_t w = gw; w < P.n_list; w += total) {
+        const uint32_t f = P.frag_list ? P.frag_list[w] : w;
+        const uint32_t m = P.frag_msg ? P.frag_msg[f] : f;
+        const uint32_t k = P.frag_first ? f - P.frag_first[m] : 0u;
+        const uint32_t mlen = P.len[m];
+        const uint32_t n = min(kFragBytes, mlen - k * kFragBytes);
+        uint32_t tsize = 256;
+        while (tsize < 16384u && tsize < n) tsize <<= 1;
+        {
+            uint4* t4 = reinterpret_cast<uint4*>(table);
+            for (uint32_t i = lane; i < tsize / 8; i += 32) t4[i] = make_uint4(0, 0, 0, 0);
+        }
+        __syncwarp();
+        const uint8_t* in = P.in + P.off[m] + (size_t)k * kFragBytes;
+        uint8_t* out = P.scratch + (P.frag_slot ? P.frag_slot[f] : (uint64_t)f * P.slot_stride);
+        const uint32_t clen = compress_fragment_warp(in, n, out, table, tsize, lane);
+        if (lane == 0) P.frag_clen[f] = clen;
+        __syncwarp();
+    }
+}
+
 // message sizes: varint + sum of its fragments; also each fragment's offset
 // inside its message stream.
 __global__ void snappy_message_sizes_kernel(const uint32_t* __restrict__ len, const uint32_t* __restrict__ frag_first,
@@ -440,6 +473,17 @@ int launch_compress(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t
         P.frag_clen = d_frag_clen;
         P.n_list = L.n_class[c];
         P.table_entries = class_entries[c];
+        if (c == 2 && ctx->gtab_warps_per_sm > 0) {  // 64 KiB fragments: tables in HBM/L2, many resident warps
+            const uint32_t want = (uint32_t)ctx->num_sms * (uint32_t)ctx->gtab_warps_per_sm;
+            const uint32_t warps = std::min<uint32_t>(want, (P.n_list + 7) / 8 * 8);
+            const uint32_t gblocks = (warps + 7) / 8;
+            if ((rc = ws_reserve(ctx, lane, lane.ws_tab, (size_t)gblocks * 8 * 32768))) return rc;
+            snappy_compress_fragments_gtab_kernel<<<gblocks, 256, 0, lane.stream>>>(
+                P, static_cast<uint16_t*>(lane.ws_tab.p));
+            ctx->launches++;
+            B2C_CUDA(ctx, cudaGetLastError());
+            continue;
+        }
         const uint32_t wpb = class_warps[c];
         const uint32_t blocks = (P.n_list + wpb - 1) / wpb;
         const size_t smem = (size_t)wpb * class_entries[c] * 2;

@@ -17,6 +17,8 @@
 // like IncrementalCopy (snappy.cc:98-103).  Small messages are decoded into a
 // per-warp shared-memory buffer (back-references resolve at shared-memory
 // latency) and flushed coalesced; large ones decode straight into HBM.
+#include <algorithm>
+
 #include "b2c_internal.cuh"
 
 namespace b2c {
@@ -235,7 +237,7 @@ struct ScanOut {
         if (!act) return;
         const uint32_t k0 = out_pos >> 16;
         if (len && ((out_pos + len - 1) >> 16) != k0) bad = 1;
-        if ((out_pos & 0xffffu) == 0 && k0 > 0 && k0 < nblk) blk_ip[k0] = at;
+        if (blk_ip && (out_pos & 0xffffu) == 0 && k0 > 0 && k0 < nblk) blk_ip[k0] = at;
         if (kind != 0 && offset > (out_pos & 0xffffu)) bad = 1;
     }
     __device__ __forceinline__ uint8_t ld(uint32_t) const { return 0; }
@@ -602,6 +604,73 @@ __global__ void snappy_ulen_kernel(const uint8_t* __restrict__ in, const uint64_
     const uint32_t k = read_preamble(in + off[m], len[m], &v);
     ulen[m] = k ? v : 0;
     if (status) status[m] = k ? B2C_OK : B2C_CORRUPT;
+}
+
+// IsValidCompressed for a batch: the batched decoder's parse + checks, no data movement.
+__global__ void __launch_bounds__(256) snappy_validate_kernel(const uint8_t* __restrict__ in,
+                                                              const uint64_t* __restrict__ off,
+                                                              const uint32_t* __restrict__ len, uint32_t n_msgs,
+                                                              uint32_t* __restrict__ ulen, int32_t* __restrict__ status) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t wib = threadIdx.x >> 5;
+    const uint32_t m = blockIdx.x * (blockDim.x >> 5) + wib;
+    if (m >= n_msgs) return;
+    const uint8_t* src = in + off[m];
+    const uint32_t n = len[m];
+    uint32_t expected = 0;
+    const uint32_t k = read_preamble(src, n, &expected);
+    int st = B2C_CORRUPT;
+    if (k) {
+        ScanOut so{nullptr, 0u, 0u};
+        BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * 1024);
+        st = decode_message_batched(src, n, k, so, expected, lane, sc);
+    }
+    if (lane == 0) {
+        status[m] = st;
+        if (ulen) ulen[m] = k ? expected : 0;
+    }
+}
+
+// verify step of b2c_snappy_decompress_verify_dev
+__global__ void snappy_verify_crc_kernel(const uint32_t* __restrict__ crc, const uint32_t* __restrict__ masked_want,
+                                         const uint32_t* __restrict__ ulen, const uint32_t* __restrict__ cap,
+                                         int32_t* __restrict__ status, uint32_t n) {
+    const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= n || status[m] != B2C_OK) return;
+    const uint32_t c = crc[m];
+    const uint32_t masked = ((c >> 15) | (c << 17)) + 0xa282ead8u;  // crc32c::Mask, crc32c.h:38-41
+    if (ulen[m] != cap[m] || masked != masked_want[m]) status[m] = B2C_CRC_MISMATCH;
+}
+
+int launch_validate(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint32_t* d_ulen,
+                    int32_t* d_status) {
+    if (L.n == 0) return B2C_OK;
+    snappy_validate_kernel<<<(L.n + 7) / 8, 256, 8 * 1024, lane.stream>>>(d_in, L.d_off, L.d_len, L.n, d_ulen, d_status);
+    ctx->launches++;
+    B2C_CUDA(ctx, cudaGetLastError());
+    return B2C_OK;
+}
+
+int launch_decompress_verify(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint8_t* d_in, const LayoutView& out,
+                             uint8_t* d_out, const uint32_t* d_masked_crc, uint32_t* d_ulen, int32_t* d_status) {
+    if (in.n == 0) return B2C_OK;
+    // temporaries after whatever the decoder itself keeps in ws_misc
+    // (the decoder keeps block offsets / modes at the start of ws_misc, the CRC launcher its chunk remainders)
+    const size_t dec_words = std::max((size_t)out.n_frags + 2 * (size_t)out.n, (size_t)out.n_chunks) + 16;
+    int rc = ws_reserve(ctx, lane, lane.ws_misc, (dec_words + 2 * (size_t)in.n + 16) * 4);
+    if (rc) return rc;
+    uint32_t* tmp = static_cast<uint32_t*>(lane.ws_misc.p) + dec_words;
+    uint32_t* d_crc = tmp;
+    uint32_t* d_ul = d_ulen ? d_ulen : tmp + in.n;
+    if ((rc = launch_decompress(ctx, lane, in, d_in, out, d_out, d_ul, d_status))) return rc;
+    // the CRC launcher parks multi-chunk remainders at the start of ws_misc: the decoder is done with it by now
+    if ((rc = launch_crc32c(ctx, lane, out, d_out, nullptr, d_crc))) return rc;
+    snappy_verify_crc_kernel<<<(in.n + 255) / 256, 256, 0, lane.stream>>>(d_crc, d_masked_crc, d_ul, out.d_len, d_status,
+                                                                        in.n);
+    ctx->launches++;
+    B2C_CUDA(ctx, cudaGetLastError());
+    return B2C_OK;
 }
 
 int launch_ulen(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint32_t* d_ulen,

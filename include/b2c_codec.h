@@ -39,6 +39,7 @@ extern "C" {
 #define B2C_OK 0
 #define B2C_CORRUPT 1   /* malformed snappy stream: reference returns false (snappy.cc:867) */
 #define B2C_TOO_SMALL 2 /* output slot smaller than the stream's uncompressed length */
+#define B2C_CRC_MISMATCH 3 /* b2c_snappy_decompress_verify_dev: decoded fine, checksum differs */
 
 #define B2C_E_CUDA (-1)     /* CUDA runtime/driver failure (text in b2c_last_error) */
 #define B2C_E_ARG (-2)      /* invalid argument */
@@ -195,6 +196,25 @@ int b2c_snappy_uncompressed_length_dev(b2c_ctx* ctx, const b2c_layout* in_layout
 int b2c_snappy_decompress_dev(b2c_ctx* ctx, const b2c_layout* in_layout, const void* d_in,
                               const b2c_layout* out_layout, void* d_out, uint32_t* d_ulen,
                               int32_t* d_status);
+
+/* butil::snappy::IsValidCompressed(Source*) per stream (snappy.cc:1252-1291, the
+ * SnappyDecompressionValidator writer): d_status[i] = B2C_OK iff the reference would
+ * accept stream i, B2C_CORRUPT otherwise.  Nothing is decoded; d_ulen (nullable)
+ * receives the preamble's length. */
+int b2c_snappy_validate_dev(b2c_ctx* ctx, const b2c_layout* in_layout, const void* d_in, uint32_t* d_ulen,
+                            int32_t* d_status);
+
+/* Decompress and verify in one call — the unit of the snappy framing format's
+ * compressed chunk (src/butil/third_party/snappy/framing_format.txt:39-59,82-92):
+ * d_status[i] = B2C_OK iff stream i decodes (as b2c_snappy_decompress_dev) AND
+ * butil::crc32c::Mask(crc32c::Value(decoded bytes)) == d_masked_crc[i]; a stream that
+ * decodes but whose checksum differs gets B2C_CRC_MISMATCH.  Output slots must be sized
+ * exactly (out_layout.len[i] == uncompressed length, see
+ * b2c_snappy_uncompressed_length_dev); a stream shorter than its slot also reports
+ * B2C_CRC_MISMATCH. */
+int b2c_snappy_decompress_verify_dev(b2c_ctx* ctx, const b2c_layout* in_layout, const void* d_in,
+                                     const b2c_layout* out_layout, void* d_out, const uint32_t* d_masked_crc,
+                                     uint32_t* d_ulen, int32_t* d_status);
 
 /* ---- host (end-to-end) entry points ------------------------------------- */
 /* Message i is the concatenation of segs[seg_begin[i] .. seg_begin[i+1]) — the

@@ -352,3 +352,111 @@ def test_c2_full_size_roundtrip_properties(codec, cpu):
     for j, i in enumerate(idx):
         assert_bytes_equal(packed[int(out_off[i]):int(out_off[i + 1])].tobytes(),
                            w_out[int(w_off[j]):int(w_off[j]) + int(w_len[j])].tobytes(), f"C2 full msg {i}")
+
+
+# ---------------------------------------------------------------- validate / decompress+verify / large shapes
+def test_validate_agrees_with_oracle(codec, cpu, golden):
+    rng = np.random.default_rng(5)
+    base = [cpu.compress(O.corpus(k, n, i)) for k in ("words", "az09", "rand62") for i, n in enumerate((40, 300, 5000, 200000))]
+    streams = [bytes.fromhex(e["stream"]) for e in golden["malformed"] if e["stream"]] + base
+    for t in range(600):
+        z = bytearray(base[t % len(base)])
+        if t % 3 == 0:
+            z[int(rng.integers(0, len(z)))] ^= 1 << int(rng.integers(0, 8))
+        elif t % 3 == 1:
+            del z[int(rng.integers(1, len(z))):]
+        else:
+            z += bytes(rng.integers(0, 256, 2, dtype=np.uint8))
+        streams.append(bytes(z))
+    arena, off, ln = pack_tight(streams)
+    st, ulen = codec.validate(arena, off, ln)
+    for i, s in enumerate(streams):
+        assert (st[i] == 0) == cpu.is_valid(s), (i, s[:24].hex())
+        v = O.port().ulen_lenient(s)
+        assert int(ulen[i]) == (v or 0)
+
+
+def test_decompress_verify_masked_crc(codec, cpu):
+    # snappy framing's chunk check: masked CRC-32C of the uncompressed data (framing_format.txt:39-59)
+    msgs = [O.corpus("words", n, i).tobytes() for i, n in enumerate((0, 1, 100, 1024, 4096, 65536, 70000, 300000))]
+    streams = [cpu.compress(m) for m in msgs]
+    masked = np.array([cpu.mask(cpu.crc32c(m)) for m in msgs], dtype=np.uint32)
+    arena, off, ln = pack_tight(streams)
+    caps = np.array([len(m) for m in msgs], dtype=np.uint32)
+    o_off = np.zeros(len(caps), dtype=np.uint64)
+    o_off[1:] = np.cumsum(caps[:-1].astype(np.uint64))
+    out, st = codec.decompress_verify(arena, off, ln, o_off, caps, masked)
+    assert (st == 0).all()
+    for i, m in enumerate(msgs):
+        assert out[int(o_off[i]):int(o_off[i]) + len(m)].tobytes() == m
+    bad = masked.copy()
+    bad[3] ^= 1
+    bad[6] += 7
+    _, st = codec.decompress_verify(arena, off, ln, o_off, caps, bad)
+    assert [int(x) for x in st] == [0, 0, 0, 3, 0, 0, 3, 0]
+    # a corrupt stream stays "corrupt", not "crc mismatch"
+    streams[4] = streams[4][:-3]
+    arena, off, ln = pack_tight(streams)
+    _, st = codec.decompress_verify(arena, off, ln, o_off, caps, masked)
+    assert st[4] == 1 and st[5] == 0
+
+
+def test_c4_shape_mixed_sizes_parity(codec, cpu):
+    # BASELINE configs[3] (scaled): lognormal 64 B - 4 MiB mix — every size class and both decode modes in one batch
+    rng = np.random.default_rng(2024)
+    ln = np.clip(np.round(np.exp(rng.normal(np.log(16384), 2.0, 3000))), 64, 4 << 20).astype(np.uint32)
+    arena, off, ln = O.corpus_batch("words", ln, first_index=31)
+    crc = codec.crc32c(arena, off, ln)
+    want_crc, _ = cpu.batch_crc32c(arena, off, ln, threads=8)
+    assert (crc == want_crc).all()
+    packed, out_off = _check_compress(codec, cpu, arena, off, ln, "C4 mix")
+    back, ulen, st = codec.decompress(packed, out_off[:-1], np.diff(out_off).astype(np.uint32), off, ln)
+    assert (st == 0).all() and (ulen == ln).all()
+    for i in range(len(ln)):
+        a, b = int(off[i]), int(off[i]) + int(ln[i])
+        assert_bytes_equal(back[a:b].tobytes(), arena[a:b].tobytes(), f"C4 back {i} n={int(ln[i])}")
+
+
+@pytest.mark.parametrize("kind", ["words", "az09", "rand62"])
+def test_c5_shape_fragments_decompress_verify(codec, cpu, kind):
+    # BASELINE configs[4] (scaled): independent 64 KiB fragments, decompress + CRC32C verify
+    n = 2048
+    arena, off, ln = O.corpus_batch(kind, np.full(n, 65536, dtype=np.uint32), first_index=7)
+    packed, out_off = codec.compress(arena, off, ln)
+    crc = codec.crc32c(arena, off, ln)
+    masked = np.array([cpu.mask(int(c)) for c in crc], dtype=np.uint32)
+    out, st = codec.decompress_verify(packed, out_off[:-1], np.diff(out_off).astype(np.uint32), off, ln, masked)
+    assert (st == 0).all()
+    assert out[:int(off[-1]) + 65536].tobytes() == arena[:int(off[-1]) + 65536].tobytes()
+    w_out, w_off, w_len, _ = cpu.batch_compress(arena, off[:64], ln[:64], threads=8)
+    for i in range(64):
+        assert packed[int(out_off[i]):int(out_off[i + 1])].tobytes() == w_out[int(w_off[i]):int(w_off[i]) + int(w_len[i])].tobytes()
+
+
+def test_large_foreign_stream_falls_back_to_whole_message_decode(codec):
+    # a > 64 KiB stream whose copies reach across 64 KiB output boundaries (legal, but never produced by the
+    # reference compressor): the boundary scan must refuse to split it and the result must still be exact
+    block = O.corpus("rand62", 40000, 1).tobytes()
+    def literal(b):
+        return bytes([62 << 2]) + (len(b) - 1).to_bytes(3, "little") + b
+    def copy4(offset, length):
+        return bytes([3 | ((length - 1) << 2)]) + offset.to_bytes(4, "little")
+    body = literal(block)
+    total = len(block)
+    for _ in range(4000):          # 4000 x 64-byte copies from 40000 bytes back: crosses 64 KiB boundaries
+        body += copy4(40000, 64)
+        total += 64
+    pre = bytearray()
+    v = total
+    while v >= 128:
+        pre.append((v & 0x7f) | 0x80)
+        v >>= 7
+    pre.append(v)
+    s = bytes(pre) + body
+    ok, want = O.port().uncompress(s)
+    assert ok and len(want) == total
+    out, o_off, ulen, status = _decompress(codec, [s, s])
+    assert list(status) == [0, 0]
+    assert_bytes_equal(out[:total].tobytes(), want, "foreign large")
+    st, _ = codec.validate(*pack_tight([s]))
+    assert st[0] == 0
