@@ -56,7 +56,7 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "100", "-i", str(device)], stdout=self.f, stderr=subprocess.DEVNULL)
+                                       "-lms", "20", "-i", str(device)], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
 
@@ -237,12 +237,12 @@ def run_ours(args, rank, local_rank, world):
                arena[int(off[i]):int(off[i]) + int(ln[i])].tobytes() for i in idx), "round-trip parity"
     del packed, back
 
+    sampler = ClockSampler(local_rank) if rank == 0 else None  # samples over warm-up + timed steps (all under load)
     for _ in range(args.warmup):
         step()
     codec.sync()
     if dist is not None:
         dist.barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
     codec.prof_enable(True)
     launches0 = codec.launch_count
     e0, e1 = codec.event(), codec.event()
@@ -337,7 +337,10 @@ def run_ours(args, rank, local_rank, world):
                             "iovecs (1-2 blocks per body), outputs = page-locked host buffers"},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "snappy_compress_small_kernel" if int(ln.max()) <= 1024 else "snappy_compress_*_kernel (all size classes of the batch)", "bound": "hbm", "achieved": achieved,
-                         "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                         "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                         # dram__bytes_read+write of this kernel from the committed ncu --set full capture of this
+                         # very workload (profiles/r1_ncu_full_key_metrics.txt); unknown for other workloads
+                         "traffic": 1618794000 if (args.workload, args.corpus, n_msgs) == ("c2", "words", N_MSGS) else None,
                          "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                          "note": "byte-exact greedy LZ77 is a serial dependency chain per fragment: latency/issue bound, "
                                  "not HBM bound (see DESIGN.md)"},

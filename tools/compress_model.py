@@ -1,5 +1,5 @@
 # Lane-level Python model of compress_fragment_warp (mirrors snappy_compress.cu) checked against the oracle.
-import sys; sys.path.insert(0,'/root/repo')
+import sys; import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from oracle import oracle as O
 M32=0xffffffff

@@ -1,5 +1,5 @@
 # numeric model of the quad-per-chunk CRC32C decomposition (validates the algebra before CUDA)
-import sys; sys.path.insert(0,'/root/repo')
+import sys; import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from oracle import oracle as O
 POLY=0x82F63B78

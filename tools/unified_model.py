@@ -1,5 +1,5 @@
 # Python model of the unified (probe/copy-tail) per-thread loop used by the thread-per-message kernel.
-import sys; sys.path.insert(0,'/root/repo')
+import sys; import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from oracle import oracle as O
 from compress_model import hashb, emit_literal, emit_copy, oracle_frag
