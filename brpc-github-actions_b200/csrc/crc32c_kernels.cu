@@ -86,14 +86,59 @@ int crc_tables_init(b2c_ctx* ctx) {
 // ---------------------------------------------------------------------------
 // device code
 // ---------------------------------------------------------------------------
+// Shared-memory image.  The replicated Z^64 tables sit in two 64 KiB regions whose SHARED
+// address is 64 KiB-aligned: entry (table k, byte b, lane l) lives at
+//     region(k >> 1) + (b << 8) + (k & 1) * 128 + l * 4
+// so one PRMT builds the whole address — it drops state byte k into address bits 8..15 next to a
+// per-lane constant (region base | lane * 4) — and the table's +128 is the LDS immediate:
+// 2 instructions per lookup instead of the 4-5 of shift/mask/scale/add indexing.
 struct CrcSmem {
-    uint32_t A[4][256][32];  // replicated Z^64 tables: 128 KiB
-    uint32_t S[3][4][256];   // Z^4, Z^16, Z^32: 12 KiB
+    uint32_t S[3][4][256];   // Z^4, Z^16, Z^32: 12 KiB (plain layout, rarely used)
 };
+constexpr uint32_t kCrcRegion = 65536;
+// dynamic smem: S tables | up to 64 KiB of alignment slack | 2 regions
+constexpr size_t kCrcSmemBytes = sizeof(CrcSmem) + kCrcRegion + 2 * kCrcRegion;
 
-__device__ __forceinline__ uint32_t apply_A(const CrcSmem& sm, uint32_t x, uint32_t lane) {
-    return sm.A[0][x & 0xff][lane] ^ sm.A[1][(x >> 8) & 0xff][lane] ^ sm.A[2][(x >> 16) & 0xff][lane] ^
-           sm.A[3][x >> 24][lane];
+__device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
+    uint32_t v;
+    asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u32_p128(uint32_t saddr) {
+    uint32_t v;
+    asm("ld.shared.u32 %0, [%1+128];" : "=r"(v) : "r"(saddr));
+    return v;
+}
+
+struct CrcLane {
+    uint32_t reg0;   // shared address of region 0 | lane * 4   (bits 8..15 are zero)
+    uint32_t reg1;   // same for region 1
+    uint32_t stage;  // shared address of this thread's first staging slot (0: no room, load directly)
+};
+constexpr uint32_t kCrcStages = 3;
+constexpr uint32_t kCrcStageBytes = 1024 * 16;  // one 16-byte slot per thread of the CTA
+
+__device__ __forceinline__ void cp_async16(uint32_t saddr, const void* g) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t saddr) {
+    uint4 r;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(saddr));
+    return r;
+}
+
+// Z^64 applied to a 32-bit state: 4 conflict-free lookups
+__device__ __forceinline__ uint32_t apply_A(const CrcLane& cl, uint32_t x) {
+    const uint32_t t0 = lds_u32(__byte_perm(x, cl.reg0, 0x7604));
+    const uint32_t t1 = lds_u32_p128(__byte_perm(x, cl.reg0, 0x7614));
+    const uint32_t t2 = lds_u32(__byte_perm(x, cl.reg1, 0x7624));
+    const uint32_t t3 = lds_u32_p128(__byte_perm(x, cl.reg1, 0x7634));
+    return t0 ^ t1 ^ t2 ^ t3;
 }
 template <int D>
 __device__ __forceinline__ uint32_t apply_S(const CrcSmem& sm, uint32_t x) {
@@ -112,7 +157,8 @@ __device__ __forceinline__ uint4 ldg128_stream(const uint8_t* p) {
 }
 
 // S(l, p[0..L)) computed by the 4 lanes of one quad; result valid on all 4 lanes.
-__device__ uint32_t crc_chunk_quad(const CrcSmem& sm, const uint8_t* p, uint32_t L, uint32_t l, uint32_t lane) {
+__device__ uint32_t crc_chunk_quad(const CrcSmem& sm, const CrcLane& cl, const uint8_t* p, uint32_t L, uint32_t l,
+                                   uint32_t lane) {
     const uint32_t q = lane & 3;
     const uint32_t qbase = lane & ~3u;
     const uint32_t qmask = 0xFu << qbase;
@@ -125,16 +171,50 @@ __device__ uint32_t crc_chunk_quad(const CrcSmem& sm, const uint8_t* p, uint32_t
     const uint32_t rows = L >> 6;
     if (rows) {
         const uint8_t* lp = p + q * 16;
-        uint4 w = ldg128_stream(lp);
-        uint32_t h0 = w.x, h1 = w.y, h2 = w.z, h3 = w.w;
-        if (q == 0) h0 ^= l;
+        uint32_t h0, h1, h2, h3;
+        if (cl.stage) {
+            // The rows come through a private 3-deep cp.async ring in shared memory (16 bytes per
+            // stage per thread, L2 -> smem, no L1 allocation and no registers held while in flight):
+            // with 192 KiB of tables only ~20 KiB of L1 is left, too little to keep enough plain
+            // loads outstanding for HBM speed.
+            const uint32_t s0 = cl.stage;
+#pragma unroll
+            for (uint32_t s = 0; s < kCrcStages; s++) {
+                if (s < rows) cp_async16(s0 + s * kCrcStageBytes, lp + (size_t)s * 64);
+                cp_async_commit();
+            }
+            cp_async_wait<kCrcStages - 1>();
+            uint4 w = lds128(s0);
+            h0 = w.x; h1 = w.y; h2 = w.z; h3 = w.w;
+            if (q == 0) h0 ^= l;
+            if (kCrcStages < rows) cp_async16(s0, lp + (size_t)kCrcStages * 64);
+            cp_async_commit();
+            uint32_t slot = 1;
+            for (uint32_t it = 1; it < rows; it++) {
+                cp_async_wait<kCrcStages - 1>();
+                const uint32_t sa = s0 + slot * kCrcStageBytes;
+                w = lds128(sa);
+                h0 = apply_A(cl, h0) ^ w.x;
+                h1 = apply_A(cl, h1) ^ w.y;
+                h2 = apply_A(cl, h2) ^ w.z;
+                h3 = apply_A(cl, h3) ^ w.w;
+                if (it + kCrcStages < rows) cp_async16(sa, lp + (size_t)(it + kCrcStages) * 64);
+                cp_async_commit();
+                slot = slot + 1 == kCrcStages ? 0 : slot + 1;
+            }
+            cp_async_wait<0>();
+        } else {
+            uint4 w = ldg128_stream(lp);
+            h0 = w.x; h1 = w.y; h2 = w.z; h3 = w.w;
+            if (q == 0) h0 ^= l;
 #pragma unroll 4
-        for (uint32_t it = 1; it < rows; it++) {
-            w = ldg128_stream(lp + (size_t)it * 64);
-            h0 = apply_A(sm, h0, lane) ^ w.x;
-            h1 = apply_A(sm, h1, lane) ^ w.y;
-            h2 = apply_A(sm, h2, lane) ^ w.z;
-            h3 = apply_A(sm, h3, lane) ^ w.w;
+            for (uint32_t it = 1; it < rows; it++) {
+                w = ldg128_stream(lp + (size_t)it * 64);
+                h0 = apply_A(cl, h0) ^ w.x;
+                h1 = apply_A(cl, h1) ^ w.y;
+                h2 = apply_A(cl, h2) ^ w.z;
+                h3 = apply_A(cl, h3) ^ w.w;
+            }
         }
         // fold the 4 columns of this lane: g = S(0, 16 raw bytes)
         uint32_t g = apply_S<0>(sm, h0);
@@ -195,15 +275,28 @@ struct CrcParams {
 __global__ void __launch_bounds__(1024, 1) crc32c_chunks_kernel(CrcParams P) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     CrcSmem& sm = *reinterpret_cast<CrcSmem*>(smem_raw);
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem_raw);
+    const uint32_t region0 = (sbase + (uint32_t)sizeof(CrcSmem) + kCrcRegion - 1) & ~(kCrcRegion - 1);
     {
+        // P.tabA is [k][b][lane]; scatter 16 bytes (4 lanes) at a time into the interleaved regions
         const uint4* srcA = reinterpret_cast<const uint4*>(P.tabA);
-        uint4* dstA = reinterpret_cast<uint4*>(&sm.A[0][0][0]);
-        for (uint32_t i = threadIdx.x; i < sizeof(sm.A) / 16; i += blockDim.x) dstA[i] = srcA[i];
+        uint8_t* gen0 = smem_raw + (region0 - sbase);
+        for (uint32_t i = threadIdx.x; i < 4 * 256 * 8; i += blockDim.x) {
+            const uint32_t k = i >> 11, b = (i >> 3) & 255, l4 = i & 7;
+            *reinterpret_cast<uint4*>(gen0 + (k >> 1) * kCrcRegion + (b << 8) + (k & 1) * 128 + l4 * 16) = srcA[i];
+        }
         const uint4* srcS = reinterpret_cast<const uint4*>(P.small);
         uint4* dstS = reinterpret_cast<uint4*>(&sm.S[0][0][0]);
         for (uint32_t i = threadIdx.x; i < sizeof(sm.S) / 16; i += blockDim.x) dstS[i] = srcS[i];
     }
     __syncthreads();
+    CrcLane cl;
+    cl.reg0 = region0 | ((threadIdx.x & 31) << 2);
+    cl.reg1 = cl.reg0 + kCrcRegion;
+    {   // staging ring in the alignment slack between the small tables and region 0
+        const uint32_t slack0 = (sbase + (uint32_t)sizeof(CrcSmem) + 15u) & ~15u;
+        cl.stage = region0 - slack0 >= kCrcStages * kCrcStageBytes ? slack0 + threadIdx.x * 16 : 0u;
+    }
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t quads_per_cta = blockDim.x >> 2;
     const uint32_t total_quads = gridDim.x * quads_per_cta;
@@ -219,7 +312,7 @@ __global__ void __launch_bounds__(1024, 1) crc32c_chunks_kernel(CrcParams P) {
         const bool single = len <= kCrcChunk;
         uint32_t l = 0;
         if (k == 0) l = (P.init ? P.init[m] : 0u) ^ 0xffffffffu;
-        l = crc_chunk_quad(sm, P.data + P.off[m] + begin, L, l, lane);
+        l = crc_chunk_quad(sm, cl, P.data + P.off[m] + begin, L, l, lane);
         if ((lane & 3) == 0) {
             if (single) P.crc[m] = l ^ 0xffffffffu;
             else P.rem[c] = l;
@@ -283,7 +376,7 @@ int launch_crc32c(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* 
     if (L.n == 0) return B2C_OK;
     if (!ctx->crc_attr_done) {  // per device: a ctx is bound to one
         B2C_CUDA(ctx, cudaFuncSetAttribute(crc32c_chunks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)sizeof(CrcSmem)));
+                                           (int)kCrcSmemBytes));
         ctx->crc_attr_done = true;
     }
     uint32_t* d_rem = nullptr;
@@ -308,7 +401,7 @@ int launch_crc32c(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* 
     uint32_t grid = (L.n_chunks + quads_per_cta - 1) / quads_per_cta;
     if (grid > (uint32_t)ctx->num_sms) grid = ctx->num_sms;
     prof_mark(ctx, lane, B2C_PROF_CRC32C);
-    crc32c_chunks_kernel<<<grid, 1024, sizeof(CrcSmem), lane.stream>>>(P);
+    crc32c_chunks_kernel<<<grid, 1024, kCrcSmemBytes, lane.stream>>>(P);
     prof_mark(ctx, lane, B2C_PROF_CRC32C);
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
@@ -376,7 +469,7 @@ extern "C" int b2c_crc32c_noalloc_dev(b2c_ctx* ctx, const b2c_layout* layout, co
     if (L.n == 0) return B2C_OK;
     if (!ctx->crc_attr_done) {
         B2C_CUDA(ctx, cudaFuncSetAttribute(crc32c_chunks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)sizeof(CrcSmem)));
+                                           (int)kCrcSmemBytes));
         ctx->crc_attr_done = true;
     }
     CrcParams P;
@@ -393,7 +486,7 @@ extern "C" int b2c_crc32c_noalloc_dev(b2c_ctx* ctx, const b2c_layout* layout, co
     P.n_chunks = L.n_chunks;
     uint32_t grid = (L.n_chunks + 255) / 256;
     if (grid > (uint32_t)ctx->num_sms) grid = ctx->num_sms;
-    crc32c_chunks_kernel<<<grid, 1024, sizeof(CrcSmem), ctx->main.stream>>>(P);
+    crc32c_chunks_kernel<<<grid, 1024, kCrcSmemBytes, ctx->main.stream>>>(P);
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
     if (L.n_multi) {
