@@ -295,15 +295,34 @@ def run_ours(args, rank, local_rank, world):
         assert not status.any()
         bytes_h2d, bytes_d2h = h2d, d2h
 
-    e2e_step()  # warm-up: sizes the pinned staging and device arenas
-    if dist is not None:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-    e2e_s = time.perf_counter() - t0
-    if dist is not None:
-        e2e_s = brpc_b200.sharding.max_over_ranks(e2e_s, device="cuda")
+    def time_e2e():
+        nonlocal bytes_h2d, bytes_d2h
+        e2e_step()  # warm-up: sizes the pinned staging and device arenas
+        if dist is not None:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            dt = brpc_b200.sharding.max_over_ranks(dt, device="cuda")
+        return dt, bytes_h2d, bytes_d2h
+
+    # (a) the headline: input blocks in ordinary pageable memory (what IOBuf blocks are today); host threads gather
+    #     them into pinned staging and the copy engines move the slabs
+    e2e_s, bytes_h2d, bytes_d2h = time_e2e()
+    # (b) for the record: blocks in page-locked memory + B2C_OPT_INPUT_PINNED (the device gathers them over PCIe
+    #     itself).  On this box kernel reads of host memory reach ~35 GB/s against ~55 GB/s for the copy engines,
+    #     so (a) stays the default path.
+    p_arena = codec.pinned(len(arena))
+    p_arena[:] = arena
+    segs_pageable = segs.copy()
+    segs[:, 0] = segs[:, 0] - np.uint64(arena.ctypes.data) + np.uint64(p_arena.ctypes.data)
+    cache.clear()
+    codec.set_option(codec.OPT_INPUT_PINNED, 1)
+    e2e_zero_copy_s, _, _ = time_e2e()
+    codec.set_option(codec.OPT_INPUT_PINNED, 0)
+    segs[:] = segs_pageable
     first = b"".join(arena[int(off[i]):int(off[i]) + int(ln[i])].tobytes() for i in range(min(4, n_msgs)))
     assert h_back[:len(first)].tobytes() == first
 
@@ -334,7 +353,9 @@ def run_ours(args, rank, local_rank, world):
             "e2e": {"value": payload * world * e2e_steps / e2e_s / 1e9, "unit": "GB/s",
                     "h2d_bytes_per_step": int(bytes_h2d), "d2h_bytes_per_step": int(bytes_d2h), "steps": e2e_steps,
                     "path": "b2c_crc32c_batch + b2c_snappy_compress_batch + b2c_snappy_decompress_batch; inputs = pageable host "
-                            "iovecs (1-2 blocks per body), outputs = page-locked host buffers"},
+                            "iovecs (1-2 blocks per body) gathered into pinned staging by host threads; outputs = "
+                            "page-locked host buffers",
+                    "pinned_inputs_device_gather_value": payload * world * e2e_steps / e2e_zero_copy_s / 1e9},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "snappy_compress_small_kernel" if int(ln.max()) <= 1024 else "snappy_compress_*_kernel (all size classes of the batch)", "bound": "hbm", "achieved": achieved,
                          "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,

@@ -37,6 +37,7 @@ SYMBOLS = {
     "b2c_ctx_device": (C.c_int, [_vp]),
     "b2c_ctx_stream": (_vp, [_vp]),
     "b2c_ctx_sync": (C.c_int, [_vp]),
+    "b2c_ctx_set_option": (C.c_int, [_vp, C.c_int, C.c_int]),
     "b2c_ctx_launch_count": (C.c_uint64, [_vp]),
     "b2c_dev_alloc": (C.c_int, [_vp, C.c_size_t, C.POINTER(_vp)]),
     "b2c_dev_free": (C.c_int, [_vp, _vp]),
@@ -261,6 +262,11 @@ class Codec:
             raise B2CError(f"libb2c error {rc}: {msg}")
 
     # ---- plumbing ----------------------------------------------------------
+    OPT_INPUT_PINNED = 1
+
+    def set_option(self, option: int, value: int):
+        self._check(self.lib.b2c_ctx_set_option(self.ctx, option, value))
+
     def sync(self):
         self._check(self.lib.b2c_ctx_sync(self.ctx))
 

@@ -358,6 +358,68 @@ void LayoutPlan::bind(const uint8_t* d, LayoutView* out) const {
     out->d_multi_list = has_chunk_arrays ? reinterpret_cast<const uint32_t*>(d + o_multi) : nullptr;
 }
 
+// Zero-copy input: one warp per message walks the message's blocks in page-locked HOST memory
+// (device-visible under UVA) and writes them, concatenated, into the device arena.
+__global__ void __launch_bounds__(256) gather_host_segments_kernel(const b2c_iovec* __restrict__ segs,
+                                                                   const uint32_t* __restrict__ seg_begin,
+                                                                   const uint64_t* __restrict__ off, uint32_t cnt,
+                                                                   uint8_t* __restrict__ d_in) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warps = gridDim.x * (blockDim.x >> 5);
+    for (uint32_t m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); m < cnt; m += warps) {
+        uint8_t* dst = d_in + off[m];
+        for (uint32_t q = seg_begin[m]; q < seg_begin[m + 1]; q++) {
+            const uint8_t* src = static_cast<const uint8_t*>(segs[q].iov_base);
+            const uint32_t len = (uint32_t)segs[q].iov_len;
+            const uint32_t rel = (uint32_t)((reinterpret_cast<uintptr_t>(src) ^ reinterpret_cast<uintptr_t>(dst)) & 15);
+            if (rel == 0) {
+                // same phase modulo 16 (the arena is laid out so that a message's first block always is):
+                // every host byte crosses PCIe exactly once, in 16-byte pieces
+                uint32_t head = (16u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15)) & 15u;
+                if (head > len) head = len;
+                if (lane < head) dst[lane] = src[lane];
+                const uint32_t vecs = (len - head) >> 4;
+                const uint4* s4 = reinterpret_cast<const uint4*>(src + head);
+                uint4* d4 = reinterpret_cast<uint4*>(dst + head);
+                for (uint32_t i = lane; i < vecs; i += 32) d4[i] = s4[i];
+                const uint32_t done = head + (vecs << 4);
+                if (lane < len - done) dst[done + lane] = src[done + lane];
+            } else if ((rel & 3) == 0) {
+                uint32_t head = (4u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 3)) & 3u;
+                if (head > len) head = len;
+                if (lane < head) dst[lane] = src[lane];
+                const uint32_t words = (len - head) >> 2;
+                const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src + head);
+                uint32_t* d32 = reinterpret_cast<uint32_t*>(dst + head);
+                for (uint32_t i = lane; i < words; i += 32) d32[i] = s32[i];
+                const uint32_t done = head + (words << 2);
+                if (lane < len - done) dst[done + lane] = src[done + lane];
+            } else {
+                // word stores aligned to the destination, words assembled from the unaligned source
+                uint32_t head = (4u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 3)) & 3u;
+                if (head > len) head = len;
+                if (lane < head) dst[lane] = src[lane];
+                const uint32_t words = (len - head) >> 2;
+                uint32_t* d32 = reinterpret_cast<uint32_t*>(dst + head);
+                for (uint32_t i = lane; i < words; i += 32) d32[i] = ld32u(src + head + 4 * (size_t)i);
+                const uint32_t done = head + (words << 2);
+                if (lane < len - done) dst[done + lane] = src[done + lane];
+            }
+            dst += len;
+        }
+    }
+}
+
+int launch_gather_host(b2c_ctx* ctx, Lane& lane, const b2c_iovec* d_segs, const uint32_t* d_seg_begin,
+                       const uint64_t* d_off, uint32_t cnt, uint8_t* d_in) {
+    if (!cnt) return B2C_OK;
+    const uint32_t blocks = std::min<uint32_t>((cnt + 7) / 8, (uint32_t)ctx->num_sms * 4);
+    gather_host_segments_kernel<<<blocks, 256, 0, lane.stream>>>(d_segs, d_seg_begin, d_off, cnt, d_in);
+    ctx->launches++;
+    B2C_CUDA(ctx, cudaGetLastError());
+    return B2C_OK;
+}
+
 static int lane_create(b2c_ctx* ctx, Lane& l) {
     B2C_CUDA(ctx, cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
     B2C_CUDA(ctx, cudaEventCreateWithFlags(&l.ev_meta, cudaEventDisableTiming));
@@ -445,6 +507,14 @@ const char* b2c_last_error(const b2c_ctx* ctx) { return ctx ? ctx->err.c_str() :
 int b2c_ctx_device(const b2c_ctx* ctx) { return ctx ? ctx->device : -1; }
 void* b2c_ctx_stream(b2c_ctx* ctx) { return ctx ? (void*)ctx->main.stream : nullptr; }
 uint64_t b2c_ctx_launch_count(const b2c_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int b2c_ctx_set_option(b2c_ctx* ctx, int option, int value) {
+    if (!ctx) return B2C_E_ARG;
+    switch (option) {
+        case B2C_OPT_INPUT_PINNED: ctx->input_pinned = value != 0; return B2C_OK;
+        default: return set_err(ctx, B2C_E_ARG, "unknown option", cudaSuccess);
+    }
+}
 
 int b2c_ctx_sync(b2c_ctx* ctx) {
     if (!ctx) return B2C_E_ARG;
@@ -728,13 +798,19 @@ int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, u
     const uint64_t target = ctx->slab_bytes;
     const uint32_t max_msgs = 1u << 18;
     Slab cur = {0, 0, 0, 0};
+    const bool zc = ctx->input_pinned;
     for (uint32_t i = 0; i < n; i++) {
-        const uint64_t a = align_up(p.len[i], 16);
+        // zero-copy: give the message the same phase modulo 16 as its first block has in host memory, so the
+        // device-side gather moves whole aligned 16-byte pieces over PCIe
+        const uint32_t skew = zc && seg_begin[i] < seg_begin[i + 1]
+                                  ? (uint32_t)(reinterpret_cast<uintptr_t>(segs[seg_begin[i]].iov_base) & 15)
+                                  : 0u;
+        const uint64_t a = align_up((uint64_t)skew + p.len[i], 16);
         if (cur.m1 > cur.m0 && (cur.bytes + a > target || cur.m1 - cur.m0 >= max_msgs)) {
             p.slabs.push_back(cur);
             cur = {i, i, 0, 0};
         }
-        p.off[i] = cur.bytes;
+        p.off[i] = cur.bytes + skew;
         cur.bytes += a;
         cur.payload += p.len[i];
         cur.m1 = i + 1;
@@ -817,6 +893,81 @@ void parallel_copy(b2c_ctx* ctx, void* dst, const void* src, uint64_t bytes) {
     });
 }
 
+// preamble-derived output slot sizes of a slab of snappy streams, read straight from the segments
+void slab_caps(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, const BatchPlan& p, const Slab& s,
+               uint32_t* caps) {
+    const uint32_t cnt = s.m1 - s.m0;
+    pool(ctx).run(threads_for((uint64_t)cnt * 256), [&](unsigned t, unsigned T) {
+        uint32_t lo = s.m0 + (uint32_t)((uint64_t)cnt * t / T), hi = s.m0 + (uint32_t)((uint64_t)cnt * (t + 1) / T);
+        for (uint32_t i = lo; i < hi; i++) {
+            uint8_t head[5];
+            size_t got = 0;
+            for (uint32_t q = seg_begin[i]; q < seg_begin[i + 1] && got < 5; q++)
+                for (size_t j = 0; j < segs[q].iov_len && got < 5; j++)
+                    head[got++] = static_cast<const uint8_t*>(segs[q].iov_base)[j];
+            uint32_t ulen = 0;
+            const int kk = b2c_snappy_read_preamble(head, got, &ulen);
+            const bool plausible = kk > 0 && (uint64_t)ulen <= ((uint64_t)p.len[i] * 64) / 3 + 64;
+            caps[i - s.m0] = plausible ? ulen : 0;
+        }
+    });
+}
+
+// One slab's way into HBM.  Device image: payload at [0, s.bytes) (messages 16-byte aligned), the
+// caller's metadata (layout blobs, ...) at meta_at.  Two modes:
+//   staged    (default): host threads gather the blocks into pinned staging, one H2D copy moves
+//                        payload + metadata;
+//   zero-copy (B2C_OPT_INPUT_PINNED): the blocks already live in page-locked memory (a pinned
+//                        IOBuf block pool); only metadata + the block list are copied and a kernel
+//                        pulls the payload over PCIe straight from the blocks.
+struct SlabIO {
+    uint8_t* stage_meta = nullptr;  // host: where the caller writes its metadata
+    uint8_t* d_in = nullptr;        // device image base
+    size_t meta_at = 0;             // device offset of the metadata
+    size_t seg_at = 0;              // zero-copy: offset (from meta start) of the block list
+    uint32_t nseg = 0;
+};
+
+int slab_begin(b2c_ctx* ctx, Lane& lane, const uint32_t* seg_begin, const Slab& s, size_t meta_cap, SlabIO& io,
+               size_t keep = 0) {
+    const uint32_t cnt = s.m1 - s.m0;
+    io.meta_at = align_up(s.bytes, 256);
+    io.nseg = seg_begin[s.m1] - seg_begin[s.m0];
+    io.seg_at = align_up(meta_cap, 256);
+    const size_t zc_bytes = ctx->input_pinned ? (size_t)io.nseg * sizeof(b2c_iovec) + ((size_t)cnt + 1) * 4 + 256 : 0;
+    const size_t meta_total = io.seg_at + zc_bytes;
+    int rc;
+    if ((rc = ws_reserve(ctx, lane, lane.d_in, io.meta_at + meta_total + 64))) return rc;
+    if ((rc = pin_reserve(ctx, lane, lane.h_in, (ctx->input_pinned ? 0 : io.meta_at) + meta_total + 64, keep))) return rc;
+    io.d_in = static_cast<uint8_t*>(lane.d_in.p);
+    io.stage_meta = static_cast<uint8_t*>(lane.h_in.p) + (ctx->input_pinned ? 0 : io.meta_at);
+    return B2C_OK;
+}
+
+// `meta_bytes` of metadata are in io.stage_meta; `d_off` = device address of the slab's message offsets
+int slab_submit(b2c_ctx* ctx, Lane& lane, const b2c_iovec* segs, const uint32_t* seg_begin, const Slab& s, SlabIO& io,
+                size_t meta_bytes, const uint64_t* d_off, uint64_t& h2d) {
+    const uint32_t cnt = s.m1 - s.m0;
+    if (!ctx->input_pinned) {
+        const size_t total = io.meta_at + meta_bytes;
+        B2C_CUDA(ctx, cudaMemcpyAsync(io.d_in, lane.h_in.p, total, cudaMemcpyHostToDevice, lane.stream));
+        h2d += total;
+        return B2C_OK;
+    }
+    b2c_iovec* h_segs = reinterpret_cast<b2c_iovec*>(io.stage_meta + io.seg_at);
+    uint32_t* h_begin = reinterpret_cast<uint32_t*>(io.stage_meta + io.seg_at + (size_t)io.nseg * sizeof(b2c_iovec));
+    const uint32_t s0 = seg_begin[s.m0];
+    memcpy(h_segs, segs + s0, (size_t)io.nseg * sizeof(b2c_iovec));
+    for (uint32_t i = 0; i <= cnt; i++) h_begin[i] = seg_begin[s.m0 + i] - s0;
+    const size_t total = io.seg_at + (size_t)io.nseg * sizeof(b2c_iovec) + ((size_t)cnt + 1) * 4;
+    B2C_CUDA(ctx, cudaMemcpyAsync(io.d_in + io.meta_at, io.stage_meta, total, cudaMemcpyHostToDevice, lane.stream));
+    h2d += total + s.payload;  // the payload crosses PCIe inside the gather kernel
+    const uint8_t* d_meta = io.d_in + io.meta_at;
+    return launch_gather_host(ctx, lane, reinterpret_cast<const b2c_iovec*>(d_meta + io.seg_at),
+                              reinterpret_cast<const uint32_t*>(d_meta + io.seg_at + (size_t)io.nseg * sizeof(b2c_iovec)),
+                              d_off, cnt, io.d_in);
+}
+
 struct Trace {
     bool on;
     const char* what;
@@ -874,23 +1025,22 @@ int b2c_crc32c_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_be
         const uint32_t cnt = s.m1 - s.m0;
         LayoutPlan lp;
         TIMED(tr.layout, lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx));
-        const size_t blob_at = align_up(s.bytes, 256);
-        const size_t init_at = align_up(blob_at + lp.blob_bytes, 256);
-        const size_t in_bytes = init_at + (init ? (size_t)cnt * 4 : 0);
-        if ((rc = pin_reserve(ctx, lane, lane.h_in, in_bytes + 64))) return rc;
-        if ((rc = ws_reserve(ctx, lane, lane.d_in, in_bytes + 64))) return rc;
+        const size_t init_rel = align_up(lp.blob_bytes, 256);            // metadata: layout blob | init values
+        const size_t meta_bytes = init_rel + (init ? (size_t)cnt * 4 : 0);
+        SlabIO io;
+        if ((rc = slab_begin(ctx, lane, seg_begin, s, meta_bytes, io))) return rc;
         if ((rc = pin_reserve(ctx, lane, lane.h_out, (size_t)cnt * 4 + 64))) return rc;
         if ((rc = ws_reserve(ctx, lane, lane.d_out, (size_t)cnt * 4 + 64))) return rc;
-        uint8_t* stage = static_cast<uint8_t*>(lane.h_in.p);
-        TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, stage));
-        TIMED(tr.layout, lp.fill(stage + blob_at));
-        if (init) memcpy(stage + init_at, init + s.m0, (size_t)cnt * 4);
+        if (!ctx->input_pinned)
+            TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, static_cast<uint8_t*>(lane.h_in.p)));
+        TIMED(tr.layout, lp.fill(io.stage_meta));
+        if (init) memcpy(io.stage_meta + init_rel, init + s.m0, (size_t)cnt * 4);
         auto ts = Clock::now();
-        uint8_t* d_in = static_cast<uint8_t*>(lane.d_in.p);
-        B2C_CUDA(ctx, cudaMemcpyAsync(d_in, stage, in_bytes, cudaMemcpyHostToDevice, lane.stream));
-        h2d += in_bytes;
+        uint8_t* d_in = io.d_in;
         LayoutView lv;
-        lp.bind(d_in + blob_at, &lv);
+        lp.bind(d_in + io.meta_at, &lv);
+        if ((rc = slab_submit(ctx, lane, segs, seg_begin, s, io, meta_bytes, lv.d_off, h2d))) return rc;
+        const size_t init_at = io.meta_at + init_rel;
         uint32_t* d_crc = static_cast<uint32_t*>(lane.d_out.p);
         if ((rc = launch_crc32c(ctx, lane, lv, d_in, init ? reinterpret_cast<uint32_t*>(d_in + init_at) : nullptr, d_crc)))
             return rc;
@@ -967,29 +1117,28 @@ int b2c_snappy_compress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_
             const uint32_t cnt = s.m1 - s.m0;
             LayoutPlan lp;
             TIMED(tr.layout, lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx));
-            const size_t blob_at = align_up(s.bytes, 256);
-            const size_t in_bytes = blob_at + lp.blob_bytes;
+            const size_t meta_bytes = lp.blob_bytes;
             const uint64_t cap = lp.v.max_comp;
-            const size_t meta_bytes = ((size_t)cnt + 1) * 8;
+            const size_t out_meta_bytes = ((size_t)cnt + 1) * 8;
             const size_t off_at = align_up(cap, 256);  // device: packed output, then its offsets
-            if ((rc = pin_reserve(ctx, lane, lane.h_in, in_bytes + 64))) return rc;
-            if ((rc = ws_reserve(ctx, lane, lane.d_in, in_bytes + 64))) return rc;
-            if ((rc = ws_reserve(ctx, lane, lane.d_out, off_at + meta_bytes + 64))) return rc;
-            if ((rc = pin_reserve(ctx, lane, lane.h_out, align_up(meta_bytes, 256) + cap + 64))) return rc;
-            uint8_t* stage = static_cast<uint8_t*>(lane.h_in.p);
-            TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, stage));
-            TIMED(tr.layout, lp.fill(stage + blob_at));
+            SlabIO io;
+            if ((rc = slab_begin(ctx, lane, seg_begin, s, meta_bytes, io))) return rc;
+            if ((rc = ws_reserve(ctx, lane, lane.d_out, off_at + out_meta_bytes + 64))) return rc;
+            if ((rc = pin_reserve(ctx, lane, lane.h_out, align_up(out_meta_bytes, 256) + (direct ? 0 : cap) + 64))) return rc;
+            if (!ctx->input_pinned)
+                TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, static_cast<uint8_t*>(lane.h_in.p)));
+            TIMED(tr.layout, lp.fill(io.stage_meta));
             auto ts = Clock::now();
-            uint8_t* d_in = static_cast<uint8_t*>(lane.d_in.p);
-            B2C_CUDA(ctx, cudaMemcpyAsync(d_in, stage, in_bytes, cudaMemcpyHostToDevice, lane.stream));
-            h2d += in_bytes;
+            uint8_t* d_in = io.d_in;
             LayoutView lv;
-            lp.bind(d_in + blob_at, &lv);
+            lp.bind(d_in + io.meta_at, &lv);
+            if ((rc = slab_submit(ctx, lane, segs, seg_begin, s, io, meta_bytes, lv.d_off, h2d))) return rc;
+            const size_t meta_bytes_out = out_meta_bytes;
             uint8_t* d_out = static_cast<uint8_t*>(lane.d_out.p);
             uint64_t* d_out_off = reinterpret_cast<uint64_t*>(d_out + off_at);
             if ((rc = launch_compress(ctx, lane, lv, d_in, d_out, cap, d_out_off))) return rc;
-            B2C_CUDA(ctx, cudaMemcpyAsync(lane.h_out.p, d_out_off, meta_bytes, cudaMemcpyDeviceToHost, lane.stream));
-            d2h += meta_bytes;
+            B2C_CUDA(ctx, cudaMemcpyAsync(lane.h_out.p, d_out_off, meta_bytes_out, cudaMemcpyDeviceToHost, lane.stream));
+            d2h += meta_bytes_out;
             B2C_CUDA(ctx, cudaEventRecord(lane.ev_meta, lane.stream));
             tr.submit += secs(ts, Clock::now());
         }
@@ -1041,13 +1190,16 @@ int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint3
         const uint32_t cnt = s.m1 - s.m0;
         LayoutPlan lin;
         TIMED(tr.layout, lin.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx));
-        if ((rc = pin_reserve(ctx, lane, lane.h_in, align_up(s.bytes, 256) + lin.blob_bytes + (size_t)cnt * 16 + 4096)))
-            return rc;
-        uint8_t* stage = static_cast<uint8_t*>(lane.h_in.p);
         if (o_off.size() < cnt) o_off.resize(cnt);
         if (o_cap.size() < cnt) o_cap.resize(cnt);
-        // output slot sizes come from the (lenient) preambles, read by the gathering threads
-        TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, stage, o_cap.data()));
+        // output slot sizes come from the (lenient) preambles
+        if (ctx->input_pinned) {
+            TIMED(tr.gather, slab_caps(ctx, segs, seg_begin, bp, s, o_cap.data()));
+        } else {  // read by the gathering threads while the bytes are in their cache
+            if ((rc = pin_reserve(ctx, lane, lane.h_in, align_up(s.bytes, 256) + lin.blob_bytes + (size_t)cnt * 16 + 4096)))
+                return rc;
+            TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, static_cast<uint8_t*>(lane.h_in.p), o_cap.data()));
+        }
         auto tl = Clock::now();
         uint64_t pos = 0;
         for (uint32_t i = 0; i < cnt; i++) {
@@ -1061,25 +1213,22 @@ int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint3
         out_off[s.m1] = out_base;
         LayoutPlan lout;
         lout.plan(cnt, o_off.data(), o_cap.data(), ctx);
-        const size_t blob_in_at = align_up(s.bytes, 256);
-        const size_t blob_out_at = align_up(blob_in_at + lin.blob_bytes, 256);
-        const size_t in_bytes = blob_out_at + lout.blob_bytes;
-        if ((rc = pin_reserve(ctx, lane, lane.h_in, in_bytes + 64, s.bytes))) return rc;  // keeps the gathered slab
-        stage = static_cast<uint8_t*>(lane.h_in.p);
-        lin.fill(stage + blob_in_at);
-        lout.fill(stage + blob_out_at);
+        const size_t blob_out_rel = align_up(lin.blob_bytes, 256);  // metadata: input layout blob | output layout blob
+        const size_t meta_bytes = blob_out_rel + lout.blob_bytes;
+        SlabIO io;
+        if ((rc = slab_begin(ctx, lane, seg_begin, s, meta_bytes, io, /*keep=*/s.bytes))) return rc;
+        lin.fill(io.stage_meta);
+        lout.fill(io.stage_meta + blob_out_rel);
         tr.layout += secs(tl, Clock::now());
         const size_t st_at = align_up(pos, 256);
-        if ((rc = ws_reserve(ctx, lane, lane.d_in, in_bytes + 64))) return rc;
         if ((rc = ws_reserve(ctx, lane, lane.d_out, st_at + (size_t)cnt * 4 + 64))) return rc;
-        if ((rc = pin_reserve(ctx, lane, lane.h_out, st_at + (size_t)cnt * 4 + 64))) return rc;
+        if ((rc = pin_reserve(ctx, lane, lane.h_out, (direct ? 0 : st_at) + st_at + (size_t)cnt * 4 + 64))) return rc;
         auto ts = Clock::now();
-        uint8_t* d_in = static_cast<uint8_t*>(lane.d_in.p);
-        B2C_CUDA(ctx, cudaMemcpyAsync(d_in, stage, in_bytes, cudaMemcpyHostToDevice, lane.stream));
-        h2d += in_bytes;
+        uint8_t* d_in = io.d_in;
         LayoutView vin, vout;
-        lin.bind(d_in + blob_in_at, &vin);
-        lout.bind(d_in + blob_out_at, &vout);
+        lin.bind(d_in + io.meta_at, &vin);
+        lout.bind(d_in + io.meta_at + blob_out_rel, &vout);
+        if ((rc = slab_submit(ctx, lane, segs, seg_begin, s, io, meta_bytes, vin.d_off, h2d))) return rc;
         uint8_t* d_out = static_cast<uint8_t*>(lane.d_out.p);
         int32_t* d_status = reinterpret_cast<int32_t*>(d_out + st_at);
         if ((rc = launch_decompress(ctx, lane, vin, d_in, vout, d_out, nullptr, d_status))) return rc;

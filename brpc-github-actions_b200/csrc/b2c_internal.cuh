@@ -115,6 +115,7 @@ struct b2c_ctx {
     size_t slab_bytes = 32u << 20;
     unsigned host_threads = 0;
     bool trace = false;
+    bool input_pinned = false;  // B2C_OPT_INPUT_PINNED: *_batch inputs are page-locked, gather them on the device
     bool ring_decode = false;        // B2C_RING_DECODE=1: unsplittable large slots decode through a 64 KiB smem ring
     bool block_decode = true;        // B2C_BLOCK_DECODE=0: never split large streams into 64 KiB blocks
     bool ring_attr_done = false;

@@ -71,6 +71,16 @@ int b2c_ctx_device(const b2c_ctx* ctx);
 /* cudaStream_t of the ctx, as an opaque pointer */
 void* b2c_ctx_stream(b2c_ctx* ctx);
 int b2c_ctx_sync(b2c_ctx* ctx);
+/* Options.
+ *   B2C_OPT_INPUT_PINNED (default 0): promise that EVERY input block handed to the *_batch
+ *     entry points lies in page-locked host memory that the device can address with the same
+ *     pointer (cudaHostAlloc / b2c_host_alloc_pinned; the bRPC-side equivalent is a pinned IOBuf
+ *     block pool installed through iobuf::blockmem_allocate, src/butil/iobuf.cpp:163-170, as
+ *     src/brpc/rdma/block_pool.cpp does for RDMA).  The library then skips the host-side gather:
+ *     only the block list is copied and a kernel pulls the blocks over PCIe itself.  Passing a
+ *     pageable block with this option set is a fatal device fault. */
+#define B2C_OPT_INPUT_PINNED 1
+int b2c_ctx_set_option(b2c_ctx* ctx, int option, int value);
 /* Number of kernels this ctx has launched so far (bench.py's gpu_launches). */
 uint64_t b2c_ctx_launch_count(const b2c_ctx* ctx);
 

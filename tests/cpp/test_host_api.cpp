@@ -15,6 +15,10 @@
 #include <string>
 #include <vector>
 
+#include <atomic>
+#include <thread>
+
+#include "b200_aggregator.hpp"
 #include "b200_codec.hpp"
 #include "b2o.h"
 
@@ -182,6 +186,47 @@ static void batch_calls() {
     CHECK(ok[4] && ok[6] && back[6] == bodies[6]);
 }
 
+// Many threads issue one-message calls (the CompressHandler calling pattern, one bthread per message);
+// the aggregator must turn them into few GPU batches and hand every caller its own exact result.
+static void aggregator_many_threads() {
+    b200::BatchAggregator::Options opt;
+    opt.max_wait_us = 2000;
+    b200::BatchAggregator agg(opt);
+    const int kThreads = 32, kPer = 40;
+    std::atomic<int> bad(0);
+    std::vector<std::thread> th;
+    for (int t = 0; t < kThreads; t++) {
+        th.emplace_back([&, t] {
+            for (int i = 0; i < kPer; i++) {
+                std::string body((size_t)((t * 131 + i * 977) % 6000), '\0');
+                b2o_corpus_fill(B2O_WORDS, t * 1000 + i, reinterpret_cast<uint8_t*>(&body[0]), body.size());
+                std::string z, back;
+                if (!agg.Compress(blocks_of(body, 1500), &z) || z != oracle_compress(body)) bad++;
+                if (agg.Crc32c(blocks_of(body, 700)) !=
+                    b2o_crc32c_value(reinterpret_cast<const uint8_t*>(body.data()), body.size()))
+                    bad++;
+                if (!agg.Decompress(blocks_of(z, 200), &back) || back != body) bad++;
+                if (i % 10 == 0 && z.size() > 4) {  // a corrupt stream fails alone
+                    std::string cut = z.substr(0, z.size() - 2), junk;
+                    uint32_t ulen = 0;
+                    std::vector<uint8_t> tmp(8000);
+                    int want = b2o_snappy_uncompress(reinterpret_cast<const uint8_t*>(cut.data()), cut.size(), tmp.data(),
+                                                     tmp.size(), &ulen);
+                    if (agg.Decompress(blocks_of(cut, 200), &junk) != (want != 0)) bad++;
+                }
+            }
+        });
+    }
+    for (auto& x : th) x.join();
+    CHECK(bad.load() == 0);
+    b200::BatchAggregator::Stats st = agg.stats();
+    CHECK(st.calls >= (uint64_t)kThreads * kPer * 3);
+    CHECK(st.batches < st.calls / 4);  // batching really happened
+    CHECK(st.largest_batch > 4);
+    printf("aggregator: %llu calls in %llu batches (largest %llu)\n", (unsigned long long)st.calls,
+           (unsigned long long)st.batches, (unsigned long long)st.largest_batch);
+}
+
 int main() {
     crc_standard_results();
     crc_values_extend_mask();
@@ -190,6 +235,7 @@ int main() {
     throughput_shapes();
     mass_snappy_iobuf();
     batch_calls();
+    aggregator_many_threads();
     if (g_fail) {
         fprintf(stderr, "%d check(s) failed\n", g_fail);
         return 1;

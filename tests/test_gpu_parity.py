@@ -460,3 +460,38 @@ def test_large_foreign_stream_falls_back_to_whole_message_decode(codec):
     assert_bytes_equal(out[:total].tobytes(), want, "foreign large")
     st, _ = codec.validate(*pack_tight([s]))
     assert st[0] == 0
+
+
+def test_e2e_zero_copy_gather_from_pinned_blocks(codec, cpu):
+    """B2C_OPT_INPUT_PINNED: the input blocks live in page-locked memory (a pinned IOBuf block pool) and
+    the device gathers them itself; results must equal the staged path and the oracle."""
+    import brpc_b200
+    rng = np.random.default_rng(33)
+    ln = np.concatenate([np.full(6000, 1024), rng.integers(0, 70000, 300), np.array([0, 1, 1 << 20])]).astype(np.uint32)
+    rng.shuffle(ln)
+    arena, off, ln = O.corpus_batch("words", ln, first_index=55)
+    pinned = codec.pinned(len(arena))
+    pinned[:] = arena
+    for kw in ({"cuts": rng.integers(0, 5000, len(ln))}, {"seg_bytes": 8160}, {"seg_bytes": 333}):
+        segs, sb = brpc_b200.make_iovecs(pinned, off, ln, **kw)
+        codec.set_option(codec.OPT_INPUT_PINNED, 1)
+        try:
+            crc = codec.crc32c_batch(segs, sb)
+            out = codec.pinned(int(sum(32 + int(l) + int(l) // 6 + 5 for l in ln)))
+            out_off = codec.compress_batch(segs, sb, out)
+            csegs, csb = brpc_b200.make_iovecs(out, out_off[:-1], np.diff(out_off).astype(np.uint32), seg_bytes=4096)
+            back = codec.pinned(int(ln.astype(np.uint64).sum()) + 64)
+            b_off, status = codec.decompress_batch(csegs, csb, back)
+        finally:
+            codec.set_option(codec.OPT_INPUT_PINNED, 0)
+        want_crc, _ = cpu.batch_crc32c(arena, off, ln, threads=8)
+        assert (crc == want_crc).all()
+        w_out, w_off, w_len, _ = cpu.batch_compress(arena, off, ln, threads=8)
+        assert (np.diff(out_off).astype(np.uint32) == w_len).all()
+        for i in range(0, len(ln), 37):
+            assert_bytes_equal(out[int(out_off[i]):int(out_off[i + 1])].tobytes(),
+                               w_out[int(w_off[i]):int(w_off[i]) + int(w_len[i])].tobytes(), f"zc msg {i}")
+        assert (status == 0).all() and (np.diff(b_off).astype(np.uint32) == ln).all()
+        for i in range(0, len(ln), 37):
+            a, b = int(off[i]), int(off[i]) + int(ln[i])
+            assert_bytes_equal(back[int(b_off[i]):int(b_off[i + 1])].tobytes(), arena[a:b].tobytes(), f"zc back {i}")
