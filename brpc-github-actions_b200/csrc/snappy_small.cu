@@ -249,172 +249,148 @@ struct SmallDecompressParams {
     uint32_t n_list;
 };
 
+// Each slot owns a contiguous, byte-addressable output buffer of kSmallSlotBytes in shared memory
+// (stride 1040 B: at most LPW lanes of a warp touch it at once, so bank collisions are rare and
+// the code needs no interleaved-address arithmetic).  The lane decodes tag by tag with plain byte
+// loops — the copy loop IS IncrementalCopy (snappy.cc:98-103), overlap semantics included — and
+// when all lanes of the warp are done the warp flushes every slot with coalesced 16-byte stores.
+// Back-reference copy inside a slot's shared-memory buffer.  With offset >= 4 the four source bytes
+// of a round all precede its first destination byte, so they are loaded together (one shared-memory
+// round trip per 4 bytes instead of one per byte); shorter offsets replicate byte by byte exactly as
+// IncrementalCopy does (snappy.cc:98-103).
+__device__ __forceinline__ void slot_copy(uint8_t* d, const uint8_t* s, uint32_t len, uint32_t offset) {
+    uint32_t i = 0;
+    if (offset >= 4) {
+        for (; i + 4 <= len; i += 4) {  // the 4 source bytes of a round precede its first destination byte
+            const uint8_t b0 = s[i], b1 = s[i + 1], b2 = s[i + 2], b3 = s[i + 3];
+            d[i] = b0;
+            d[i + 1] = b1;
+            d[i + 2] = b2;
+            d[i + 3] = b3;
+        }
+    }
+    for (; i < len; i++) d[i] = s[i];
+}
+
+constexpr uint32_t kSmallSlotBytes = kSmallMax + 16;
+
 template <int LPW>
 __global__ void __launch_bounds__(1024 / LPW) snappy_decompress_small_kernel(SmallDecompressParams P) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t slot = (threadIdx.x >> 5) * LPW + lane;
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t slot = warp * LPW + lane;  // meaningful for lane < LPW
     const uint32_t idx = blockIdx.x * 32 + slot;
-    if (lane >= LPW || idx >= P.n_list) return;
-    const uint32_t m = P.list ? P.list[idx] : idx;
-    const uint8_t* in = P.in + P.in_off[m];
-    const uint32_t n = P.in_len[m];
-    const uint32_t cap = P.out_cap[m];
-    // this slot's output column: word w lives at col[w * 32]
-    uint32_t* col = reinterpret_cast<uint32_t*>(smem_raw) + slot;
-
-    // ---- input funnel: `have` upcoming stream bytes sit in `bits`, refilled one aligned word at a time
-    const uint32_t* inext = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(in) & ~uintptr_t(3));
-    const uint32_t* const iend =
-        reinterpret_cast<const uint32_t*>((reinterpret_cast<uintptr_t>(in) + n + 3) & ~uintptr_t(3));
-    uint64_t bits = 0;
-    uint32_t have = 0;
-    auto refill = [&]() {  // afterwards have >= 5 (or the stream is exhausted and zeros follow)
-        while (have <= 4) {
-            const uint32_t w = inext < iend ? *inext : 0u;
-            inext++;
-            bits |= (uint64_t)w << (8 * have);
-            have += 4;
-        }
-    };
-    auto consume = [&](uint32_t k) {
-        bits >>= 8 * k;
-        have -= k;
-    };
-    {
-        const uint32_t lead = (uint32_t)(reinterpret_cast<uintptr_t>(in) & 3);
-        refill();
-        consume(lead);
-        refill();
-    }
-    // ---- output funnel: the pending partial word is mirrored in shared memory after every push,
-    //      so back-references can always read produced bytes from the column
-    uint32_t oacc = 0, onacc = 0, owords = 0;
-    auto push = [&](uint32_t v, uint32_t k) {  // k in 1..4, v has no bits above 8k
-        const uint32_t sh = 8 * onacc;
-        const uint32_t lo = oacc | (v << sh);
-        const uint32_t hi = __funnelshift_l(v, 0u, sh);
-        onacc += k;
-        col[owords * 32] = lo;
-        if (onacc >= 4) {
-            owords++;
-            onacc -= 4;
-            oacc = hi;
-            if (onacc) col[owords * 32] = hi;
-        } else {
-            oacc = lo;
-        }
-    };
-    auto lds32u = [&](uint32_t p) -> uint32_t {  // 4 produced bytes starting at byte p
-        const uint32_t* w = col + (p >> 2) * 32;
-        return __funnelshift_r(w[0], w[32], (p & 3) * 8);
-    };
-
-    // lenient preamble, snappy.cc:692-711
-    uint32_t expected = 0, ip = 0;
+    const bool live = lane < LPW && idx < P.n_list;
+    uint32_t m = 0, expected = 0;
     int st = B2C_OK;
-    {
-        uint32_t shift = 0;
-        for (;;) {
-            if (shift >= 32 || ip >= n) {
-                st = B2C_CORRUPT;
-                break;
+    if (live) {
+        m = P.list ? P.list[idx] : idx;
+        const uint8_t* in = P.in + P.in_off[m];
+        const uint32_t n = P.in_len[m];
+        const uint32_t cap = P.out_cap[m];
+        uint8_t* ob = smem_raw + (size_t)slot * kSmallSlotBytes;
+        // lenient preamble, snappy.cc:692-711
+        uint32_t ip = 0;
+        {
+            uint32_t shift = 0;
+            for (;;) {
+                if (shift >= 32 || ip >= n) {
+                    st = B2C_CORRUPT;
+                    break;
+                }
+                const uint32_t c = in[ip++];
+                expected |= (c & 0x7f) << shift;
+                if (c < 128) break;
+                shift += 7;
             }
-            const uint32_t c = (uint32_t)bits & 0xff;
-            consume(1);
-            refill();
-            ip++;
-            expected |= (c & 0x7f) << shift;
-            if (c < 128) break;
-            shift += 7;
         }
-    }
-    if (st == B2C_OK && expected > cap) st = B2C_TOO_SMALL;
-    uint32_t produced = 0;
-    if (st == B2C_OK) {
-        for (;;) {
-            if (ip == n) {  // clean eof: snappy.cc:867
-                if (produced != expected) st = B2C_CORRUPT;
-                break;
-            }
-            const uint32_t c = (uint32_t)bits & 0xff;
-            const uint32_t kind = c & 3;
-            const uint32_t extra = kind == 0 ? (c >= 0xf0 ? (c >> 2) - 59 : 0) : kind == 1 ? 1 : kind == 2 ? 2 : 4;
-            if (n - ip < extra + 1) {  // tag cut short
-                st = B2C_CORRUPT;
-                break;
-            }
-            uint32_t trailer = (uint32_t)(bits >> 8);
-            if (extra < 4) trailer &= (1u << (8 * extra)) - 1u;
-            consume(1 + extra);
-            refill();
-            ip += 1 + extra;
-            if (kind == 0) {
-                uint32_t len = (c >> 2) + 1;
-                if (len >= 61) len = trailer + 1u;  // may wrap to 0 like the reference
-                if (n - ip < len || expected - produced < len) {
-                    st = B2C_CORRUPT;
+        if (st == B2C_OK && expected > cap) st = B2C_TOO_SMALL;
+        uint32_t op = 0;
+        if (st == B2C_OK) {
+            for (;;) {
+                if (ip == n) {  // clean eof: snappy.cc:867
+                    if (op != expected) st = B2C_CORRUPT;
                     break;
                 }
-                uint32_t i = 0;
-                for (; i + 4 <= len; i += 4) {
-                    push((uint32_t)bits, 4);
-                    consume(4);
-                    refill();
-                }
-                if (i < len) {
-                    const uint32_t k = len - i;
-                    push((uint32_t)bits & ((1u << (8 * k)) - 1u), k);
-                    consume(k);
-                    refill();
-                }
-                produced += len;
-                ip += len;
-            } else {
-                uint32_t len, offset;
-                if (kind == 1) {
-                    len = ((c >> 2) & 7) + 4;
-                    offset = ((c >> 5) << 8) | (trailer & 0xff);
-                } else {
-                    len = (c >> 2) + 1;
-                    offset = trailer;
-                }
-                if (offset == 0 || offset > produced || expected - produced < len) {
-                    st = B2C_CORRUPT;
-                    break;
-                }
-                const uint32_t src = produced - offset;
-                if (offset >= 4) {
-                    // 4 bytes per round: the source bytes of a round were all produced before it
+                const uint32_t x = ld32u(in + ip);  // tag byte + up to 3 trailer bytes
+                const uint32_t c = x & 0xff;
+                const uint32_t kind = c & 3;
+                if (kind == 1) {  // copy, 1-byte offset (by far the most frequent tag of text-like bodies)
+                    if (n - ip < 2) { st = B2C_CORRUPT; break; }
+                    const uint32_t len = ((c >> 2) & 7) + 4;
+                    const uint32_t offset = ((c >> 5) << 8) | ((x >> 8) & 0xff);
+                    ip += 2;
+                    if (offset == 0 || offset > op || expected - op < len) { st = B2C_CORRUPT; break; }
+                    slot_copy(ob + op, ob + op - offset, len, offset);
+                    op += len;
+                } else if (kind == 0) {
+                    uint32_t len = (c >> 2) + 1;
+                    uint32_t extra = 0;
+                    if (len >= 61) {
+                        extra = len - 60;
+                        if (n - ip < extra + 1) { st = B2C_CORRUPT; break; }
+                        uint32_t v = x >> 8;
+                        if (extra == 4) v |= (uint32_t)in[ip + 4] << 24;
+                        else v &= (1u << (8 * extra)) - 1u;
+                        len = v + 1u;  // may wrap to 0 like the reference
+                    }
+                    ip += 1 + extra;
+                    if (n - ip < len || expected - op < len) { st = B2C_CORRUPT; break; }
+                    const uint8_t* __restrict__ s = in + ip;
+                    uint8_t* d = ob + op;
                     uint32_t i = 0;
-                    for (; i + 4 <= len; i += 4) push(lds32u(src + i), 4);
-                    if (i < len) push(lds32u(src + i) & ((1u << (8 * (len - i))) - 1u), len - i);
-                } else {
-                    for (uint32_t i = 0; i < len; i++) push(lds32u(src + i) & 0xffu, 1);  // IncrementalCopy, snappy.cc:98-103
+                    for (; i + 4 <= len; i += 4) {  // 4 independent loads, then 4 stores
+                        const uint8_t b0 = s[i], b1 = s[i + 1], b2 = s[i + 2], b3 = s[i + 3];
+                        d[i] = b0;
+                        d[i + 1] = b1;
+                        d[i + 2] = b2;
+                        d[i + 3] = b3;
+                    }
+                    for (; i < len; i++) d[i] = s[i];
+                    op += len;
+                    ip += len;
+                } else {  // copy, 2- or 4-byte offset
+                    const uint32_t extra = kind == 2 ? 2u : 4u;
+                    if (n - ip < extra + 1) { st = B2C_CORRUPT; break; }
+                    const uint32_t len = (c >> 2) + 1;
+                    uint32_t offset = x >> 8;
+                    if (kind == 2) offset &= 0xffffu;
+                    else offset |= (uint32_t)in[ip + 4] << 24;
+                    ip += 1 + extra;
+                    if (offset == 0 || offset > op || expected - op < len) { st = B2C_CORRUPT; break; }
+                    slot_copy(ob + op, ob + op - offset, len, offset);
+                    op += len;
                 }
-                produced += len;
             }
         }
+        P.status[m] = st;
+        if (P.ulen) P.ulen[m] = expected;
     }
-    P.status[m] = st;
-    if (P.ulen) P.ulen[m] = expected;
-    if (st != B2C_OK) return;
-    // flush this slot's column
-    uint8_t* gout = P.out + P.out_off[m];
-    if ((reinterpret_cast<uintptr_t>(gout) & 15) == 0) {
-        uint32_t b = 0;
-        for (; b + 16 <= expected; b += 16) {
-            const uint32_t w = b >> 2;
-            *reinterpret_cast<uint4*>(gout + b) =
-                make_uint4(col[(w + 0) * 32], col[(w + 1) * 32], col[(w + 2) * 32], col[(w + 3) * 32]);
+    __syncwarp();
+    // warp-cooperative flush of this warp's slots
+    const uint32_t flush_len = live && st == B2C_OK ? expected : 0u;
+    const uint64_t gaddr = live ? reinterpret_cast<uint64_t>(P.out + P.out_off[m]) : 0ull;
+#pragma unroll
+    for (int j = 0; j < LPW; j++) {
+        const uint32_t len = __shfl_sync(0xffffffffu, flush_len, j);
+        if (len == 0) continue;
+        const uint64_t ga = ((uint64_t)__shfl_sync(0xffffffffu, (uint32_t)(gaddr >> 32), j) << 32) |
+                            __shfl_sync(0xffffffffu, (uint32_t)gaddr, j);
+        uint8_t* g = reinterpret_cast<uint8_t*>(ga);
+        const uint8_t* sb = smem_raw + (size_t)(warp * LPW + j) * kSmallSlotBytes;
+        if ((ga & 15) == 0) {
+            const uint32_t vecs = len >> 4;
+            for (uint32_t i = lane; i < vecs; i += 32)
+                reinterpret_cast<uint4*>(g)[i] = reinterpret_cast<const uint4*>(sb)[i];
+            for (uint32_t i = (vecs << 4) + lane; i < len; i += 32) g[i] = sb[i];
+        } else {
+            for (uint32_t i = lane; i < len; i += 32) g[i] = sb[i];
         }
-        for (; b < expected; b++) gout[b] = (uint8_t)(col[(b >> 2) * 32] >> (8 * (b & 3)));
-    } else {
-        for (uint32_t b = 0; b < expected; b++) gout[b] = (uint8_t)(col[(b >> 2) * 32] >> (8 * (b & 3)));
     }
 }
 
-constexpr size_t kSmallDecompressSmem = (size_t)(kSmallMax + 8) * 32;  // 32 columns of 258 words
+constexpr size_t kSmallDecompressSmem = (size_t)kSmallSlotBytes * 32;
 
 // ---------------------------------------------------------------------------
 template <int LPW>
