@@ -20,16 +20,48 @@
 namespace b2c {
 
 constexpr uint32_t kSmallMax = 1024;
-constexpr uint32_t kSmallInWords = kSmallMax / 4 + 4;  // spare words: unaligned reads past the end stay in-bounds
 
 // A CTA always owns 32 bodies ("slots"); LPW of each warp's lanes carry one body each, so a
 // CTA has 32/LPW warps.  Fewer bodies per warp = more warps for the same shared memory: the
 // serial chains of different bodies then interleave in the schedulers instead of being
 // executed in lock-step (ncu on LPW=32: 10 of 32 lanes active, 0.2 IPC per warp, 2 warps/SM).
+constexpr uint32_t kSmallInStride = kSmallMax + 32;  // per-slot input buffer: 1 KiB + slack for 16-byte reads past the end
 struct SmallCompressSmem {
-    uint16_t table[1024 * 32];           // [entry][slot]
-    uint32_t in[kSmallInWords * 32];     // [word][slot]
+    uint16_t table[1024 * 32];              // [entry][slot]
+    uint8_t in[kSmallInStride * 32];        // [slot][byte], filled by TMA bulk copies
 };
+
+// ---- TMA bulk copy (cp.async.bulk, SASS UBLKCP) + mbarrier helpers ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P1;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, 0x989680;\n\t"
+        "@P1 bra WAIT_DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "WAIT_DONE:\n\t"
+        "}" ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 
 __device__ __forceinline__ uint32_t hash_bytes_s(uint32_t bytes, uint32_t shift) {  // snappy.cc:47-50
     return (bytes * 0x1e35a7bdu) >> shift;
@@ -96,33 +128,34 @@ __global__ void __launch_bounds__(1024 / LPW) snappy_compress_small_kernel(Small
         n = min(kFragBytes, P.len[m] - k * kFragBytes);
         gin = P.in + P.off[m] + (size_t)k * kFragBytes;
     }
-    // stage this lane's body into its word column
-    uint32_t* in_s = sm.in + slot;
-    if (live) {
-        if ((reinterpret_cast<uintptr_t>(gin) & 15) == 0) {
-            for (uint32_t b = 0; b < n; b += 16) {
-                const uint4 v = *reinterpret_cast<const uint4*>(gin + b);
-                const uint32_t w = b >> 2;
-                in_s[(w + 0) * 32] = v.x;
-                in_s[(w + 1) * 32] = v.y;
-                in_s[(w + 2) * 32] = v.z;
-                in_s[(w + 3) * 32] = v.w;
-            }
-        } else {
-            for (uint32_t b = 0; b < n; b += 4) in_s[(b >> 2) * 32] = ld32u(gin + b);
-        }
-    }
+    // Stage this lane's body into its slot: a 16-byte-aligned body is fetched by ONE TMA bulk copy
+    // (cp.async.bulk global -> shared, completion counted on an mbarrier; no registers, no LSU
+    // instructions); other alignments fall back to word loads.
+    __shared__ uint64_t stage_bar;
+    if (threadIdx.x == 0) mbar_init(&stage_bar, blockDim.x);
     __syncthreads();
+    uint8_t* in_b = sm.in + (size_t)slot * kSmallInStride;
+    if (live && n && (reinterpret_cast<uintptr_t>(gin) & 15) == 0) {
+        const uint32_t bytes = (n + 15u) & ~15u;
+        mbar_arrive_expect_tx(&stage_bar, bytes);
+        tma_bulk_g2s(in_b, gin, bytes, &stage_bar);
+    } else {
+        if (live)
+            for (uint32_t b = 0; b < n; b += 4) *reinterpret_cast<uint32_t*>(in_b + b) = ld32u(gin + b);
+        mbar_arrive(&stage_bar);
+    }
+    mbar_wait(&stage_bar, 0);
+    __syncthreads();  // the zeroed tables (generic stores of other threads) must be visible too
     if (!live) return;
     // 8 bytes starting at byte p of this body
     auto ld64s = [&](uint32_t p) -> uint64_t {
-        const uint32_t* w = in_s + (p >> 2) * 32;
-        const uint32_t a = w[0], b = w[32], c = w[64], sh = (p & 3) * 8;
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(in_b + (p & ~3u));
+        const uint32_t a = w[0], b = w[1], c = w[2], sh = (p & 3) * 8;
         return ((uint64_t)__funnelshift_r(b, c, sh) << 32) | __funnelshift_r(a, b, sh);
     };
     auto ld32s = [&](uint32_t p) -> uint32_t {
-        const uint32_t* w = in_s + (p >> 2) * 32;
-        return __funnelshift_r(w[0], w[32], (p & 3) * 8);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(in_b + (p & ~3u));
+        return __funnelshift_r(w[0], w[1], (p & 3) * 8);
     };
     uint16_t* tab = sm.table + slot;
     uint32_t tsize = 256;  // GetHashTable sizing, snappy.cc:253-256
@@ -211,8 +244,8 @@ __global__ void __launch_bounds__(1024 / LPW) snappy_compress_small_kernel(Small
                 // snappy.cc:430-433: insert ip-1; one 4-word read yields both load32(ip-1) and bytes ip..ip+7
                 {
                     const uint32_t q = ip - 1;
-                    const uint32_t* w = in_s + (q >> 2) * 32;
-                    const uint32_t a = w[0], b = w[32], c = w[64], e = w[96], sh = (q & 3) * 8;
+                    const uint32_t* w = reinterpret_cast<const uint32_t*>(in_b + (q & ~3u));
+                    const uint32_t a = w[0], b = w[1], c = w[2], e = w[3], sh = (q & 3) * 8;
                     const uint32_t p0 = __funnelshift_r(a, b, sh), p1 = __funnelshift_r(b, c, sh),
                                    p2 = __funnelshift_r(c, e, sh);  // bytes q..q+11
                     tab[hash_bytes_s(p0, shift) * 32] = (uint16_t)q;
