@@ -20,6 +20,7 @@
 
 #include "b200_aggregator.hpp"
 #include "b200_codec.hpp"
+#include "b200_framing.hpp"
 #include "b2o.h"
 
 static int g_fail = 0;
@@ -186,6 +187,76 @@ static void batch_calls() {
     CHECK(ok[4] && ok[6] && back[6] == bodies[6]);
 }
 
+// ---- snappy framing format (framing_format.txt): CPU statement of the spec as the checker ----
+static uint32_t cpu_masked_crc(const std::string& s) {
+    return b2o_crc32c_mask(b2o_crc32c_value(reinterpret_cast<const uint8_t*>(s.data()), s.size()));
+}
+static std::string le32(uint32_t v) {
+    char b[4] = {(char)(v & 0xff), (char)((v >> 8) & 0xff), (char)((v >> 16) & 0xff), (char)(v >> 24)};
+    return std::string(b, 4);
+}
+static std::string chunk(uint8_t type, const std::string& data) {
+    char h[4] = {(char)type, (char)(data.size() & 0xff), (char)((data.size() >> 8) & 0xff), (char)((data.size() >> 16) & 0xff)};
+    return std::string(h, 4) + data;
+}
+static const std::string kSzId = std::string("\xff\x06\x00\x00sNaPpY", 10);
+static std::string cpu_frame(const std::string& payload) {
+    std::string out = kSzId;
+    for (size_t p = 0; p < payload.size(); p += 65536) {
+        std::string piece = payload.substr(p, 65536);
+        std::string z = oracle_compress(piece);
+        if (z.size() < piece.size()) out += chunk(0x00, le32(cpu_masked_crc(piece)) + z);
+        else out += chunk(0x01, le32(cpu_masked_crc(piece)) + piece);
+    }
+    return out;
+}
+
+static void framing_format() {
+    std::vector<std::string> payloads;
+    for (int i = 0; i < 12; i++) {
+        static const size_t sizes[] = {0, 1, 100, 65535, 65536, 65537, 200000, 1 << 20, 5000, 131072, 70000, 33};
+        std::string s(sizes[i], '\0');
+        b2o_corpus_fill(i % 3 == 0 ? B2O_RAND62 : i % 3 == 1 ? B2O_WORDS : B2O_AZ09, i, reinterpret_cast<uint8_t*>(&s[0]), s.size());
+        payloads.push_back(s);
+    }
+    std::vector<BlockList> in;
+    for (const std::string& s : payloads) in.push_back(blocks_of(s, 8160));
+    std::vector<std::string> framed, back;
+    std::vector<bool> ok;
+    b200::framing::EncodeBatch(in, &framed);
+    for (size_t i = 0; i < payloads.size(); i++) CHECK(framed[i] == cpu_frame(payloads[i]));
+    std::vector<BlockList> fin;
+    for (const std::string& s : framed) fin.push_back(blocks_of(s, 4000));
+    b200::framing::DecodeBatch(fin, &back, &ok);
+    for (size_t i = 0; i < payloads.size(); i++) CHECK(ok[i] && back[i] == payloads[i]);
+    // hand-built streams: skippable / padding / repeated identifier are ignored; errors are errors
+    const std::string body = payloads[2];
+    const std::string good_chunk = chunk(0x00, le32(cpu_masked_crc(body)) + oracle_compress(body));
+    const std::string raw_chunk = chunk(0x01, le32(cpu_masked_crc(body)) + body);
+    struct Case { std::string stream; bool ok; std::string want; };
+    std::string bad_crc = good_chunk;
+    bad_crc[5] ^= 1;
+    std::vector<Case> cases = {
+        {kSzId, true, ""},
+        {kSzId + good_chunk, true, body},
+        {kSzId + raw_chunk + good_chunk, true, body + body},
+        {kSzId + chunk(0xfe, std::string(7, '\0')) + good_chunk + chunk(0x80, "future") + kSzId + raw_chunk, true, body + body},
+        {good_chunk, false, ""},                                  // no stream identifier
+        {kSzId + chunk(0x02, "x") + good_chunk, false, ""},       // reserved unskippable
+        {kSzId + bad_crc, false, ""},                             // checksum mismatch
+        {kSzId + good_chunk.substr(0, good_chunk.size() - 1), false, ""},  // chunk cut short
+        {kSzId + chunk(0xff, "sNaPpX") + good_chunk, false, ""},  // malformed repeated identifier
+        {kSzId + chunk(0x00, le32(cpu_masked_crc(body)) + std::string("\x05\x10hel", 5)), false, ""},  // bad snappy data
+    };
+    std::vector<BlockList> cin;
+    for (const Case& c : cases) cin.push_back(blocks_of(c.stream, 64));
+    b200::framing::DecodeBatch(cin, &back, &ok);
+    for (size_t i = 0; i < cases.size(); i++) {
+        CHECK(ok[i] == cases[i].ok);
+        CHECK(back[i] == cases[i].want);
+    }
+}
+
 // Many threads issue one-message calls (the CompressHandler calling pattern, one bthread per message);
 // the aggregator must turn them into few GPU batches and hand every caller its own exact result.
 static void aggregator_many_threads() {
@@ -235,6 +306,7 @@ int main() {
     throughput_shapes();
     mass_snappy_iobuf();
     batch_calls();
+    framing_format();
     aggregator_many_threads();
     if (g_fail) {
         fprintf(stderr, "%d check(s) failed\n", g_fail);
