@@ -468,6 +468,8 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     if (const char* s = getenv("B2C_GTAB_WPS")) ctx->gtab_warps_per_sm = atoi(s);
     if (const char* s = getenv("B2C_SMALL_KERNELS")) ctx->small_kernels = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL_LPW_C")) ctx->small_lpw_compress = atoi(s);
+    if (const char* s = getenv("B2C_WINDOW")) ctx->window_mask = atoi(s);
+    if (const char* s = getenv("B2C_SMALL2")) ctx->small_two_phase = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL_LPW_D")) ctx->small_lpw_decompress = atoi(s);
     int rc = B2C_OK;
     do {
@@ -481,6 +483,7 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
         if (rc) break;
         if ((rc = crc_tables_init(ctx))) break;
         rc = small_kernels_configure(ctx);
+        if (!rc) rc = window_kernels_configure(ctx);
     } while (0);
     if (rc != B2C_OK) {
         fprintf(stderr, "b2c_ctx_create failed: %s\n", ctx->err.c_str());

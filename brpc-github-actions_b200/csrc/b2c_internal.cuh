@@ -122,6 +122,8 @@ struct b2c_ctx {
     bool batch_decode = true;        // B2C_BATCH_DECODE=0: one tag per step in the warp decoder
     bool batch_decode_small = false; // B2C_BATCH_DECODE_SMALL=1: <=1 KiB slots use the warp batch decoder, not one lane per stream
     bool nt_gather = true;  // B2C_NT_GATHER=0: plain memcpy into staging
+    bool small_two_phase = true;  // B2C_SMALL2=0 restores the one-phase kernel; <=1 KiB bodies compress as find (lane per body) then encode (warp per body)
+    int window_mask = 0;    // B2C_WINDOW: bit c set = fragment class c compresses with the window-parallel kernel
 };
 
 struct b2c_layout {
@@ -169,6 +171,10 @@ int launch_compress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const u
                           uint32_t* d_frag_clen);
 int launch_decompress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint8_t* d_in,
                             const LayoutView& out, uint8_t* d_out, uint32_t* d_ulen, int32_t* d_status);
+// window-parallel warp-per-fragment compressor (snappy_window.cu); c = fragment class 0..2
+int window_kernels_configure(b2c_ctx* ctx);
+int launch_compress_window(b2c_ctx* ctx, Lane& lane, const LayoutView& L, int c, const uint8_t* d_in, uint8_t* scratch,
+                           uint32_t* d_frag_clen);
 // exclusive scan of u32 values into u64 offsets: out[0]=0 ... out[n]=total
 int launch_scan_u32_u64(b2c_ctx* ctx, Lane& lane, const uint32_t* d_vals, uint32_t n, uint64_t* d_out,
                         void* d_tmp /* >= 8*(n/1024+2) */);

@@ -456,6 +456,10 @@ int launch_compress(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t
     prof_mark(ctx, lane, B2C_PROF_COMPRESS);
     for (int c = 0; c < 3; c++) {
         if (!L.n_class[c]) continue;
+        if (ctx->window_mask & (1 << c)) {  // window-parallel warp per fragment
+            if ((rc = launch_compress_window(ctx, lane, L, c, d_in, scratch, d_frag_clen))) return rc;
+            continue;
+        }
         if (c == 0 && ctx->small_kernels) {  // bodies <= 1 KiB: one lane per fragment
             if ((rc = launch_compress_small(ctx, lane, L, d_in, scratch, d_frag_clen))) return rc;
             continue;

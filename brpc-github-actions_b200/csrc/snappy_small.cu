@@ -15,7 +15,9 @@
 //               so back-references resolve at shared-memory latency.
 // Output bytes of the compressor are funnelled through a 64-bit register and stored
 // as aligned words.
-#include "b2c_internal.cuh"
+#include <algorithm>
+
+#include "snappy_emit.cuh"
 
 namespace b2c {
 
@@ -106,64 +108,27 @@ struct SmallCompressParams {
     uint32_t n_list;
 };
 
-template <int LPW>
-__global__ void __launch_bounds__(1024 / LPW) snappy_compress_small_kernel(SmallCompressParams P) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    SmallCompressSmem& sm = *reinterpret_cast<SmallCompressSmem*>(smem_raw);
-    const uint32_t lane = threadIdx.x & 31;
-    const uint32_t slot = (threadIdx.x >> 5) * LPW + lane;  // meaningful for lane < LPW
-    const uint32_t idx = blockIdx.x * 32 + slot;
-    const bool live = lane < LPW && idx < P.n_list;
-    // zero all 32 tables together (GetHashTable's memset, snappy.cc:269)
-    {
-        uint4* t4 = reinterpret_cast<uint4*>(sm.table);
-        for (uint32_t i = threadIdx.x; i < sizeof(sm.table) / 16; i += blockDim.x) t4[i] = make_uint4(0, 0, 0, 0);
-    }
-    uint32_t f = 0, n = 0;
-    const uint8_t* gin = nullptr;
-    if (live) {
-        f = P.frag_list ? P.frag_list[idx] : idx;
-        const uint32_t m = P.frag_msg ? P.frag_msg[f] : f;
-        const uint32_t k = P.frag_first ? f - P.frag_first[m] : 0u;
-        n = min(kFragBytes, P.len[m] - k * kFragBytes);
-        gin = P.in + P.off[m] + (size_t)k * kFragBytes;
-    }
-    // Stage this lane's body into its slot: a 16-byte-aligned body is fetched by ONE TMA bulk copy
-    // (cp.async.bulk global -> shared, completion counted on an mbarrier; no registers, no LSU
-    // instructions); other alignments fall back to word loads.
-    __shared__ uint64_t stage_bar;
-    if (threadIdx.x == 0) mbar_init(&stage_bar, blockDim.x);
-    __syncthreads();
-    uint8_t* in_b = sm.in + (size_t)slot * kSmallInStride;
-    if (live && n && (reinterpret_cast<uintptr_t>(gin) & 15) == 0) {
-        const uint32_t bytes = (n + 15u) & ~15u;
-        mbar_arrive_expect_tx(&stage_bar, bytes);
-        tma_bulk_g2s(in_b, gin, bytes, &stage_bar);
-    } else {
-        if (live)
-            for (uint32_t b = 0; b < n; b += 4) *reinterpret_cast<uint32_t*>(in_b + b) = ld32u(gin + b);
-        mbar_arrive(&stage_bar);
-    }
-    mbar_wait(&stage_bar, 0);
-    __syncthreads();  // the zeroed tables (generic stores of other threads) must be visible too
-    if (!live) return;
+// CompressFragment for one body by ONE lane.  `in_al` is 4-byte aligned and the body starts `bias`
+// (0..3) bytes after it; `tab` = this body's zeroed table, entries TSTRIDE u16 apart; `dst` 4-byte aligned.
+template <int TSTRIDE>
+__device__ __forceinline__ uint32_t small_compress_body(const uint8_t* in_al, const uint32_t bias, const uint32_t n,
+                                                         uint16_t* tab, uint32_t* dst) {
     // 8 bytes starting at byte p of this body
     auto ld64s = [&](uint32_t p) -> uint64_t {
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(in_b + (p & ~3u));
-        const uint32_t a = w[0], b = w[1], c = w[2], sh = (p & 3) * 8;
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(in_al + ((p + bias) & ~3u));
+        const uint32_t a = w[0], b = w[1], c = w[2], sh = ((p + bias) & 3) * 8;
         return ((uint64_t)__funnelshift_r(b, c, sh) << 32) | __funnelshift_r(a, b, sh);
     };
     auto ld32s = [&](uint32_t p) -> uint32_t {
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(in_b + (p & ~3u));
-        return __funnelshift_r(w[0], w[1], (p & 3) * 8);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(in_al + ((p + bias) & ~3u));
+        return __funnelshift_r(w[0], w[1], ((p + bias) & 3) * 8);
     };
-    uint16_t* tab = sm.table + slot;
     uint32_t tsize = 256;  // GetHashTable sizing, snappy.cc:253-256
     while (tsize < 16384u && tsize < n) tsize <<= 1;
     const uint32_t shift = 32 - (31 - __clz(tsize));
 
     OutFunnel o;
-    o.dst = reinterpret_cast<uint32_t*>(P.scratch + (P.frag_slot ? P.frag_slot[f] : (uint64_t)f * P.slot_stride));
+    o.dst = dst;
     o.acc = 0;
     o.nacc = 0;
     o.words = 0;
@@ -199,8 +164,8 @@ __global__ void __launch_bounds__(1024 / LPW) snappy_compress_small_kernel(Small
             have_d = false;
             const uint32_t cur = (uint32_t)d;
             const uint32_t h = hash_bytes_s(cur, shift);
-            const uint32_t cand = tab[h * 32];
-            tab[h * 32] = (uint16_t)ip;
+            const uint32_t cand = tab[h * TSTRIDE];
+            tab[h * TSTRIDE] = (uint16_t)ip;
             const uint64_t x = ld64s(cand) ^ d;
             if ((uint32_t)x == 0) {
                 if (ip > next_emit) emit_literal(next_emit, ip - next_emit);  // snappy.cc:403
@@ -244,11 +209,11 @@ __global__ void __launch_bounds__(1024 / LPW) snappy_compress_small_kernel(Small
                 // snappy.cc:430-433: insert ip-1; one 4-word read yields both load32(ip-1) and bytes ip..ip+7
                 {
                     const uint32_t q = ip - 1;
-                    const uint32_t* w = reinterpret_cast<const uint32_t*>(in_b + (q & ~3u));
-                    const uint32_t a = w[0], b = w[1], c = w[2], e = w[3], sh = (q & 3) * 8;
+                    const uint32_t* w = reinterpret_cast<const uint32_t*>(in_al + ((q + bias) & ~3u));
+                    const uint32_t a = w[0], b = w[1], c = w[2], e = w[3], sh = ((q + bias) & 3) * 8;
                     const uint32_t p0 = __funnelshift_r(a, b, sh), p1 = __funnelshift_r(b, c, sh),
                                    p2 = __funnelshift_r(c, e, sh);  // bytes q..q+11
-                    tab[hash_bytes_s(p0, shift) * 32] = (uint16_t)q;
+                    tab[hash_bytes_s(p0, shift) * TSTRIDE] = (uint16_t)q;
                     d = ((uint64_t)__funnelshift_r(p1, p2, 8) << 32) | __funnelshift_r(p0, p1, 8);
                     have_d = true;
                 }
@@ -263,7 +228,213 @@ __global__ void __launch_bounds__(1024 / LPW) snappy_compress_small_kernel(Small
         }
     }
     if (next_emit < n) emit_literal(next_emit, n - next_emit);  // emit_remainder, snappy.cc:446-450
-    P.frag_clen[f] = o.finish();
+    return o.finish();
+}
+
+template <int LPW>
+__global__ void __launch_bounds__(1024 / LPW) snappy_compress_small_kernel(SmallCompressParams P) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    SmallCompressSmem& sm = *reinterpret_cast<SmallCompressSmem*>(smem_raw);
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t slot = (threadIdx.x >> 5) * LPW + lane;  // meaningful for lane < LPW
+    const uint32_t idx = blockIdx.x * 32 + slot;
+    const bool live = lane < LPW && idx < P.n_list;
+    // zero all 32 tables together (GetHashTable's memset, snappy.cc:269)
+    {
+        uint4* t4 = reinterpret_cast<uint4*>(sm.table);
+        for (uint32_t i = threadIdx.x; i < sizeof(sm.table) / 16; i += blockDim.x) t4[i] = make_uint4(0, 0, 0, 0);
+    }
+    uint32_t f = 0, n = 0;
+    const uint8_t* gin = nullptr;
+    if (live) {
+        f = P.frag_list ? P.frag_list[idx] : idx;
+        const uint32_t m = P.frag_msg ? P.frag_msg[f] : f;
+        const uint32_t k = P.frag_first ? f - P.frag_first[m] : 0u;
+        n = min(kFragBytes, P.len[m] - k * kFragBytes);
+        gin = P.in + P.off[m] + (size_t)k * kFragBytes;
+    }
+    // Stage this lane's body into its slot: a 16-byte-aligned body is fetched by ONE TMA bulk copy
+    // (cp.async.bulk global -> shared, completion counted on an mbarrier; no registers, no LSU
+    // instructions); other alignments fall back to word loads.
+    __shared__ uint64_t stage_bar;
+    if (threadIdx.x == 0) mbar_init(&stage_bar, blockDim.x);
+    __syncthreads();
+    uint8_t* in_b = sm.in + (size_t)slot * kSmallInStride;
+    if (live && n && (reinterpret_cast<uintptr_t>(gin) & 15) == 0) {
+        const uint32_t bytes = (n + 15u) & ~15u;
+        mbar_arrive_expect_tx(&stage_bar, bytes);
+        tma_bulk_g2s(in_b, gin, bytes, &stage_bar);
+    } else {
+        if (live)
+            for (uint32_t b = 0; b < n; b += 4) *reinterpret_cast<uint32_t*>(in_b + b) = ld32u(gin + b);
+        mbar_arrive(&stage_bar);
+    }
+    mbar_wait(&stage_bar, 0);
+    __syncthreads();  // the zeroed tables (generic stores of other threads) must be visible too
+    if (!live) return;
+    P.frag_clen[f] = small_compress_body<32>(
+        in_b, 0u, n, sm.table + slot,
+        reinterpret_cast<uint32_t*>(P.scratch + (P.frag_slot ? P.frag_slot[f] : (uint64_t)f * P.slot_stride)));
+}
+
+// ---------------------------------------------------------------------------
+// compress in two phases: FIND (one lane per body) then ENCODE (one warp per body)
+// ---------------------------------------------------------------------------
+// The chain through the hash table is what has to be serial; encoding what it found is not.  In
+// the one-phase kernel above a lane that finds a match spends ~100 further instructions pushing
+// the literal and the copy through its output funnel while the other lanes of its warp wait
+// (divergence), so almost every trip through the loop pays for the encode path.  Here a lane only
+// RECORDS the match as one packed word (position | offset << 10 | length << 20; all < 1024 for
+// a body <= 1 KiB) in a small L2-resident list, and once the warp's bodies are through, the
+// whole warp encodes each list 32 elements at a time (emit_elements_warp: one lane per element,
+// prefix sum over encoded sizes).  Byte-exact with CompressFragment: the elements and their
+// order are the reference's, only the moment they are written changes.
+template <int TSTRIDE>
+__device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const uint32_t n, uint16_t* tab,
+                                                    uint32_t* __restrict__ elist) {
+    auto ld64s = [&](uint32_t p) -> uint64_t {
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(in_b + (p & ~3u));
+        const uint32_t a = w[0], b = w[1], c = w[2], sh = (p & 3) * 8;
+        return ((uint64_t)__funnelshift_r(b, c, sh) << 32) | __funnelshift_r(a, b, sh);
+    };
+    uint32_t tsize = 256;  // GetHashTable sizing, snappy.cc:253-256
+    while (tsize < 16384u && tsize < n) tsize <<= 1;
+    const uint32_t shift = 32 - (31 - __clz(tsize));
+    uint32_t ne = 0;
+    if (n >= 15) {  // kInputMarginBytes, snappy.cc:344-347
+        const uint32_t ip_limit = n - 15;
+        uint32_t ip = 1, skip = 32, nxt = 0;
+        bool probing = true, have_d = false;
+        uint64_t d = 0;  // bytes ip..ip+7 when have_d
+        for (;;) {  // the unified probe / copy-tail loop of small_compress_body
+            if (probing) {
+                nxt = ip + (skip++ >> 5);
+                if (nxt > ip_limit) break;  // snappy.cc:386-388
+            }
+            if (!have_d) d = ld64s(ip);
+            have_d = false;
+            const uint32_t h = hash_bytes_s((uint32_t)d, shift);
+            const uint32_t cand = tab[h * TSTRIDE];
+            tab[h * TSTRIDE] = (uint16_t)ip;
+            const uint64_t x = ld64s(cand) ^ d;
+            if ((uint32_t)x == 0) {
+                uint32_t matched;  // FindMatchLength, snappy-internal.h:86-120
+                const uint32_t xh = (uint32_t)(x >> 32);
+                if (xh) {
+                    matched = 4 + ((uint32_t)(__ffs(xh) - 1) >> 3);
+                } else {
+                    matched = 8;
+                    for (;;) {
+                        const uint32_t rem = n - (ip + matched);
+                        if (rem == 0) break;
+                        const uint64_t y = ld64s(cand + matched) ^ ld64s(ip + matched);
+                        uint32_t nb = y ? (uint32_t)(__ffsll((long long)y) - 1) >> 3 : 8u;
+                        nb = min(nb, rem);
+                        matched += nb;
+                        if (nb < 8) break;
+                    }
+                }
+                elist[ne++] = ip | ((ip - cand) << 10) | (matched << 20);
+                ip += matched;
+                if (ip >= ip_limit) break;  // snappy.cc:427-429
+                {  // snappy.cc:430-433: insert ip-1; one 4-word read yields load32(ip-1) and bytes ip..ip+7
+                    const uint32_t q = ip - 1;
+                    const uint32_t* w = reinterpret_cast<const uint32_t*>(in_b + (q & ~3u));
+                    const uint32_t a = w[0], b = w[1], c = w[2], e = w[3], sh = (q & 3) * 8;
+                    const uint32_t p0 = __funnelshift_r(a, b, sh), p1 = __funnelshift_r(b, c, sh),
+                                   p2 = __funnelshift_r(c, e, sh);  // bytes q..q+11
+                    tab[hash_bytes_s(p0, shift) * TSTRIDE] = (uint16_t)q;
+                    d = ((uint64_t)__funnelshift_r(p1, p2, 8) << 32) | __funnelshift_r(p0, p1, 8);
+                    have_d = true;
+                }
+                probing = false;
+            } else if (probing) {
+                ip = nxt;
+            } else {  // snappy.cc:441-442
+                ip += 1;
+                probing = true;
+                skip = 32;
+            }
+        }
+    }
+    return ne;
+}
+
+constexpr uint32_t kSmallMaxElems = kSmallMax / 4;  // copies cover >= 4 input bytes each and do not overlap
+
+// Persistent CTAs of 32 bodies (LPW per warp); `elists` = gridDim.x * 32 lists of kSmallMaxElems words.
+template <int LPW>
+__global__ void __launch_bounds__(1024 / LPW) snappy_compress_small2_kernel(SmallCompressParams P, uint32_t* elists) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    SmallCompressSmem& sm = *reinterpret_cast<SmallCompressSmem*>(smem_raw);
+    __shared__ uint64_t stage_bar;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t slot = warp * LPW + lane;  // meaningful for lane < LPW
+    if (threadIdx.x == 0) mbar_init(&stage_bar, blockDim.x);
+    const uint32_t groups = (P.n_list + 31) / 32;
+    uint32_t parity = 0;
+    for (uint32_t g = blockIdx.x; g < groups; g += gridDim.x, parity ^= 1) {
+        const uint32_t idx = g * 32 + slot;
+        const bool live = lane < LPW && idx < P.n_list;
+        __syncthreads();  // previous group's tables and staged bodies are no longer in use (and stage_bar is initialised)
+        {
+            uint4* t4 = reinterpret_cast<uint4*>(sm.table);
+            for (uint32_t i = threadIdx.x; i < sizeof(sm.table) / 16; i += blockDim.x) t4[i] = make_uint4(0, 0, 0, 0);
+        }
+        uint32_t f = 0, n = 0;
+        const uint8_t* gin = nullptr;
+        if (live) {
+            f = P.frag_list ? P.frag_list[idx] : idx;
+            const uint32_t m = P.frag_msg ? P.frag_msg[f] : f;
+            const uint32_t k = P.frag_first ? f - P.frag_first[m] : 0u;
+            n = min(kFragBytes, P.len[m] - k * kFragBytes);
+            gin = P.in + P.off[m] + (size_t)k * kFragBytes;
+        }
+        uint8_t* in_b = sm.in + (size_t)slot * kSmallInStride;
+        if (live && n && (reinterpret_cast<uintptr_t>(gin) & 15) == 0) {  // one TMA bulk copy per body
+            const uint32_t bytes = (n + 15u) & ~15u;
+            mbar_arrive_expect_tx(&stage_bar, bytes);
+            tma_bulk_g2s(in_b, gin, bytes, &stage_bar);
+        } else {
+            if (live)
+                for (uint32_t b = 0; b < n; b += 4) *reinterpret_cast<uint32_t*>(in_b + b) = ld32u(gin + b);
+            mbar_arrive(&stage_bar);
+        }
+        mbar_wait(&stage_bar, parity);
+        __syncthreads();  // the zeroed tables (generic stores of other threads) must be visible too
+        // ---- phase 1: find ----
+        uint32_t* my_list = elists + ((size_t)blockIdx.x * 32 + slot) * kSmallMaxElems;
+        uint32_t ne = 0;
+        if (live) ne = small_find_body<32>(in_b, n, sm.table + slot, my_list);
+        __syncwarp();  // the lists written by this warp's lanes are read by all of its lanes below
+        // ---- phase 2: encode, one body at a time by the whole warp ----
+        uint8_t* my_out = live ? P.scratch + (P.frag_slot ? P.frag_slot[f] : (uint64_t)f * P.slot_stride) : nullptr;
+#pragma unroll 1
+        for (uint32_t j = 0; j < (uint32_t)LPW; j++) {
+            if (!__shfl_sync(0xffffffffu, (int)live, j)) continue;
+            const uint32_t nej = __shfl_sync(0xffffffffu, ne, j), nj = __shfl_sync(0xffffffffu, n, j),
+                           fj = __shfl_sync(0xffffffffu, f, j);
+            const uint64_t oa = reinterpret_cast<uint64_t>(my_out);
+            uint8_t* out = reinterpret_cast<uint8_t*>(((uint64_t)__shfl_sync(0xffffffffu, (uint32_t)(oa >> 32), j) << 32) |
+                                                      __shfl_sync(0xffffffffu, (uint32_t)oa, j));
+            const InShared in{sm.in + (size_t)(warp * LPW + j) * kSmallInStride};
+            const uint32_t* el = elists + ((size_t)blockIdx.x * 32 + warp * LPW + j) * kSmallMaxElems;
+            uint32_t op = 0, next_emit = 0;
+            for (uint32_t base = 0; base < nej; base += 32) {
+                const bool has = base + lane < nej;
+                const uint32_t e = has ? __ldcg(el + base + lane) : 0u;
+                const uint32_t p = e & 1023u, off = (e >> 10) & 1023u, mm = e >> 20;
+                const uint32_t end = p + mm;
+                uint32_t ls = __shfl_up_sync(0xffffffffu, end, 1);
+                if (lane == 0) ls = next_emit;
+                next_emit = __shfl_sync(0xffffffffu, end, min(31u, nej - base - 1));
+                op = emit_elements_warp(in, has, ls, p, off, mm, out, op, lane);
+            }
+            op = emit_remainder_warp(in, next_emit, nj, out, op, lane);
+            if (lane == 0) P.frag_clen[fj] = op;
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------
@@ -430,6 +601,8 @@ template <int LPW>
 static int configure_one(b2c_ctx* ctx) {
     B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_compress_small_kernel<LPW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)sizeof(SmallCompressSmem)));
+    B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_compress_small2_kernel<LPW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(SmallCompressSmem)));
     B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_decompress_small_kernel<LPW>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallDecompressSmem));
     return B2C_OK;
@@ -459,6 +632,21 @@ int launch_compress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const u
     P.n_list = L.n_class[0];
     const uint32_t blocks = (P.n_list + 31) / 32;
     const size_t smem = sizeof(SmallCompressSmem);
+    if (ctx->small_two_phase) {  // find, then encode; persistent CTAs own their element lists
+        const uint32_t grid = std::min<uint32_t>(blocks, (uint32_t)ctx->num_sms * 2);
+        int rc;
+        if ((rc = ws_reserve(ctx, lane, lane.ws_tab, (size_t)grid * 32 * kSmallMaxElems * 4))) return rc;
+        uint32_t* el = static_cast<uint32_t*>(lane.ws_tab.p);
+        switch (ctx->small_lpw_compress) {
+            case 4: snappy_compress_small2_kernel<4><<<grid, 256, smem, lane.stream>>>(P, el); break;
+            case 16: snappy_compress_small2_kernel<16><<<grid, 64, smem, lane.stream>>>(P, el); break;
+            case 32: snappy_compress_small2_kernel<32><<<grid, 32, smem, lane.stream>>>(P, el); break;
+            default: snappy_compress_small2_kernel<8><<<grid, 128, smem, lane.stream>>>(P, el); break;
+        }
+        ctx->launches++;
+        B2C_CUDA(ctx, cudaGetLastError());
+        return B2C_OK;
+    }
     switch (ctx->small_lpw_compress) {
         case 4: snappy_compress_small_kernel<4><<<blocks, 256, smem, lane.stream>>>(P); break;
         case 16: snappy_compress_small_kernel<16><<<blocks, 64, smem, lane.stream>>>(P); break;
