@@ -72,6 +72,10 @@ SYMBOLS = {
     "b2c_snappy_decompress_verify_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b2c_snappy_compress_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _vp, C.c_uint64, _u64p]),
     "b2c_snappy_decompress_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _vp, C.c_uint64, _u64p, _i32p]),
+    "b2c_snappy_compress_crc_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _vp, C.c_uint64, _u64p, _u32p,
+                                                C.c_int]),
+    "b2c_snappy_decompress_verify_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _u32p, _vp, C.c_uint64,
+                                                     _u64p, _i32p]),
     "b2c_crc32c_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _u32p, _u32p]),
     "b2c_last_transfer_bytes": (None, [_vp, _u64p, _u64p]),
 }
@@ -425,6 +429,28 @@ class Codec:
         self._check(self.lib.b2c_snappy_decompress_batch(self.ctx, self._segs(raw_segs), _ptr(seg_begin, _u32p), n,
                                                          out.ctypes.data, out.nbytes, _ptr(out_off, _u64p),
                                                          _ptr(status, _i32p)))
+        return out_off, status
+
+    def compress_crc_batch(self, raw_segs: np.ndarray, seg_begin: np.ndarray, out: np.ndarray, masked: bool = True):
+        """Sender side in one pass: (out_off, crc) -- the compressed streams and each body's (masked) CRC32C."""
+        n = len(seg_begin) - 1
+        out_off = np.empty(n + 1, dtype=np.uint64)
+        crc = np.empty(n, dtype=np.uint32)
+        self._check(self.lib.b2c_snappy_compress_crc_batch(self.ctx, self._segs(raw_segs), _ptr(seg_begin, _u32p), n,
+                                                           out.ctypes.data, out.nbytes, _ptr(out_off, _u64p),
+                                                           _ptr(crc, _u32p), 1 if masked else 0))
+        return out_off, crc
+
+    def decompress_verify_batch(self, raw_segs: np.ndarray, seg_begin: np.ndarray, masked_crc: np.ndarray,
+                                out: np.ndarray):
+        """Receiver side in one pass: decode and check every body against its masked CRC32C."""
+        n = len(seg_begin) - 1
+        out_off = np.empty(n + 1, dtype=np.uint64)
+        status = np.empty(n, dtype=np.int32)
+        mc = np.ascontiguousarray(masked_crc, dtype=np.uint32)
+        self._check(self.lib.b2c_snappy_decompress_verify_batch(self.ctx, self._segs(raw_segs), _ptr(seg_begin, _u32p), n,
+                                                                _ptr(mc, _u32p), out.ctypes.data, out.nbytes,
+                                                                _ptr(out_off, _u64p), _ptr(status, _i32p)))
         return out_off, status
 
     def prof_enable(self, on: bool = True):

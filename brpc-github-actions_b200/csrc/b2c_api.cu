@@ -1060,13 +1060,14 @@ int b2c_crc32c_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_be
     return B2C_OK;
 }
 
-int b2c_snappy_compress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, void* out,
-                              uint64_t out_cap, uint64_t* out_off) {
+// compress (+ optionally checksum the same staged bodies): crc == nullptr is plain b2c_snappy_compress_batch
+static int compress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, void* out,
+                               uint64_t out_cap, uint64_t* out_off, uint32_t* crc, bool masked) {
     if (!ctx || !out_off || (n && (!segs || !seg_begin || !out))) return B2C_E_ARG;
     out_off[0] = 0;
     if (n == 0) return B2C_OK;
     B2C_CUDA(ctx, cudaSetDevice(ctx->device));
-    Trace tr(ctx->trace, "compress_batch");
+    Trace tr(ctx->trace, crc ? "compress_crc_batch" : "compress_batch");
     BatchPlan bp(ctx);
     int rc;
     TIMED(tr.plan, rc = plan_batch(ctx, segs, seg_begin, n, bp));
@@ -1089,7 +1090,7 @@ int b2c_snappy_compress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_
         if (fetch_base + total > out_cap)
             return set_err(ctx, B2C_E_CAPACITY, "compress_batch: out_cap too small", cudaSuccess);
         fetch_base += total;
-        const size_t data_at = align_up(((size_t)cnt + 1) * 8, 256);
+        const size_t data_at = align_up(((size_t)cnt + 1) * 8 + (crc ? (size_t)cnt * 4 : 0), 256);
         uint8_t* dst = direct ? static_cast<uint8_t*>(out) + slab_base[k] : static_cast<uint8_t*>(lane.h_out.p) + data_at;
         B2C_CUDA(ctx, cudaMemcpyAsync(dst, lane.d_out.p, total, cudaMemcpyDeviceToHost, lane.stream));
         d2h += total;
@@ -1103,17 +1104,26 @@ int b2c_snappy_compress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_
         const uint32_t cnt = s.m1 - s.m0;
         TIMED(tr.wait, B2C_CUDA(ctx, cudaEventSynchronize(lane.ev_done)));
         const uint64_t* meta = static_cast<const uint64_t*>(lane.h_out.p);
-        const size_t data_at = align_up(((size_t)cnt + 1) * 8, 256);
+        const size_t data_at = align_up(((size_t)cnt + 1) * 8 + (crc ? (size_t)cnt * 4 : 0), 256);
         auto tc = Clock::now();
         if (!direct)
             parallel_copy(ctx, static_cast<uint8_t*>(out) + out_base, static_cast<uint8_t*>(lane.h_out.p) + data_at,
                           slab_total[k]);
         for (uint32_t i = 0; i < cnt; i++) out_off[s.m0 + i + 1] = out_base + meta[i + 1];
+        if (crc) {
+            const uint32_t* c = reinterpret_cast<const uint32_t*>(meta + cnt + 1);
+            if (masked)
+                for (uint32_t i = 0; i < cnt; i++) crc[s.m0 + i] = b2c_crc32c_mask(c[i]);
+            else
+                memcpy(crc + s.m0, c, (size_t)cnt * 4);
+        }
         out_base += slab_total[k];
         tr.copy_out += secs(tc, Clock::now());
         return B2C_OK;
     };
-    for (size_t k = 0; k < K + 2; k++) {
+    // software pipeline over the lanes: slab k is submitted, slab k-2's sizes are read and its bytes fetched,
+    // slab k-3 is handed to the caller -- so the host never waits for the slab it has just submitted
+    for (size_t k = 0; k < K + 3; k++) {
         if (k < K) {
             Lane& lane = ctx->pipe[k % kPipeLanes];
             const Slab& s = bp.slabs[k];
@@ -1122,7 +1132,7 @@ int b2c_snappy_compress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_
             TIMED(tr.layout, lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx));
             const size_t meta_bytes = lp.blob_bytes;
             const uint64_t cap = lp.v.max_comp;
-            const size_t out_meta_bytes = ((size_t)cnt + 1) * 8;
+            const size_t out_meta_bytes = ((size_t)cnt + 1) * 8 + (crc ? (size_t)cnt * 4 : 0);
             const size_t off_at = align_up(cap, 256);  // device: packed output, then its offsets
             SlabIO io;
             if ((rc = slab_begin(ctx, lane, seg_begin, s, meta_bytes, io))) return rc;
@@ -1139,14 +1149,16 @@ int b2c_snappy_compress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_
             const size_t meta_bytes_out = out_meta_bytes;
             uint8_t* d_out = static_cast<uint8_t*>(lane.d_out.p);
             uint64_t* d_out_off = reinterpret_cast<uint64_t*>(d_out + off_at);
+            if (crc && (rc = launch_crc32c(ctx, lane, lv, d_in, nullptr, reinterpret_cast<uint32_t*>(d_out_off + cnt + 1))))
+                return rc;
             if ((rc = launch_compress(ctx, lane, lv, d_in, d_out, cap, d_out_off))) return rc;
             B2C_CUDA(ctx, cudaMemcpyAsync(lane.h_out.p, d_out_off, meta_bytes_out, cudaMemcpyDeviceToHost, lane.stream));
             d2h += meta_bytes_out;
             B2C_CUDA(ctx, cudaEventRecord(lane.ev_meta, lane.stream));
             tr.submit += secs(ts, Clock::now());
         }
-        if (k >= 1 && k - 1 < K && (rc = fetch(k - 1))) return rc;
-        if (k >= 2 && k - 2 < K && (rc = finish(k - 2))) return rc;
+        if (k >= 2 && k - 2 < K && (rc = fetch(k - 2))) return rc;
+        if (k >= 3 && k - 3 < K && (rc = finish(k - 3))) return rc;
     }
     ctx->last_h2d = h2d;
     ctx->last_d2h = d2h;
@@ -1154,13 +1166,25 @@ int b2c_snappy_compress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_
     return B2C_OK;
 }
 
-int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, void* out,
-                                uint64_t out_cap, uint64_t* out_off, int32_t* status) {
+int b2c_snappy_compress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, void* out,
+                              uint64_t out_cap, uint64_t* out_off) {
+    return compress_batch_impl(ctx, segs, seg_begin, n, out, out_cap, out_off, nullptr, false);
+}
+
+int b2c_snappy_compress_crc_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, void* out,
+                                  uint64_t out_cap, uint64_t* out_off, uint32_t* crc, int masked) {
+    if (n && !crc) return B2C_E_ARG;
+    return compress_batch_impl(ctx, segs, seg_begin, n, out, out_cap, out_off, crc, masked != 0);
+}
+
+// decompress (+ optionally verify each result against masked_crc): masked_crc == nullptr is plain b2c_snappy_decompress_batch
+static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, void* out,
+                                 uint64_t out_cap, uint64_t* out_off, int32_t* status, const uint32_t* masked_crc) {
     if (!ctx || !out_off || (n && (!segs || !seg_begin || !status))) return B2C_E_ARG;
     out_off[0] = 0;
     if (n == 0) return B2C_OK;
     B2C_CUDA(ctx, cudaSetDevice(ctx->device));
-    Trace tr(ctx->trace, "decompress_batch");
+    Trace tr(ctx->trace, masked_crc ? "decompress_verify_batch" : "decompress_batch");
     BatchPlan bp(ctx);
     int rc;
     TIMED(tr.plan, rc = plan_batch(ctx, segs, seg_begin, n, bp));
@@ -1216,12 +1240,14 @@ int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint3
         out_off[s.m1] = out_base;
         LayoutPlan lout;
         lout.plan(cnt, o_off.data(), o_cap.data(), ctx);
-        const size_t blob_out_rel = align_up(lin.blob_bytes, 256);  // metadata: input layout blob | output layout blob
-        const size_t meta_bytes = blob_out_rel + lout.blob_bytes;
+        const size_t blob_out_rel = align_up(lin.blob_bytes, 256);  // metadata: input layout blob | output layout blob | crcs
+        const size_t crc_rel = align_up(blob_out_rel + lout.blob_bytes, 256);
+        const size_t meta_bytes = masked_crc ? crc_rel + (size_t)cnt * 4 : blob_out_rel + lout.blob_bytes;
         SlabIO io;
         if ((rc = slab_begin(ctx, lane, seg_begin, s, meta_bytes, io, /*keep=*/s.bytes))) return rc;
         lin.fill(io.stage_meta);
         lout.fill(io.stage_meta + blob_out_rel);
+        if (masked_crc) memcpy(io.stage_meta + crc_rel, masked_crc + s.m0, (size_t)cnt * 4);
         tr.layout += secs(tl, Clock::now());
         const size_t st_at = align_up(pos, 256);
         if ((rc = ws_reserve(ctx, lane, lane.d_out, st_at + (size_t)cnt * 4 + 64))) return rc;
@@ -1234,7 +1260,12 @@ int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint3
         if ((rc = slab_submit(ctx, lane, segs, seg_begin, s, io, meta_bytes, vin.d_off, h2d))) return rc;
         uint8_t* d_out = static_cast<uint8_t*>(lane.d_out.p);
         int32_t* d_status = reinterpret_cast<int32_t*>(d_out + st_at);
-        if ((rc = launch_decompress(ctx, lane, vin, d_in, vout, d_out, nullptr, d_status))) return rc;
+        if (masked_crc) {
+            const uint32_t* d_expect = reinterpret_cast<const uint32_t*>(d_in + io.meta_at + crc_rel);
+            if ((rc = launch_decompress_verify(ctx, lane, vin, d_in, vout, d_out, d_expect, nullptr, d_status))) return rc;
+        } else if ((rc = launch_decompress(ctx, lane, vin, d_in, vout, d_out, nullptr, d_status))) {
+            return rc;
+        }
         if (direct) {
             const uint64_t base = out_off[s.m0];
             if (pos) B2C_CUDA(ctx, cudaMemcpyAsync(static_cast<uint8_t*>(out) + base, d_out, pos, cudaMemcpyDeviceToHost, lane.stream));
@@ -1254,6 +1285,18 @@ int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint3
     ctx->last_d2h = d2h;
     tr.report(K, bp.payload);
     return B2C_OK;
+}
+
+int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, void* out,
+                                uint64_t out_cap, uint64_t* out_off, int32_t* status) {
+    return decompress_batch_impl(ctx, segs, seg_begin, n, out, out_cap, out_off, status, nullptr);
+}
+
+int b2c_snappy_decompress_verify_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n,
+                                       const uint32_t* masked_crc, void* out, uint64_t out_cap, uint64_t* out_off,
+                                       int32_t* status) {
+    if (n && !masked_crc) return B2C_E_ARG;
+    return decompress_batch_impl(ctx, segs, seg_begin, n, out, out_cap, out_off, status, masked_crc);
 }
 
 }  // extern "C"

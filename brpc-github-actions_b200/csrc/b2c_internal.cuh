@@ -14,7 +14,7 @@ namespace b2c {
 
 constexpr uint32_t kFragBytes = 65536;  // snappy.h:202-203 kBlockSize
 constexpr uint32_t kCrcChunk = 4096;    // bytes per CRC work item (one quad of lanes)
-constexpr int kPipeLanes = 3;           // staging slots of the end-to-end pipeline
+constexpr int kPipeLanes = 4;           // staging slots of the end-to-end pipeline
 
 struct DevBuf {
     void* p = nullptr;

@@ -239,10 +239,29 @@ int b2c_snappy_compress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_
 
 /* brpc::policy::SnappyDecompress(const IOBuf&, IOBuf*) for a batch
  * (snappy_compress.cpp:57-61).  Decoded message i = out[out_off[i], out_off[i+1]);
- * status[i] as for b2c_snappy_decompress_dev (a failed message occupies 0 bytes). */
+ * status[i] as for b2c_snappy_decompress_dev.  Slot i is as long as stream i's preamble
+ * claims (0 when the preamble is malformed or claims more than a stream of that size can
+ * expand to), so a stream that fails later still occupies its slot, contents unspecified. */
 int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin,
                                 uint32_t n, void* out, uint64_t out_cap, uint64_t* out_off,
                                 int32_t* status);
+
+/* The sender's two passes over a body in one: b2c_snappy_compress_batch plus
+ * crc[i] = butil::crc32c::Value(body i) (crc32c.h:31-33), or Mask() of it when masked != 0
+ * (crc32c.h:44-48) -- the pair a checksummed, snappy-compressed frame carries
+ * (framing_format.txt:39-59).  The bodies cross PCIe once for both results.  No single
+ * counterpart in the reference: it replaces the SnappyCompress call and the crc32c::Value
+ * call a sender makes on the same IOBuf. */
+int b2c_snappy_compress_crc_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin,
+                                  uint32_t n, void* out, uint64_t out_cap, uint64_t* out_off,
+                                  uint32_t* crc, int masked);
+
+/* The receiver's counterpart: b2c_snappy_decompress_batch plus the check of
+ * b2c_snappy_decompress_verify_dev against masked_crc[i]; status[i] additionally takes
+ * B2C_CRC_MISMATCH.  The decoded bytes are checksummed in HBM before they leave the GPU. */
+int b2c_snappy_decompress_verify_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin,
+                                       uint32_t n, const uint32_t* masked_crc, void* out,
+                                       uint64_t out_cap, uint64_t* out_off, int32_t* status);
 
 /* butil::crc32c::Extend for a batch (crc32c.h:19-29); init may be NULL (== Value). */
 int b2c_crc32c_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n,

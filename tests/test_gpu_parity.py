@@ -303,6 +303,47 @@ def test_e2e_iovec_batches(codec, cpu):
         assert h2d > 0 and d2h > 0
 
 
+def test_e2e_fused_sender_and_receiver_calls(codec, cpu):
+    """compress+crc in one pass, decompress+verify in one pass: same bytes and checksums as the separate calls
+    (and as the CPU checker), and a flipped checksum / a damaged stream are told apart."""
+    import brpc_b200
+    rng = np.random.default_rng(5)
+    lens = np.concatenate([np.full(6000, 1024), rng.integers(0, 3000, 500), [0, 1, 70000, 1 << 20]]).astype(np.uint32)
+    arena, off, ln = O.corpus_batch("words", lens, first_index=3)
+    segs, sb = brpc_b200.make_iovecs(arena, off, ln, seg_bytes=8160)
+    cap = int(sum(32 + int(l) + int(l) // 6 + 5 for l in ln))
+    out, out2 = np.empty(cap, dtype=np.uint8), codec.pinned(cap)
+    ref_off = codec.compress_batch(segs, sb, out)
+    want_crc, _ = cpu.batch_crc32c(arena, off, ln, threads=8)
+    for masked in (False, True):
+        o_off, crc = codec.compress_crc_batch(segs, sb, out2, masked=masked)
+        assert (o_off == ref_off).all()
+        assert out2[:int(o_off[-1])].tobytes() == out[:int(ref_off[-1])].tobytes()
+        want = np.array([cpu.mask(int(c)) for c in want_crc], dtype=np.uint32) if masked else want_crc
+        assert (crc == want).all()
+    # receiver: streams back in 100-byte blocks, one checksum flipped, one stream damaged
+    clen = np.diff(ref_off).astype(np.uint32)
+    damaged = out.copy()
+    victim = 17
+    damaged[int(ref_off[victim]) + 3] ^= 0xFF  # 2 preamble bytes, the literal's tag, then its first byte: decodes, to other bytes
+    csegs, csb = brpc_b200.make_iovecs(damaged, ref_off[:-1], clen, seg_bytes=100)
+    bad_crc = crc.copy()
+    bad_crc[40] ^= 1
+    back = codec.pinned(int(ln.astype(np.uint64).sum()) + 64)
+    b_off, status = codec.decompress_verify_batch(csegs, csb, bad_crc, back)
+    expect = np.zeros(len(ln), dtype=np.int32)
+    expect[40] = 3  # B2C_CRC_MISMATCH
+    ok = [i for i in range(len(ln)) if i != victim]
+    assert (status[ok] == expect[ok]).all()
+    assert status[victim] == 3
+    assert (np.diff(b_off).astype(np.uint32) == ln).all()
+    for i in list(range(0, len(ln), 97)) + [len(ln) - 1, len(ln) - 2]:
+        if i == victim:
+            continue
+        a, b = int(off[i]), int(off[i]) + int(ln[i])
+        assert_bytes_equal(back[int(b_off[i]):int(b_off[i + 1])].tobytes(), arena[a:b].tobytes(), f"fused back {i}")
+
+
 def test_e2e_decompress_rejects_like_reference(codec, golden):
     import brpc_b200
     es = [e for e in golden["malformed"] if e["stream"]]
