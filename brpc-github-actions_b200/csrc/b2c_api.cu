@@ -18,6 +18,7 @@
 #include <chrono>
 #include <condition_variable>
 #include <functional>
+#include <memory>
 #include <mutex>
 #include <new>
 #include <thread>
@@ -110,7 +111,8 @@ public:
     // run fn(t, T) for t in [0, T) with T = min(size, want)
     void run(unsigned want, const std::function<void(unsigned, unsigned)>& fn) {
         unsigned T = std::max(1u, std::min(n_, want));
-        if (T == 1) {
+        // a section started by this very thread is still running on the workers: do the work here
+        if (T == 1 || (async_.load(std::memory_order_acquire) && owner_.load(std::memory_order_relaxed) == std::this_thread::get_id())) {
             fn(0, 1);
             return;
         }
@@ -118,6 +120,7 @@ public:
         {
             std::lock_guard<std::mutex> g(mu_);
             fn_ = &fn;
+            base_ = 0;
             active_ = T;
             pending_ = T - 1;
             gen_++;
@@ -128,13 +131,48 @@ public:
         done_cv_.wait(g, [this] { return pending_ == 0; });
         fn_ = nullptr;
     }
+    // Start fn(t, T) on the WORKERS only and return; the caller goes on with other work and
+    // must call wait() (same thread) before the next start().  Without workers it runs here.
+    void start(unsigned want, std::function<void(unsigned, unsigned)> fn) {
+        if (n_ == 1) {
+            fn(0, 1);
+            return;
+        }
+        run_mu_.lock();
+        owner_.store(std::this_thread::get_id(), std::memory_order_relaxed);
+        async_.store(true, std::memory_order_release);
+        afn_ = std::move(fn);
+        const unsigned T = std::max(1u, std::min(n_ - 1, want));
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            fn_ = &afn_;
+            base_ = 1;
+            active_ = T;
+            pending_ = T;
+            gen_++;
+        }
+        cv_.notify_all();
+    }
+    bool started_here() const {
+        return async_.load(std::memory_order_acquire) && owner_.load(std::memory_order_relaxed) == std::this_thread::get_id();
+    }
+    void wait() {
+        if (!started_here()) return;
+        {
+            std::unique_lock<std::mutex> g(mu_);
+            done_cv_.wait(g, [this] { return pending_ == 0; });
+            fn_ = nullptr;
+        }
+        async_.store(false, std::memory_order_release);
+        run_mu_.unlock();
+    }
 
 private:
     void loop(unsigned t) {
         uint64_t seen = 0;
         for (;;) {
             const std::function<void(unsigned, unsigned)>* fn = nullptr;
-            unsigned T = 0;
+            unsigned T = 0, t_rel = 0;
             {
                 std::unique_lock<std::mutex> g(mu_);
                 cv_.wait(g, [&] { return gen_ != seen; });
@@ -142,9 +180,10 @@ private:
                 if (stop_) return;
                 fn = fn_;
                 T = active_;
+                t_rel = t - base_;  // the caller is share 0 of a synchronous section, not of a started one
             }
-            if (fn && t < T) {
-                (*fn)(t, T);
+            if (fn && t >= base_ && t_rel < T) {
+                (*fn)(t_rel, T);
                 std::lock_guard<std::mutex> g(mu_);
                 if (--pending_ == 0) done_cv_.notify_one();
             }
@@ -155,6 +194,10 @@ private:
     std::mutex mu_, run_mu_;
     std::condition_variable cv_, done_cv_;
     const std::function<void(unsigned, unsigned)>* fn_ = nullptr;
+    std::function<void(unsigned, unsigned)> afn_;  // the started section's function (owned)
+    std::atomic<bool> async_{false};
+    std::atomic<std::thread::id> owner_{};
+    unsigned base_ = 0;  // first participating worker id
     unsigned active_ = 0, pending_ = 0;
     uint64_t gen_ = 0;
     bool stop_ = false;
@@ -185,17 +228,27 @@ static unsigned threads_for(uint64_t bytes) { return (unsigned)std::min<uint64_t
 static inline int frag_class(uint32_t fl) { return fl <= 1024 ? 0 : fl <= 4096 ? 1 : 2; }
 static inline int slot_class(uint32_t cap) { return cap <= 1024 ? 0 : cap <= 8192 ? 1 : 2; }
 
-namespace {
-struct PlanStats {
-    uint64_t payload = 0, arena_end = 0, max_comp = 0, slot_sum = 0, F = 0, C = 0;
-    uint32_t max_len = 0, n_multi = 0, n_class[3] = {0, 0, 0}, n_dclass[3] = {0, 0, 0};
-};
+void PlanStats::merge(const PlanStats& p) {
+    payload += p.payload;
+    arena_end = std::max(arena_end, p.arena_end);
+    max_comp += p.max_comp;
+    slot_sum += p.slot_sum;
+    F += p.F;
+    C += p.C;
+    max_len = std::max(max_len, p.max_len);
+    n_multi += p.n_multi;
+    for (int c = 0; c < 3; c++) {
+        n_class[c] += p.n_class[c];
+        n_dclass[c] += p.n_dclass[c];
+    }
+}
+
 void plan_range(const uint64_t* off, const uint32_t* len, uint32_t lo, uint32_t hi, PlanStats& st) {
     const uint64_t full_slot = align_up(max_clen(kFragBytes), 16);
     for (uint32_t m = lo; m < hi; m++) {
         const uint32_t l = len[m];
         st.payload += l;
-        st.arena_end = std::max<uint64_t>(st.arena_end, off[m] + l);
+        if (off) st.arena_end = std::max<uint64_t>(st.arena_end, off[m] + l);
         st.max_comp += max_clen(l) + 5;
         st.max_len = std::max(st.max_len, l);
         const uint32_t nf = l ? (uint32_t)(((uint64_t)l + kFragBytes - 1) / kFragBytes) : 1u;
@@ -210,15 +263,12 @@ void plan_range(const uint64_t* off, const uint32_t* len, uint32_t lo, uint32_t 
         st.n_dclass[slot_class(l)]++;
     }
 }
-}  // namespace
 
 void LayoutPlan::plan(uint32_t n_, const uint64_t* off_, const uint32_t* len_, b2c_ctx* par) {
-    n = n_;
-    off = off_;
-    len = len_;
-    v = LayoutView();
-    v.n = n;
     PlanStats tot;
+    const uint32_t n = n_;
+    const uint64_t* off = off_;
+    const uint32_t* len = len_;
     if (par && n >= (1u << 14)) {
         PlanStats part[64];
         unsigned used = 1;
@@ -226,24 +276,19 @@ void LayoutPlan::plan(uint32_t n_, const uint64_t* off_, const uint32_t* len_, b
             if (t == 0) used = T;
             plan_range(off, len, (uint32_t)((uint64_t)n * t / T), (uint32_t)((uint64_t)n * (t + 1) / T), part[t]);
         });
-        for (unsigned t = 0; t < used; t++) {
-            const PlanStats& p = part[t];
-            tot.payload += p.payload;
-            tot.arena_end = std::max(tot.arena_end, p.arena_end);
-            tot.max_comp += p.max_comp;
-            tot.slot_sum += p.slot_sum;
-            tot.F += p.F;
-            tot.C += p.C;
-            tot.max_len = std::max(tot.max_len, p.max_len);
-            tot.n_multi += p.n_multi;
-            for (int c = 0; c < 3; c++) {
-                tot.n_class[c] += p.n_class[c];
-                tot.n_dclass[c] += p.n_dclass[c];
-            }
-        }
+        for (unsigned t = 0; t < used; t++) tot.merge(part[t]);
     } else {
         plan_range(off, len, 0, n, tot);
     }
+    plan_with(n_, off_, len_, tot);
+}
+
+void LayoutPlan::plan_with(uint32_t n_, const uint64_t* off_, const uint32_t* len_, const PlanStats& tot) {
+    n = n_;
+    off = off_;
+    len = len_;
+    v = LayoutView();
+    v.n = n;
     v.payload = tot.payload;
     v.arena_end = tot.arena_end;
     v.max_comp = tot.max_comp;
@@ -469,6 +514,7 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     if (const char* s = getenv("B2C_SMALL_KERNELS")) ctx->small_kernels = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL_LPW_C")) ctx->small_lpw_compress = atoi(s);
     if (const char* s = getenv("B2C_WINDOW")) ctx->window_mask = atoi(s);
+    if (const char* s = getenv("B2C_ASYNC_GATHER")) ctx->async_gather = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL2")) ctx->small_two_phase = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL_LPW_D")) ctx->small_lpw_decompress = atoi(s);
     int rc = B2C_OK;
@@ -808,13 +854,15 @@ int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, u
         const uint32_t skew = zc && seg_begin[i] < seg_begin[i + 1]
                                   ? (uint32_t)(reinterpret_cast<uintptr_t>(segs[seg_begin[i]].iov_base) & 15)
                                   : 0u;
-        const uint64_t a = align_up((uint64_t)skew + p.len[i], 16);
+        // staged: a message of >= 256 bytes starts on a 64-byte line, so the gather writes whole lines only
+        const uint64_t pad = (!zc && p.len[i] >= 256) ? align_up(cur.bytes, 64) - cur.bytes : 0;
+        const uint64_t a = pad + align_up((uint64_t)skew + p.len[i], 16);
         if (cur.m1 > cur.m0 && (cur.bytes + a > target || cur.m1 - cur.m0 >= max_msgs)) {
             p.slabs.push_back(cur);
             cur = {i, i, 0, 0};
         }
-        p.off[i] = cur.bytes + skew;
-        cur.bytes += a;
+        p.off[i] = cur.bytes + (cur.bytes ? pad : 0) + skew;
+        cur.bytes += cur.bytes ? a : a - pad;
         cur.payload += p.len[i];
         cur.m1 = i + 1;
         p.payload += p.len[i];
@@ -823,50 +871,39 @@ int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, u
     return B2C_OK;
 }
 
-// Copy with non-temporal stores: staging is written once by the CPU and then only read by the
-// DMA engine, so bypassing the cache saves the read-for-ownership of every destination line.
-inline void copy_stream(uint8_t* dst, const uint8_t* src, size_t n) {
-    if (n < 256) {
-        memcpy(dst, src, n);
-        return;
-    }
-    // whole 64-byte destination lines only: a partially written write-combining buffer is costly
-    size_t head = (64 - (reinterpret_cast<uintptr_t>(dst) & 63)) & 63;
-    if (head) {
-        memcpy(dst, src, head);
-        dst += head;
-        src += head;
-        n -= head;
-    }
-    size_t blocks = n / 64;
-    for (size_t i = 0; i < blocks; i++) {
-        __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src));
-        __m128i b = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + 16));
-        __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + 32));
-        __m128i d = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + 48));
-        _mm_stream_si128(reinterpret_cast<__m128i*>(dst), a);
-        _mm_stream_si128(reinterpret_cast<__m128i*>(dst + 16), b);
-        _mm_stream_si128(reinterpret_cast<__m128i*>(dst + 32), c);
-        _mm_stream_si128(reinterpret_cast<__m128i*>(dst + 48), d);
-        src += 64;
-        dst += 64;
-    }
-    n -= blocks * 64;
-    if (n) memcpy(dst, src, n);
-}
-
 // memcpy every segment of the slab's messages into pinned staging.  When `caps` is given the
 // messages are snappy streams: the thread that just copied a stream also reads its (lenient)
 // preamble while the bytes are still in its cache and records the plausible output size
 // (0 = malformed or impossible claim; a stream cannot expand more than 64/3 times, snappy.cc:867).
-void gather_slab(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, const BatchPlan& p, const Slab& s,
-                 uint8_t* stage, uint32_t* caps = nullptr) {
+// Layout statistics the gathering workers collect on the way (so the submitting thread does not
+// have to walk the slab's messages again): one PlanStats per worker, merged by the caller.
+struct SlabStats {
+    PlanStats in[64];    // of the slab's messages as laid out in staging
+    PlanStats caps[64];  // of the preamble-derived output slots (decompress)
+    void merged(PlanStats& a, PlanStats& b) const {
+        for (int t = 0; t < 64; t++) a.merge(in[t]), b.merge(caps[t]);
+    }
+};
+
+std::function<void(unsigned, unsigned)> gather_job(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin,
+                                                   const BatchPlan& p, const Slab s, uint8_t* stage, uint32_t* caps,
+                                                   SlabStats* stats) {
     const uint32_t cnt = s.m1 - s.m0;
     const bool stream = ctx->nt_gather;
-    pool(ctx).run(threads_for(s.bytes), [&](unsigned t, unsigned T) {
-        uint32_t lo = s.m0 + (uint32_t)((uint64_t)cnt * t / T), hi = s.m0 + (uint32_t)((uint64_t)cnt * (t + 1) / T);
+    const uint64_t* poff = p.off.data();
+    const uint32_t* plen = p.len.data();
+    // messages are handed out in chunks of ~256 KiB from a shared counter: with every core busy a
+    // static split would wait for whichever worker the OS preempted
+    auto next = std::make_shared<std::atomic<uint32_t>>(0u);
+    const uint32_t chunk = (uint32_t)std::min<uint64_t>(1024, std::max<uint64_t>(1, (256u << 10) / (s.bytes / std::max(cnt, 1u) + 1)));
+    return [=](unsigned t, unsigned) {
+        for (;;) {
+        const uint32_t c0 = next->fetch_add(chunk, std::memory_order_relaxed);
+        if (c0 >= cnt) break;
+        const uint32_t lo = s.m0 + c0, hi = s.m0 + std::min(cnt, c0 + chunk);
+        if (stats) plan_range(poff, plen, lo, hi, stats->in[t & 63]);
         for (uint32_t i = lo; i < hi; i++) {
-            uint8_t* d = stage + p.off[i];
+            uint8_t* d = stage + poff[i];
             if (caps) {
                 uint8_t head[5];
                 size_t got = 0;
@@ -875,18 +912,31 @@ void gather_slab(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin,
                         head[got++] = static_cast<const uint8_t*>(segs[q].iov_base)[j];
                 uint32_t ulen = 0;
                 const int kk = b2c_snappy_read_preamble(head, got, &ulen);
-                const bool plausible = kk > 0 && (uint64_t)ulen <= ((uint64_t)p.len[i] * 64) / 3 + 64;
+                const bool plausible = kk > 0 && (uint64_t)ulen <= ((uint64_t)plen[i] * 64) / 3 + 64;
                 caps[i - s.m0] = plausible ? ulen : 0;
             }
-            for (uint32_t q = seg_begin[i]; q < seg_begin[i + 1]; q++) {
-                if (stream) copy_stream(d, static_cast<const uint8_t*>(segs[q].iov_base), segs[q].iov_len);
-                else memcpy(d, segs[q].iov_base, segs[q].iov_len);
-                d += segs[q].iov_len;
-            }
+            gather_message(d, segs + seg_begin[i], seg_begin[i + 1] - seg_begin[i], plen[i], stream);
         }
-        if (stream) _mm_sfence();
-    });
+        if (stats && caps) plan_range(nullptr, caps, lo - s.m0, hi - s.m0, stats->caps[t & 63]);
+        }
+        if (stream) gather_fence();
+    };
 }
+
+// Start gathering a slab on the pool's workers; the calling thread goes on (layouts, submits,
+// copy-outs of other slabs) and calls pool(ctx).wait() before it touches the staging.
+void gather_slab_start(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, const BatchPlan& p, const Slab& s,
+                       uint8_t* stage, uint32_t* caps, SlabStats* stats) {
+    *stats = SlabStats();
+    pool(ctx).start(threads_for(s.bytes), gather_job(ctx, segs, seg_begin, p, s, stage, caps, stats));
+    if (!ctx->async_gather) pool(ctx).wait();
+}
+
+// Ends a started section on every way out of a *_batch call.
+struct PoolGuard {
+    b2c_ctx* ctx;
+    ~PoolGuard() { pool(ctx).wait(); }
+};
 
 void parallel_copy(b2c_ctx* ctx, void* dst, const void* src, uint64_t bytes) {
     if (!bytes) return;
@@ -1021,29 +1071,65 @@ int b2c_crc32c_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_be
         TIMED(tr.copy_out, memcpy(crc + s.m0, lane.h_out.p, (size_t)(s.m1 - s.m0) * 4));
         return B2C_OK;
     };
-    for (size_t k = 0; k < K; k++) {
-        if (k >= (size_t)kPipeLanes && (rc = finish(k - kPipeLanes))) return rc;
+    // Slab k+1 is gathered by the pool's workers while this thread lays out, submits and retires
+    // the slabs around it.
+    // The staging offset of the metadata is known before the layout is (meta_at depends on the payload only), so
+    // the gather can start first and the layout is sized afterwards from the statistics the workers collected.
+    struct Prep {
+        LayoutPlan lp;
+        SlabIO io;
+        size_t init_rel = 0, meta_bytes = 0;
+    } prep[2];
+    std::unique_ptr<SlabStats[]> stats(new SlabStats[2]);
+    PoolGuard guard{ctx};
+    auto layout = [&](size_t k) {  // after the gather: size the layout
+        const Slab& s = bp.slabs[k];
+        const uint32_t cnt = s.m1 - s.m0;
+        Prep& P = prep[k & 1];
+        if (ctx->input_pinned) {
+            P.lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, nullptr);
+        } else {
+            PlanStats a, b;
+            stats[k & 1].merged(a, b);
+            P.lp.plan_with(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, a);
+        }
+        P.init_rel = align_up(P.lp.blob_bytes, 256);  // metadata: layout blob | init values
+        P.meta_bytes = P.init_rel + (init ? (size_t)cnt * 4 : 0);
+    };
+    auto prepare = [&](size_t k) -> int {  // reserve the lane's input side and start the gather
         Lane& lane = ctx->pipe[k % kPipeLanes];
         const Slab& s = bp.slabs[k];
         const uint32_t cnt = s.m1 - s.m0;
-        LayoutPlan lp;
-        TIMED(tr.layout, lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx));
-        const size_t init_rel = align_up(lp.blob_bytes, 256);            // metadata: layout blob | init values
-        const size_t meta_bytes = init_rel + (init ? (size_t)cnt * 4 : 0);
-        SlabIO io;
-        if ((rc = slab_begin(ctx, lane, seg_begin, s, meta_bytes, io))) return rc;
-        if ((rc = pin_reserve(ctx, lane, lane.h_out, (size_t)cnt * 4 + 64))) return rc;
-        if ((rc = ws_reserve(ctx, lane, lane.d_out, (size_t)cnt * 4 + 64))) return rc;
+        int r;
+        Prep& P = prep[k & 1];
+        if (ctx->input_pinned) layout(k);  // no gather to hide it behind: the exact size now
+        const size_t meta_cap = ctx->input_pinned ? P.meta_bytes
+                                                  : LayoutPlan::max_blob_bytes(cnt, s.payload) + 256 + (size_t)cnt * 4;
+        if ((r = slab_begin(ctx, lane, seg_begin, s, meta_cap, P.io))) return r;
+        if ((r = pin_reserve(ctx, lane, lane.h_out, (size_t)cnt * 4 + 64))) return r;
+        if ((r = ws_reserve(ctx, lane, lane.d_out, (size_t)cnt * 4 + 64))) return r;
         if (!ctx->input_pinned)
-            TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, static_cast<uint8_t*>(lane.h_in.p)));
-        TIMED(tr.layout, lp.fill(io.stage_meta));
-        if (init) memcpy(io.stage_meta + init_rel, init + s.m0, (size_t)cnt * 4);
+            gather_slab_start(ctx, segs, seg_begin, bp, s, static_cast<uint8_t*>(lane.h_in.p), nullptr, &stats[k & 1]);
+        return B2C_OK;
+    };
+    if ((rc = prepare(0))) return rc;
+    for (size_t k = 0; k < K; k++) {
+        TIMED(tr.gather, pool(ctx).wait());
+        if (k + 1 >= (size_t)kPipeLanes && (rc = finish(k + 1 - kPipeLanes))) return rc;  // frees slab k+1's lane
+        if (k + 1 < K && (rc = prepare(k + 1))) return rc;
+        Lane& lane = ctx->pipe[k % kPipeLanes];
+        const Slab& s = bp.slabs[k];
+        const uint32_t cnt = s.m1 - s.m0;
+        Prep& P = prep[k & 1];
+        if (!ctx->input_pinned) TIMED(tr.layout, layout(k));
+        TIMED(tr.layout, P.lp.fill(P.io.stage_meta));
+        if (init) memcpy(P.io.stage_meta + P.init_rel, init + s.m0, (size_t)cnt * 4);
         auto ts = Clock::now();
-        uint8_t* d_in = io.d_in;
+        uint8_t* d_in = P.io.d_in;
         LayoutView lv;
-        lp.bind(d_in + io.meta_at, &lv);
-        if ((rc = slab_submit(ctx, lane, segs, seg_begin, s, io, meta_bytes, lv.d_off, h2d))) return rc;
-        const size_t init_at = io.meta_at + init_rel;
+        P.lp.bind(d_in + P.io.meta_at, &lv);
+        if ((rc = slab_submit(ctx, lane, segs, seg_begin, s, P.io, P.meta_bytes, lv.d_off, h2d))) return rc;
+        const size_t init_at = P.io.meta_at + P.init_rel;
         uint32_t* d_crc = static_cast<uint32_t*>(lane.d_out.p);
         if ((rc = launch_crc32c(ctx, lane, lv, d_in, init ? reinterpret_cast<uint32_t*>(d_in + init_at) : nullptr, d_crc)))
             return rc;
@@ -1052,7 +1138,7 @@ int b2c_crc32c_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_be
         B2C_CUDA(ctx, cudaEventRecord(lane.ev_done, lane.stream));
         tr.submit += secs(ts, Clock::now());
     }
-    for (size_t k = K > (size_t)kPipeLanes ? K - kPipeLanes : 0; k < K; k++)
+    for (size_t k = K + 1 > (size_t)kPipeLanes ? K + 1 - kPipeLanes : 0; k < K; k++)
         if ((rc = finish(k))) return rc;
     ctx->last_h2d = h2d;
     ctx->last_d2h = d2h;
@@ -1121,44 +1207,77 @@ static int compress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint32
         tr.copy_out += secs(tc, Clock::now());
         return B2C_OK;
     };
-    // software pipeline over the lanes: slab k is submitted, slab k-2's sizes are read and its bytes fetched,
-    // slab k-3 is handed to the caller -- so the host never waits for the slab it has just submitted
+    // Software pipeline over the lanes.  While the pool's workers gather slab k+1, this thread retires slab k-3
+    // (which frees slab k+1's lane), lays out and submits slab k, and reads slab k-2's sizes to fetch its bytes --
+    // so it never waits for the slab it has just submitted.
+    struct Prep {
+        LayoutPlan lp;
+        SlabIO io;
+        size_t meta_bytes = 0, out_meta_bytes = 0, off_at = 0;
+        uint64_t cap = 0;
+    } prep[2];
+    std::unique_ptr<SlabStats[]> stats(new SlabStats[2]);
+    PoolGuard guard{ctx};
+    auto layout = [&](size_t k) {  // size the layout: from the workers' statistics once the gather is through
+        const Slab& s = bp.slabs[k];
+        const uint32_t cnt = s.m1 - s.m0;
+        Prep& P = prep[k & 1];
+        if (ctx->input_pinned) {
+            P.lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, nullptr);
+        } else {
+            PlanStats a, b;
+            stats[k & 1].merged(a, b);
+            P.lp.plan_with(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, a);
+        }
+        P.meta_bytes = P.lp.blob_bytes;
+    };
+    auto prepare = [&](size_t k) -> int {  // reserve the lane's buffers and start the gather
+        Lane& lane = ctx->pipe[k % kPipeLanes];
+        const Slab& s = bp.slabs[k];
+        const uint32_t cnt = s.m1 - s.m0;
+        Prep& P = prep[k & 1];
+        if (ctx->input_pinned) layout(k);
+        // sum of MaxCompressedLength(len)+5 without walking the messages: 32 + len + len/6 + 5 each
+        P.cap = s.payload + s.payload / 6 + 37ull * cnt;
+        P.out_meta_bytes = ((size_t)cnt + 1) * 8 + (crc ? (size_t)cnt * 4 : 0);
+        P.off_at = align_up(P.cap, 256);  // device: packed output, then its offsets (then the checksums)
+        int r;
+        const size_t meta_cap = ctx->input_pinned ? P.meta_bytes : LayoutPlan::max_blob_bytes(cnt, s.payload);
+        if ((r = slab_begin(ctx, lane, seg_begin, s, meta_cap, P.io))) return r;
+        if ((r = ws_reserve(ctx, lane, lane.d_out, P.off_at + P.out_meta_bytes + 64))) return r;
+        if ((r = pin_reserve(ctx, lane, lane.h_out, align_up(P.out_meta_bytes, 256) + (direct ? 0 : P.cap) + 64))) return r;
+        if (!ctx->input_pinned)
+            gather_slab_start(ctx, segs, seg_begin, bp, s, static_cast<uint8_t*>(lane.h_in.p), nullptr, &stats[k & 1]);
+        return B2C_OK;
+    };
+    if ((rc = prepare(0))) return rc;
     for (size_t k = 0; k < K + 3; k++) {
+        if (k < K) TIMED(tr.gather, pool(ctx).wait());
+        if (k >= 3 && k - 3 < K && (rc = finish(k - 3))) return rc;  // frees slab k+1's lane; the pool is idle here
         if (k < K) {
+            if (k + 1 < K && (rc = prepare(k + 1))) return rc;
             Lane& lane = ctx->pipe[k % kPipeLanes];
             const Slab& s = bp.slabs[k];
             const uint32_t cnt = s.m1 - s.m0;
-            LayoutPlan lp;
-            TIMED(tr.layout, lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx));
-            const size_t meta_bytes = lp.blob_bytes;
-            const uint64_t cap = lp.v.max_comp;
-            const size_t out_meta_bytes = ((size_t)cnt + 1) * 8 + (crc ? (size_t)cnt * 4 : 0);
-            const size_t off_at = align_up(cap, 256);  // device: packed output, then its offsets
-            SlabIO io;
-            if ((rc = slab_begin(ctx, lane, seg_begin, s, meta_bytes, io))) return rc;
-            if ((rc = ws_reserve(ctx, lane, lane.d_out, off_at + out_meta_bytes + 64))) return rc;
-            if ((rc = pin_reserve(ctx, lane, lane.h_out, align_up(out_meta_bytes, 256) + (direct ? 0 : cap) + 64))) return rc;
-            if (!ctx->input_pinned)
-                TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, static_cast<uint8_t*>(lane.h_in.p)));
-            TIMED(tr.layout, lp.fill(io.stage_meta));
+            Prep& P = prep[k & 1];
+            if (!ctx->input_pinned) TIMED(tr.layout, layout(k));
+            TIMED(tr.layout, P.lp.fill(P.io.stage_meta));
             auto ts = Clock::now();
-            uint8_t* d_in = io.d_in;
+            uint8_t* d_in = P.io.d_in;
             LayoutView lv;
-            lp.bind(d_in + io.meta_at, &lv);
-            if ((rc = slab_submit(ctx, lane, segs, seg_begin, s, io, meta_bytes, lv.d_off, h2d))) return rc;
-            const size_t meta_bytes_out = out_meta_bytes;
+            P.lp.bind(d_in + P.io.meta_at, &lv);
+            if ((rc = slab_submit(ctx, lane, segs, seg_begin, s, P.io, P.meta_bytes, lv.d_off, h2d))) return rc;
             uint8_t* d_out = static_cast<uint8_t*>(lane.d_out.p);
-            uint64_t* d_out_off = reinterpret_cast<uint64_t*>(d_out + off_at);
+            uint64_t* d_out_off = reinterpret_cast<uint64_t*>(d_out + P.off_at);
             if (crc && (rc = launch_crc32c(ctx, lane, lv, d_in, nullptr, reinterpret_cast<uint32_t*>(d_out_off + cnt + 1))))
                 return rc;
-            if ((rc = launch_compress(ctx, lane, lv, d_in, d_out, cap, d_out_off))) return rc;
-            B2C_CUDA(ctx, cudaMemcpyAsync(lane.h_out.p, d_out_off, meta_bytes_out, cudaMemcpyDeviceToHost, lane.stream));
-            d2h += meta_bytes_out;
+            if ((rc = launch_compress(ctx, lane, lv, d_in, d_out, P.cap, d_out_off))) return rc;
+            B2C_CUDA(ctx, cudaMemcpyAsync(lane.h_out.p, d_out_off, P.out_meta_bytes, cudaMemcpyDeviceToHost, lane.stream));
+            d2h += P.out_meta_bytes;
             B2C_CUDA(ctx, cudaEventRecord(lane.ev_meta, lane.stream));
             tr.submit += secs(ts, Clock::now());
         }
         if (k >= 2 && k - 2 < K && (rc = fetch(k - 2))) return rc;
-        if (k >= 3 && k - 3 < K && (rc = finish(k - 3))) return rc;
     }
     ctx->last_h2d = h2d;
     ctx->last_d2h = d2h;
@@ -1193,7 +1312,6 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
     const size_t K = bp.slabs.size();
     std::vector<uint64_t> slab_out(K, 0);
     std::vector<uint64_t>& o_off = ctx->tmp_off;
-    std::vector<uint32_t>& o_cap = ctx->tmp_cap;
     const bool direct = is_pinned_host(out);  // caller's buffer is page-locked: DMA straight into it
     auto finish = [&](size_t k) -> int {
         Lane& lane = ctx->pipe[k % kPipeLanes];
@@ -1210,24 +1328,48 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
         tr.copy_out += secs(tc, Clock::now());
         return B2C_OK;
     };
-    for (size_t k = 0; k < K; k++) {
-        if (k >= (size_t)kPipeLanes && (rc = finish(k - kPipeLanes))) return rc;
+    // While the pool's workers gather slab k+1 (and read its preambles), this thread sizes slab k's output
+    // slots from ITS preambles, lays it out, submits it and retires slab k-3.
+    LayoutPlan lin_ring[2];
+    std::vector<uint32_t>* cap_ring[2] = {&ctx->tmp_cap, &ctx->tmp_cap2};
+    std::unique_ptr<SlabStats[]> stats(new SlabStats[2]);
+    PoolGuard guard{ctx};
+    auto prepare = [&](size_t k) -> int {
         Lane& lane = ctx->pipe[k % kPipeLanes];
         const Slab& s = bp.slabs[k];
         const uint32_t cnt = s.m1 - s.m0;
-        LayoutPlan lin;
-        TIMED(tr.layout, lin.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx));
-        if (o_off.size() < cnt) o_off.resize(cnt);
-        if (o_cap.size() < cnt) o_cap.resize(cnt);
+        std::vector<uint32_t>& caps = *cap_ring[k & 1];
+        if (caps.size() < cnt) caps.resize(cnt);
         // output slot sizes come from the (lenient) preambles
         if (ctx->input_pinned) {
-            TIMED(tr.gather, slab_caps(ctx, segs, seg_begin, bp, s, o_cap.data()));
+            TIMED(tr.layout, lin_ring[k & 1].plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, nullptr));
+            TIMED(tr.gather, slab_caps(ctx, segs, seg_begin, bp, s, caps.data()));
         } else {  // read by the gathering threads while the bytes are in their cache
-            if ((rc = pin_reserve(ctx, lane, lane.h_in, align_up(s.bytes, 256) + lin.blob_bytes + (size_t)cnt * 16 + 4096)))
-                return rc;
-            TIMED(tr.gather, gather_slab(ctx, segs, seg_begin, bp, s, static_cast<uint8_t*>(lane.h_in.p), o_cap.data()));
+            int r;
+            if ((r = pin_reserve(ctx, lane, lane.h_in,
+                                 align_up(s.bytes, 256) + 2 * LayoutPlan::max_blob_bytes(cnt, s.payload) + (size_t)cnt * 16 + 4096)))
+                return r;
+            gather_slab_start(ctx, segs, seg_begin, bp, s, static_cast<uint8_t*>(lane.h_in.p), caps.data(), &stats[k & 1]);
         }
+        return B2C_OK;
+    };
+    if ((rc = prepare(0))) return rc;
+    for (size_t k = 0; k < K; k++) {
+        TIMED(tr.gather, pool(ctx).wait());
+        if (k + 1 >= (size_t)kPipeLanes && (rc = finish(k + 1 - kPipeLanes))) return rc;  // frees slab k+1's lane
+        if (k + 1 < K && (rc = prepare(k + 1))) return rc;
+        Lane& lane = ctx->pipe[k % kPipeLanes];
+        const Slab& s = bp.slabs[k];
+        const uint32_t cnt = s.m1 - s.m0;
+        LayoutPlan& lin = lin_ring[k & 1];
+        const std::vector<uint32_t>& o_cap = *cap_ring[k & 1];
+        if (o_off.size() < cnt) o_off.resize(cnt);
         auto tl = Clock::now();
+        PlanStats st_in, st_out;
+        if (!ctx->input_pinned) {
+            stats[k & 1].merged(st_in, st_out);
+            lin.plan_with(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, st_in);
+        }
         uint64_t pos = 0;
         for (uint32_t i = 0; i < cnt; i++) {
             o_off[i] = pos;
@@ -1239,7 +1381,12 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
         out_base += pos;
         out_off[s.m1] = out_base;
         LayoutPlan lout;
-        lout.plan(cnt, o_off.data(), o_cap.data(), ctx);
+        if (ctx->input_pinned) {
+            lout.plan(cnt, o_off.data(), o_cap.data(), nullptr);
+        } else {  // the workers summed everything but the end of the arena, which is the running total
+            st_out.arena_end = pos;
+            lout.plan_with(cnt, o_off.data(), o_cap.data(), st_out);
+        }
         const size_t blob_out_rel = align_up(lin.blob_bytes, 256);  // metadata: input layout blob | output layout blob | crcs
         const size_t crc_rel = align_up(blob_out_rel + lout.blob_bytes, 256);
         const size_t meta_bytes = masked_crc ? crc_rel + (size_t)cnt * 4 : blob_out_rel + lout.blob_bytes;
@@ -1279,7 +1426,7 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
         B2C_CUDA(ctx, cudaEventRecord(lane.ev_done, lane.stream));
         tr.submit += secs(ts, Clock::now());
     }
-    for (size_t k = K > (size_t)kPipeLanes ? K - kPipeLanes : 0; k < K; k++)
+    for (size_t k = K + 1 > (size_t)kPipeLanes ? K + 1 - kPipeLanes : 0; k < K; k++)
         if ((rc = finish(k))) return rc;
     ctx->last_h2d = h2d;
     ctx->last_d2h = d2h;

@@ -69,6 +69,15 @@ struct LayoutView {
     const uint32_t* d_multi_list = nullptr;    // [n_multi]
 };
 
+// What one pass over (off, len) has to know to size a layout; partial sums add up (merge).
+struct PlanStats {
+    uint64_t payload = 0, arena_end = 0, max_comp = 0, slot_sum = 0, F = 0, C = 0;
+    uint32_t max_len = 0, n_multi = 0, n_class[3] = {0, 0, 0}, n_dclass[3] = {0, 0, 0};
+    void merge(const PlanStats& p);
+};
+// accumulate messages [lo, hi); off may be null (arena_end is then left to the caller)
+void plan_range(const uint64_t* off, const uint32_t* len, uint32_t lo, uint32_t hi, PlanStats& st);
+
 // Host-side derivation of a LayoutView's arrays into one contiguous blob.
 struct LayoutPlan {
     uint32_t n = 0;
@@ -84,6 +93,12 @@ struct LayoutPlan {
 
     // `par`: when non-null, large batches are scanned with the ctx's host thread pool
     void plan(uint32_t n, const uint64_t* off, const uint32_t* len, b2c_ctx* par = nullptr);
+    void plan_with(uint32_t n, const uint64_t* off, const uint32_t* len, const PlanStats& tot);  // stats made elsewhere
+    // upper bound of blob_bytes for any layout of n messages totalling `payload` bytes
+    static size_t max_blob_bytes(uint32_t n, uint64_t payload) {
+        const uint64_t F = n + payload / kFragBytes, C = n + payload / kCrcChunk;
+        return (size_t)(28ull * n + 16 * F + 4 * C + 512);
+    }
     void fill(uint8_t* blob) const;                           // blob_bytes of host memory
     void bind(const uint8_t* d_blob, LayoutView* out) const;  // device address of the uploaded blob
 };
@@ -107,7 +122,7 @@ struct b2c_ctx {
     uint32_t prof_used[B2C_PROF_COUNT] = {0, 0, 0, 0};
     // reusable host arrays of the *_batch entry points (avoid page-faulting fresh vectors per call)
     std::vector<uint64_t> bp_off, tmp_off;
-    std::vector<uint32_t> bp_len, tmp_cap;
+    std::vector<uint32_t> bp_len, tmp_cap, tmp_cap2;
     int gtab_warps_per_sm = 16;  // B2C_GTAB_WPS: resident warps per SM of the HBM-table compressor (0 = shared-memory tables); 16 keeps all tables L2-resident
     bool small_kernels = true;  // B2C_SMALL_KERNELS=0 routes <=1 KiB bodies through the warp kernels
     int small_lpw_compress = 4, small_lpw_decompress = 8;  // bodies per warp (B2C_SMALL_LPW_C / _D: 4, 8, 16, 32)
@@ -122,6 +137,7 @@ struct b2c_ctx {
     bool batch_decode = true;        // B2C_BATCH_DECODE=0: one tag per step in the warp decoder
     bool batch_decode_small = false; // B2C_BATCH_DECODE_SMALL=1: <=1 KiB slots use the warp batch decoder, not one lane per stream
     bool nt_gather = true;  // B2C_NT_GATHER=0: plain memcpy into staging
+    bool async_gather = true;  // B2C_ASYNC_GATHER=0: the submitting thread waits for each slab's gather before anything else
     bool small_two_phase = true;  // B2C_SMALL2=0 restores the one-phase kernel; <=1 KiB bodies compress as find (lane per body) then encode (warp per body)
     int window_mask = 0;    // B2C_WINDOW: bit c set = fragment class c compresses with the window-parallel kernel
 };
@@ -171,6 +187,9 @@ int launch_compress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const u
                           uint32_t* d_frag_clen);
 int launch_decompress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint8_t* d_in,
                             const LayoutView& out, uint8_t* d_out, uint32_t* d_ulen, int32_t* d_status);
+// host_gather.cpp: one message's blocks concatenated into staging (non-temporal whole-line stores when `stream`)
+void gather_message(uint8_t* dst, const b2c_iovec* segs, uint32_t nseg, uint64_t total, bool stream);
+void gather_fence();
 // window-parallel warp-per-fragment compressor (snappy_window.cu); c = fragment class 0..2
 int window_kernels_configure(b2c_ctx* ctx);
 int launch_compress_window(b2c_ctx* ctx, Lane& lane, const LayoutView& L, int c, const uint8_t* d_in, uint8_t* scratch,
