@@ -292,49 +292,64 @@ __global__ void __launch_bounds__(1024 / LPW) snappy_compress_small_kernel(Small
 template <int TSTRIDE>
 __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const uint32_t n, uint16_t* tab,
                                                     uint32_t* __restrict__ elist) {
-    auto ld64s = [&](uint32_t p) -> uint64_t {
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(in_b + (p & ~3u));
-        const uint32_t a = w[0], b = w[1], c = w[2], sh = (p & 3) * 8;
-        return ((uint64_t)__funnelshift_r(b, c, sh) << 32) | __funnelshift_r(a, b, sh);
-    };
     uint32_t tsize = 256;  // GetHashTable sizing, snappy.cc:253-256
     while (tsize < 16384u && tsize < n) tsize <<= 1;
     const uint32_t shift = 32 - (31 - __clz(tsize));
-    uint32_t ne = 0;
+    uint32_t* ep = elist;
     if (n >= 15) {  // kInputMarginBytes, snappy.cc:344-347
         const uint32_t ip_limit = n - 15;
-        uint32_t ip = 1, skip = 32, nxt = 0;
-        bool probing = true, have_d = false;
-        uint64_t d = 0;  // bytes ip..ip+7 when have_d
-        for (;;) {  // the unified probe / copy-tail loop of small_compress_body
-            if (probing) {
-                nxt = ip + (skip++ >> 5);
-                if (nxt > ip_limit) break;  // snappy.cc:386-388
-            }
-            if (!have_d) d = ld64s(ip);
-            have_d = false;
-            const uint32_t h = hash_bytes_s((uint32_t)d, shift);
+        // `s` is the reference's `skip` (snappy.cc:377-385) with one extra state: s == 31 marks the table
+        // step the copy loop makes right after a copy (snappy.cc:430-439).  That step advances by one byte
+        // on a miss and is followed by the first probe of a fresh `skip = 32` sequence -- exactly what
+        // step = max(1, s >> 5), s++ yields -- so one loop without mode flags serves both.
+        uint32_t ip = 1, s = 32;
+        uint32_t d0, d1;  // bytes ip..ip+7
+        {
+            const uint32_t* w = reinterpret_cast<const uint32_t*>(in_b);
+            d0 = __funnelshift_r(w[0], w[1], 8);
+            d1 = __funnelshift_r(w[1], w[2], 8);
+        }
+        for (;;) {
+            const uint32_t nxt = ip + max(1u, s >> 5);
+            s++;
+            if (nxt > ip_limit) break;  // snappy.cc:386-388 (never true right after a copy: ip < ip_limit there)
+            const uint32_t h = hash_bytes_s(d0, shift);
             const uint32_t cand = tab[h * TSTRIDE];
             tab[h * TSTRIDE] = (uint16_t)ip;
-            const uint64_t x = ld64s(cand) ^ d;
-            if ((uint32_t)x == 0) {
-                uint32_t matched;  // FindMatchLength, snappy-internal.h:86-120
-                const uint32_t xh = (uint32_t)(x >> 32);
+            const uint32_t* wa = reinterpret_cast<const uint32_t*>(in_b + (cand & ~3u));
+            const uint32_t sa = (cand & 3) * 8;
+            const uint32_t a0 = wa[0], a1 = wa[1];
+            uint32_t a2 = wa[2];
+            if (__funnelshift_r(a0, a1, sa) == d0) {
+                // FindMatchLength, snappy-internal.h:86-120.  ip + 15 < n here, so the first 8 bytes are in range.
+                uint32_t matched;
+                const uint32_t xh = __funnelshift_r(a1, a2, sa) ^ d1;
                 if (xh) {
                     matched = 4 + ((uint32_t)(__ffs(xh) - 1) >> 3);
                 } else {
                     matched = 8;
+                    const uint32_t* wb = reinterpret_cast<const uint32_t*>(in_b + (ip & ~3u)) + 3;
+                    const uint32_t sb = (ip & 3) * 8;
+                    uint32_t b2 = wb[-1];
+                    wa += 3;  // wa / wb: the next unread word of each side; a2 / b2: the last one read
                     for (;;) {
                         const uint32_t rem = n - (ip + matched);
                         if (rem == 0) break;
-                        const uint64_t y = ld64s(cand + matched) ^ ld64s(ip + matched);
-                        uint32_t nb = y ? (uint32_t)(__ffsll((long long)y) - 1) >> 3 : 8u;
-                        nb = min(nb, rem);
+                        const uint32_t a3 = wa[0], a4 = wa[1], b3 = wb[0], b4 = wb[1];
+                        const uint32_t y0 = __funnelshift_r(a2, a3, sa) ^ __funnelshift_r(b2, b3, sb);
+                        const uint32_t y1 = __funnelshift_r(a3, a4, sa) ^ __funnelshift_r(b3, b4, sb);
+                        const uint32_t y = y0 ? y0 : y1;
+                        uint32_t nb = (y0 ? 0u : 4u) + ((uint32_t)(__ffs(y) - 1) >> 3);  // y == 0: ffs - 1 = ~0 -> large
+                        nb = min(nb, min(8u, rem));
                         matched += nb;
                         if (nb < 8) break;
+                        a2 = a4;
+                        b2 = b4;
+                        wa += 2;
+                        wb += 2;
                     }
                 }
-                elist[ne++] = ip | ((ip - cand) << 10) | (matched << 20);
+                *ep++ = ip | ((ip - cand) << 10) | (matched << 20);
                 ip += matched;
                 if (ip >= ip_limit) break;  // snappy.cc:427-429
                 {  // snappy.cc:430-433: insert ip-1; one 4-word read yields load32(ip-1) and bytes ip..ip+7
@@ -344,20 +359,21 @@ __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const u
                     const uint32_t p0 = __funnelshift_r(a, b, sh), p1 = __funnelshift_r(b, c, sh),
                                    p2 = __funnelshift_r(c, e, sh);  // bytes q..q+11
                     tab[hash_bytes_s(p0, shift) * TSTRIDE] = (uint16_t)q;
-                    d = ((uint64_t)__funnelshift_r(p1, p2, 8) << 32) | __funnelshift_r(p0, p1, 8);
-                    have_d = true;
+                    d0 = __funnelshift_r(p0, p1, 8);
+                    d1 = __funnelshift_r(p1, p2, 8);
                 }
-                probing = false;
-            } else if (probing) {
+                s = 31;
+            } else {
                 ip = nxt;
-            } else {  // snappy.cc:441-442
-                ip += 1;
-                probing = true;
-                skip = 32;
+                const uint32_t* w = reinterpret_cast<const uint32_t*>(in_b + (ip & ~3u));
+                const uint32_t sh = (ip & 3) * 8;
+                const uint32_t b = w[1];
+                d0 = __funnelshift_r(w[0], b, sh);
+                d1 = __funnelshift_r(b, w[2], sh);
             }
         }
     }
-    return ne;
+    return (uint32_t)(ep - elist);
 }
 
 constexpr uint32_t kSmallMaxElems = kSmallMax / 4;  // copies cover >= 4 input bytes each and do not overlap
