@@ -289,13 +289,28 @@ __global__ void __launch_bounds__(1024 / LPW) snappy_compress_small_kernel(Small
 // whole warp encodes each list 32 elements at a time (emit_elements_warp: one lane per element,
 // prefix sum over encoded sizes).  Byte-exact with CompressFragment: the elements and their
 // order are the reference's, only the moment they are written changes.
+// The table is addressed as a 32-bit shared-memory address kept opaque to the compiler, which
+// otherwise re-derives it from the input slot's address on every trip (2 extra instructions per access).
+__device__ __forceinline__ uint32_t tab_swap(uint32_t addr, uint32_t v) {  // returns the old entry, stores v
+    uint16_t old;
+    asm volatile("ld.shared.u16 %0, [%1];\n\tst.shared.u16 [%1], %2;" : "=h"(old) : "r"(addr), "h"((uint16_t)v) : "memory");
+    return old;
+}
+__device__ __forceinline__ void tab_store(uint32_t addr, uint32_t v) {
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)v) : "memory");
+}
+
 template <int TSTRIDE>
 __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const uint32_t n, uint16_t* tab,
                                                     uint32_t* __restrict__ elist) {
+    uint32_t tab_s = smem_u32(tab);
+    asm volatile("" : "+r"(tab_s));
+    uint64_t list = reinterpret_cast<uint64_t>(elist);
+    asm volatile("" : "+l"(list));  // one 64-bit base: element k goes to list + 4k with a single wide multiply-add
+    uint32_t ne = 0;
     uint32_t tsize = 256;  // GetHashTable sizing, snappy.cc:253-256
     while (tsize < 16384u && tsize < n) tsize <<= 1;
     const uint32_t shift = 32 - (31 - __clz(tsize));
-    uint32_t* ep = elist;
     if (n >= 15) {  // kInputMarginBytes, snappy.cc:344-347
         const uint32_t ip_limit = n - 15;
         // `s` is the reference's `skip` (snappy.cc:377-385) with one extra state: s == 31 marks the table
@@ -314,8 +329,7 @@ __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const u
             s++;
             if (nxt > ip_limit) break;  // snappy.cc:386-388 (never true right after a copy: ip < ip_limit there)
             const uint32_t h = hash_bytes_s(d0, shift);
-            const uint32_t cand = tab[h * TSTRIDE];
-            tab[h * TSTRIDE] = (uint16_t)ip;
+            const uint32_t cand = tab_swap(tab_s + h * (2 * TSTRIDE), ip);
             const uint32_t* wa = reinterpret_cast<const uint32_t*>(in_b + (cand & ~3u));
             const uint32_t sa = (cand & 3) * 8;
             const uint32_t a0 = wa[0], a1 = wa[1];
@@ -349,7 +363,9 @@ __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const u
                         wb += 2;
                     }
                 }
-                *ep++ = ip | ((ip - cand) << 10) | (matched << 20);
+                asm volatile("st.global.u32 [%0], %1;" ::"l"(list + 4ull * ne), "r"(ip | ((ip - cand) << 10) | (matched << 20))
+                             : "memory");
+                ne++;
                 ip += matched;
                 if (ip >= ip_limit) break;  // snappy.cc:427-429
                 {  // snappy.cc:430-433: insert ip-1; one 4-word read yields load32(ip-1) and bytes ip..ip+7
@@ -358,7 +374,7 @@ __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const u
                     const uint32_t a = w[0], b = w[1], c = w[2], e = w[3], sh = (q & 3) * 8;
                     const uint32_t p0 = __funnelshift_r(a, b, sh), p1 = __funnelshift_r(b, c, sh),
                                    p2 = __funnelshift_r(c, e, sh);  // bytes q..q+11
-                    tab[hash_bytes_s(p0, shift) * TSTRIDE] = (uint16_t)q;
+                    tab_store(tab_s + hash_bytes_s(p0, shift) * (2 * TSTRIDE), q);
                     d0 = __funnelshift_r(p0, p1, 8);
                     d1 = __funnelshift_r(p1, p2, 8);
                 }
@@ -373,14 +389,14 @@ __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const u
             }
         }
     }
-    return (uint32_t)(ep - elist);
+    return ne;
 }
 
 constexpr uint32_t kSmallMaxElems = kSmallMax / 4;  // copies cover >= 4 input bytes each and do not overlap
 
 // Persistent CTAs of 32 bodies (LPW per warp); `elists` = gridDim.x * 32 lists of kSmallMaxElems words.
 template <int LPW>
-__global__ void __launch_bounds__(1024 / LPW) snappy_compress_small2_kernel(SmallCompressParams P, uint32_t* elists) {
+__global__ void __launch_bounds__(1024 / LPW, 2) snappy_compress_small2_kernel(SmallCompressParams P, uint32_t* elists) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     SmallCompressSmem& sm = *reinterpret_cast<SmallCompressSmem*>(smem_raw);
     __shared__ uint64_t stage_bar;
