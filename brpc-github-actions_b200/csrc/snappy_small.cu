@@ -328,6 +328,10 @@ __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const u
             const uint32_t nxt = ip + max(1u, s >> 5);
             s++;
             if (nxt > ip_limit) break;  // snappy.cc:386-388 (never true right after a copy: ip < ip_limit there)
+            // the bytes at nxt are wanted only if this step misses, but asking for them now takes their
+            // shared-memory round trip off the dependent chain
+            const uint32_t* wn = reinterpret_cast<const uint32_t*>(in_b + (nxt & ~3u));
+            const uint32_t n0 = wn[0], n1 = wn[1], n2 = wn[2];
             const uint32_t h = hash_bytes_s(d0, shift);
             const uint32_t cand = tab_swap(tab_s + h * (2 * TSTRIDE), ip);
             const uint32_t* wa = reinterpret_cast<const uint32_t*>(in_b + (cand & ~3u));
@@ -381,11 +385,9 @@ __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const u
                 s = 31;
             } else {
                 ip = nxt;
-                const uint32_t* w = reinterpret_cast<const uint32_t*>(in_b + (ip & ~3u));
                 const uint32_t sh = (ip & 3) * 8;
-                const uint32_t b = w[1];
-                d0 = __funnelshift_r(w[0], b, sh);
-                d1 = __funnelshift_r(b, w[2], sh);
+                d0 = __funnelshift_r(n0, n1, sh);
+                d1 = __funnelshift_r(n1, n2, sh);
             }
         }
     }
@@ -642,6 +644,8 @@ static int configure_one(b2c_ctx* ctx) {
 
 int small_kernels_configure(b2c_ctx* ctx) {
     int rc;
+    B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_compress_small2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(SmallCompressSmem)));
     if ((rc = configure_one<4>(ctx))) return rc;
     if ((rc = configure_one<8>(ctx))) return rc;
     if ((rc = configure_one<16>(ctx))) return rc;
@@ -670,6 +674,7 @@ int launch_compress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const u
         if ((rc = ws_reserve(ctx, lane, lane.ws_tab, (size_t)grid * 32 * kSmallMaxElems * 4))) return rc;
         uint32_t* el = static_cast<uint32_t*>(lane.ws_tab.p);
         switch (ctx->small_lpw_compress) {
+            case 2: snappy_compress_small2_kernel<2><<<grid, 512, smem, lane.stream>>>(P, el); break;
             case 4: snappy_compress_small2_kernel<4><<<grid, 256, smem, lane.stream>>>(P, el); break;
             case 16: snappy_compress_small2_kernel<16><<<grid, 64, smem, lane.stream>>>(P, el); break;
             case 32: snappy_compress_small2_kernel<32><<<grid, 32, smem, lane.stream>>>(P, el); break;
