@@ -76,6 +76,8 @@ SYMBOLS = {
                                                 C.c_int]),
     "b2c_snappy_decompress_verify_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _u32p, _vp, C.c_uint64,
                                                      _u64p, _i32p]),
+    "b2c_snappy_decompress_iov_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, C.POINTER(IoVec), _u32p,
+                                                  _i32p]),
     "b2c_crc32c_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _u32p, _u32p]),
     "b2c_last_transfer_bytes": (None, [_vp, _u64p, _u64p]),
 }
@@ -452,6 +454,16 @@ class Codec:
                                                                 _ptr(mc, _u32p), out.ctypes.data, out.nbytes,
                                                                 _ptr(out_off, _u64p), _ptr(status, _i32p)))
         return out_off, status
+
+    def decompress_iov_batch(self, raw_segs: np.ndarray, seg_begin: np.ndarray, out_segs: np.ndarray,
+                             out_seg_begin: np.ndarray) -> np.ndarray:
+        """RawUncompressToIOVec for a batch: message i is scattered over out_segs[out_seg_begin[i]:out_seg_begin[i+1]]."""
+        n = len(seg_begin) - 1
+        status = np.empty(n, dtype=np.int32)
+        self._check(self.lib.b2c_snappy_decompress_iov_batch(self.ctx, self._segs(raw_segs), _ptr(seg_begin, _u32p), n,
+                                                             self._segs(out_segs), _ptr(out_seg_begin, _u32p),
+                                                             _ptr(status, _i32p)))
+        return status
 
     def prof_enable(self, on: bool = True):
         self._check(self.lib.b2c_prof_enable(self.ctx, 1 if on else 0))

@@ -1297,13 +1297,28 @@ int b2c_snappy_compress_crc_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uin
 }
 
 // decompress (+ optionally verify each result against masked_crc): masked_crc == nullptr is plain b2c_snappy_decompress_batch
+// Output goes either to one flat buffer (out/out_cap/out_off) or, when oiov is given, message i is scattered over
+// oiov[oiov_begin[i] .. oiov_begin[i+1]) the way SnappyIOVecWriter fills its iovecs (snappy.cc:963-1120).
 static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, void* out,
-                                 uint64_t out_cap, uint64_t* out_off, int32_t* status, const uint32_t* masked_crc) {
+                                 uint64_t out_cap, uint64_t* out_off, int32_t* status, const uint32_t* masked_crc,
+                                 const b2c_iovec* oiov = nullptr, const uint32_t* oiov_begin = nullptr) {
+    std::vector<uint64_t> own_off;
+    if (oiov_begin) {  // the flat offsets are internal in this mode
+        own_off.resize((size_t)n + 1);
+        out_off = own_off.data();
+        out_cap = ~0ull;
+        out = nullptr;
+    }
     if (!ctx || !out_off || (n && (!segs || !seg_begin || !status))) return B2C_E_ARG;
     out_off[0] = 0;
     if (n == 0) return B2C_OK;
     B2C_CUDA(ctx, cudaSetDevice(ctx->device));
-    Trace tr(ctx->trace, masked_crc ? "decompress_verify_batch" : "decompress_batch");
+    Trace tr(ctx->trace, oiov_begin ? "decompress_iov_batch" : masked_crc ? "decompress_verify_batch" : "decompress_batch");
+    // scatter mode: per in-flight slab, each message's offset in the slab's staged output and its slot length
+    // (0 with too_small set when the iovecs cannot hold what the preamble claims: SnappyIOVecWriter would overrun)
+    std::vector<uint64_t> fin_off[kPipeLanes];
+    std::vector<uint32_t> fin_len[kPipeLanes];
+    std::vector<uint8_t> fin_small[kPipeLanes];
     BatchPlan bp(ctx);
     int rc;
     TIMED(tr.plan, rc = plan_batch(ctx, segs, seg_begin, n, bp));
@@ -1312,7 +1327,7 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
     const size_t K = bp.slabs.size();
     std::vector<uint64_t> slab_out(K, 0);
     std::vector<uint64_t>& o_off = ctx->tmp_off;
-    const bool direct = is_pinned_host(out);  // caller's buffer is page-locked: DMA straight into it
+    const bool direct = !oiov_begin && is_pinned_host(out);  // caller's buffer is page-locked: DMA straight into it
     auto finish = [&](size_t k) -> int {
         Lane& lane = ctx->pipe[k % kPipeLanes];
         const Slab& s = bp.slabs[k];
@@ -1321,8 +1336,34 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
         auto tc = Clock::now();
         const uint8_t* h = static_cast<const uint8_t*>(lane.h_out.p);
         const uint64_t base = out_off[s.m0];
-        if (!direct) parallel_copy(ctx, static_cast<uint8_t*>(out) + base, h, slab_out[k]);
         const int32_t* st = reinterpret_cast<const int32_t*>(h + align_up(slab_out[k], 256));
+        if (oiov_begin) {  // scatter every decoded message over its iovecs
+            const uint64_t* foff = fin_off[k % kPipeLanes].data();
+            const uint32_t* flen = fin_len[k % kPipeLanes].data();
+            const uint8_t* fsmall = fin_small[k % kPipeLanes].data();
+            pool(ctx).run(threads_for(slab_out[k]), [&](unsigned t, unsigned T) {
+                const uint32_t lo = (uint32_t)((uint64_t)cnt * t / T), hi = (uint32_t)((uint64_t)cnt * (t + 1) / T);
+                for (uint32_t i = lo; i < hi; i++) {
+                    if (fsmall[i]) {
+                        status[s.m0 + i] = B2C_TOO_SMALL;
+                        continue;
+                    }
+                    status[s.m0 + i] = st[i] == B2C_TOO_SMALL ? B2C_CORRUPT : st[i];
+                    if (st[i] != B2C_OK) continue;
+                    const uint8_t* src = h + foff[i];
+                    uint64_t left = flen[i];
+                    for (uint32_t q = oiov_begin[s.m0 + i]; left && q < oiov_begin[s.m0 + i + 1]; q++) {
+                        const uint64_t c = std::min<uint64_t>(left, oiov[q].iov_len);
+                        memcpy(const_cast<void*>(oiov[q].iov_base), src, c);
+                        src += c;
+                        left -= c;
+                    }
+                }
+            });
+            tr.copy_out += secs(tc, Clock::now());
+            return B2C_OK;
+        }
+        if (!direct) parallel_copy(ctx, static_cast<uint8_t*>(out) + base, h, slab_out[k]);
         for (uint32_t i = 0; i < cnt; i++)  // TOO_SMALL can only mean "implausible preamble" here
             status[s.m0 + i] = st[i] == B2C_TOO_SMALL ? B2C_CORRUPT : st[i];
         tr.copy_out += secs(tc, Clock::now());
@@ -1362,13 +1403,27 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
         const Slab& s = bp.slabs[k];
         const uint32_t cnt = s.m1 - s.m0;
         LayoutPlan& lin = lin_ring[k & 1];
-        const std::vector<uint32_t>& o_cap = *cap_ring[k & 1];
+        std::vector<uint32_t>& o_cap = *cap_ring[k & 1];
         if (o_off.size() < cnt) o_off.resize(cnt);
         auto tl = Clock::now();
         PlanStats st_in, st_out;
         if (!ctx->input_pinned) {
             stats[k & 1].merged(st_in, st_out);
             lin.plan_with(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, st_in);
+        }
+        bool clamped = false;
+        if (oiov_begin) {  // a message whose iovecs cannot hold what its preamble claims is not decoded at all
+            std::vector<uint8_t>& small = fin_small[k % kPipeLanes];
+            small.assign(cnt, 0);
+            for (uint32_t i = 0; i < cnt; i++) {
+                uint64_t room = 0;
+                for (uint32_t q = oiov_begin[s.m0 + i]; q < oiov_begin[s.m0 + i + 1]; q++) room += oiov[q].iov_len;
+                if (o_cap[i] > room) {
+                    o_cap[i] = 0;
+                    small[i] = 1;
+                    clamped = true;
+                }
+            }
         }
         uint64_t pos = 0;
         for (uint32_t i = 0; i < cnt; i++) {
@@ -1380,8 +1435,12 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
         if (out_base + pos > out_cap) return set_err(ctx, B2C_E_CAPACITY, "decompress_batch: out_cap too small", cudaSuccess);
         out_base += pos;
         out_off[s.m1] = out_base;
+        if (oiov_begin) {
+            fin_off[k % kPipeLanes].assign(o_off.begin(), o_off.begin() + cnt);
+            fin_len[k % kPipeLanes].assign(o_cap.begin(), o_cap.begin() + cnt);
+        }
         LayoutPlan lout;
-        if (ctx->input_pinned) {
+        if (ctx->input_pinned || clamped) {
             lout.plan(cnt, o_off.data(), o_cap.data(), nullptr);
         } else {  // the workers summed everything but the end of the arena, which is the running total
             st_out.arena_end = pos;
@@ -1437,6 +1496,13 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
 int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, void* out,
                                 uint64_t out_cap, uint64_t* out_off, int32_t* status) {
     return decompress_batch_impl(ctx, segs, seg_begin, n, out, out_cap, out_off, status, nullptr);
+}
+
+int b2c_snappy_decompress_iov_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n,
+                                    const b2c_iovec* out_iov, const uint32_t* out_iov_begin, int32_t* status) {
+    if (n && (!out_iov_begin || (!out_iov && out_iov_begin[n] != out_iov_begin[0]))) return B2C_E_ARG;
+    if (n == 0) return ctx ? B2C_OK : B2C_E_ARG;
+    return decompress_batch_impl(ctx, segs, seg_begin, n, nullptr, 0, nullptr, status, nullptr, out_iov, out_iov_begin);
 }
 
 int b2c_snappy_decompress_verify_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n,

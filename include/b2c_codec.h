@@ -246,6 +246,16 @@ int b2c_snappy_decompress_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint3
                                 uint32_t n, void* out, uint64_t out_cap, uint64_t* out_off,
                                 int32_t* status);
 
+/* snappy::RawUncompressToIOVec (snappy.cc:1122-1132, SnappyIOVecWriter :963-1120) for a batch:
+ * decoded message i is laid over out_iov[out_iov_begin[i] .. out_iov_begin[i+1]) in order, each
+ * iovec filled before the next (the blocks an IOBuf would hand out).  status[i] = B2C_OK iff the
+ * reference returns true; B2C_TOO_SMALL when the iovecs cannot hold the length the preamble
+ * claims (the reference's writer overruns and returns false; nothing is written here);
+ * B2C_CORRUPT otherwise.  Unused tail space of the iovecs is left untouched. */
+int b2c_snappy_decompress_iov_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin,
+                                    uint32_t n, const b2c_iovec* out_iov, const uint32_t* out_iov_begin,
+                                    int32_t* status);
+
 /* The sender's two passes over a body in one: b2c_snappy_compress_batch plus
  * crc[i] = butil::crc32c::Value(body i) (crc32c.h:31-33), or Mask() of it when masked != 0
  * (crc32c.h:44-48) -- the pair a checksummed, snappy-compressed frame carries

@@ -344,6 +344,49 @@ def test_e2e_fused_sender_and_receiver_calls(codec, cpu):
         assert_bytes_equal(back[int(b_off[i]):int(b_off[i + 1])].tobytes(), arena[a:b].tobytes(), f"fused back {i}")
 
 
+def test_e2e_decompress_into_iovecs(codec, cpu):
+    """RawUncompressToIOVec for a batch: output scattered over 8160-byte blocks (and odd little ones), too little
+    room reported as the reference's writer would fail, corrupt streams rejected, spare room left untouched."""
+    import brpc_b200
+    rng = np.random.default_rng(77)
+    lens = np.concatenate([np.full(3000, 1024), rng.integers(0, 40000, 300), [0, 1, 65536, 200000]]).astype(np.uint32)
+    arena, off, ln = O.corpus_batch("words", lens, first_index=11)
+    cap = int(sum(32 + int(l) + int(l) // 6 + 5 for l in ln))
+    comp = np.empty(cap, dtype=np.uint8)
+    isegs, isb = brpc_b200.make_iovecs(arena, off, ln, seg_bytes=8160)
+    c_off = codec.compress_batch(isegs, isb, comp)
+    clen = np.diff(c_off).astype(np.uint32)
+    comp[int(c_off[5]) + 3] ^= 0x55  # literal byte of message 5: still decodes
+    comp[int(c_off[9])] = 0xFF       # preamble of message 9 now claims far more than the stream can hold
+    csegs, csb = brpc_b200.make_iovecs(comp, c_off[:-1], clen, seg_bytes=1000)
+    # output: every message gets its own region of a big buffer, cut into blocks; message 7 gets one byte too little,
+    # message 8 gets 100 spare bytes
+    room = ln.astype(np.int64).copy()
+    room[7] -= 1
+    room[8] += 100
+    room[9] += 200  # enough for what message 9's damaged preamble claims (1151): it must fail in the decoder, not on room
+    o_off = np.concatenate([[0], np.cumsum(room + 16)]).astype(np.uint64)
+    sink = np.full(int(o_off[-1]), 0xEE, dtype=np.uint8)
+    osegs, osb = brpc_b200.make_iovecs(sink, o_off[:-1], room.astype(np.uint32), seg_bytes=777)
+    status = codec.decompress_iov_batch(csegs, csb, osegs, osb)
+    for i in range(len(ln)):
+        a = int(o_off[i])
+        got = sink[a:a + int(room[i])]
+        if i == 7:
+            assert status[i] == 2 and (got == 0xEE).all()  # B2C_TOO_SMALL, nothing written
+        elif i == 9:
+            assert status[i] == 1
+        else:
+            assert status[i] == 0, i
+            want = arena[int(off[i]):int(off[i]) + int(ln[i])]
+            if i == 5:
+                assert got[:len(want)].tobytes() != want.tobytes()
+            else:
+                assert_bytes_equal(got[:len(want)].tobytes(), want.tobytes(), f"iov msg {i}")
+            assert (got[len(want):] == 0xEE).all()
+        assert (sink[a + int(room[i]):int(o_off[i + 1])] == 0xEE).all()  # the gap between regions
+
+
 def test_e2e_decompress_rejects_like_reference(codec, golden):
     import brpc_b200
     es = [e for e in golden["malformed"] if e["stream"]]
