@@ -315,6 +315,25 @@ def run_ours(args, rank, local_rank, world):
             dt = brpc_b200.sharding.max_over_ranks(dt, device="cuda")
         return dt, bytes_h2d, bytes_d2h
 
+    # what bounds the end-to-end path: this box's pinned-memory copy rate, one direction at a time (SURVEY 8(d):
+    # measured in the same run, not assumed; tools/pcie_bw.py also times both directions at once)
+    def pcie_probe():
+        nb = min(256 << 20, len(h_back))
+        out = {}
+        for name, fn, args in (("h2d_gbs", codec.lib.b2c_memcpy_h2d, (d_back.ptr, h_back.ctypes.data, nb)),
+                               ("d2h_gbs", codec.lib.b2c_memcpy_d2h, (h_back.ctypes.data, d_back.ptr, nb))):
+            fn(codec.ctx, *args)
+            codec.sync()
+            a, b = codec.event(), codec.event()
+            a.record()
+            for _ in range(4):
+                fn(codec.ctx, *args)
+            b.record()
+            codec.sync()
+            out[name] = 4 * nb / (b.elapsed_ms_since(a) * 1e-3) / 1e9
+        return out
+
+    pcie = pcie_probe() if rank == 0 else None
     # (a) the headline: input blocks in ordinary pageable memory (what IOBuf blocks are today); host threads gather
     #     them into pinned staging and the copy engines move the slabs
     e2e_s, bytes_h2d, bytes_d2h = time_e2e()
@@ -367,6 +386,7 @@ def run_ours(args, rank, local_rank, world):
                             "iovecs (1-2 blocks per body) gathered into pinned staging by host threads; outputs = "
                             "page-locked host buffers",
                     "separate_calls_value": payload * world * e2e_steps / e2e_separate_s / 1e9,
+                    "pcie_probe": pcie,
                     "pinned_inputs_device_gather_value": payload * world * e2e_steps / e2e_zero_copy_s / 1e9},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "snappy_compress_small_kernel" if int(ln.max()) <= 1024 else "snappy_compress_*_kernel (all size classes of the batch)", "bound": "hbm", "achieved": achieved,
@@ -378,6 +398,7 @@ def run_ours(args, rank, local_rank, world):
                          "note": "byte-exact greedy LZ77 is a serial dependency chain per fragment: latency/issue bound, "
                                  "not HBM bound (see DESIGN.md)"},
             "ops": per_op, "compression_ratio": comp_bytes / payload,
+            "messages_per_s": n_msgs * world * args.steps / (ms * 1e-3),
             "cpu_baseline": {"value": cpu_gbs, "unit": "GB/s", "cores": cores, "kind": cpu.kind,
                              "sample": f"full batch ({n_msgs} bodies, {payload} B) x {reps} passes of crc32c + RawCompress + "
                                        f"RawUncompress, static split over {cores} threads"},

@@ -34,6 +34,19 @@ size_t total_bytes(const BlockList& b) {
     for (const b2c_iovec& v : b) n += v.iov_len;
     return n;
 }
+uint64_t claimed_bytes(const std::vector<BlockList>& in) {  // sum of the (lenient) preambles
+    uint64_t claimed = 0;
+    for (const BlockList& b : in) {
+        uint8_t head[5];
+        size_t got = 0;
+        for (const b2c_iovec& v : b)
+            for (size_t j = 0; j < v.iov_len && got < 5; j++) head[got++] = static_cast<const uint8_t*>(v.iov_base)[j];
+        uint32_t ulen = 0;
+        if (b2c_snappy_read_preamble(head, got, &ulen)) claimed += ulen;
+    }
+    return claimed;
+}
+
 }  // namespace
 
 Context::Context(int device) : ctx_(nullptr) {
@@ -79,16 +92,7 @@ void SnappyDecompressBatch(const std::vector<BlockList>& in, std::vector<std::st
     uint64_t cap = 64;
     for (const BlockList& b : in) cap += total_bytes(b) * 64 / 3 + 64;
     // sum of the claimed lengths is usually far smaller: read the preambles first
-    uint64_t claimed = 0;
-    for (const BlockList& b : in) {
-        uint8_t head[5];
-        size_t got = 0;
-        for (const b2c_iovec& v : b)
-            for (size_t j = 0; j < v.iov_len && got < 5; j++) head[got++] = static_cast<const uint8_t*>(v.iov_base)[j];
-        uint32_t ulen = 0;
-        if (b2c_snappy_read_preamble(head, got, &ulen)) claimed += ulen;
-    }
-    cap = std::min<uint64_t>(cap, claimed + 64);
+    cap = std::min<uint64_t>(cap, claimed_bytes(in) + 64);
     std::vector<char> buf(cap);
     std::vector<uint64_t> off(n + 1);
     std::vector<int32_t> st(n);
@@ -108,6 +112,60 @@ void Crc32cBatch(const std::vector<BlockList>& in, const uint32_t* init, std::ve
     Flat f(in);
     int rc = b2c_crc32c_batch(ctx, f.segs.data(), f.begin.data(), n, init, crc->data());
     if (rc != B2C_OK) fail(ctx, "b2c_crc32c_batch", rc);
+}
+
+void SnappyCompressCrcBatch(const std::vector<BlockList>& in, std::vector<std::string>* out,
+                            std::vector<uint32_t>* masked_crc) {
+    b2c_ctx* ctx = Context::local().get();
+    const uint32_t n = (uint32_t)in.size();
+    out->assign(n, std::string());
+    masked_crc->assign(n, 0);
+    if (!n) return;
+    Flat f(in);
+    uint64_t cap = 0;
+    for (const BlockList& b : in) cap += b2c_snappy_max_compressed_length(total_bytes(b)) + 5;
+    std::vector<char> buf(cap);
+    std::vector<uint64_t> off(n + 1);
+    int rc = b2c_snappy_compress_crc_batch(ctx, f.segs.data(), f.begin.data(), n, buf.data(), cap, off.data(),
+                                           masked_crc->data(), /*masked=*/1);
+    if (rc != B2C_OK) fail(ctx, "b2c_snappy_compress_crc_batch", rc);
+    for (uint32_t i = 0; i < n; i++) (*out)[i].assign(buf.data() + off[i], off[i + 1] - off[i]);
+}
+
+void SnappyDecompressVerifyBatch(const std::vector<BlockList>& in, const std::vector<uint32_t>& masked_crc,
+                                 std::vector<std::string>* out, std::vector<Verdict>* verdict) {
+    b2c_ctx* ctx = Context::local().get();
+    const uint32_t n = (uint32_t)in.size();
+    out->assign(n, std::string());
+    verdict->assign(n, Verdict::kCorrupt);
+    if (!n) return;
+    if (masked_crc.size() != n) fail(ctx, "SnappyDecompressVerifyBatch: one checksum per body", B2C_E_ARG);
+    Flat f(in);
+    const uint64_t cap = claimed_bytes(in) + 64;
+    std::vector<char> buf(cap);
+    std::vector<uint64_t> off(n + 1);
+    std::vector<int32_t> st(n);
+    int rc = b2c_snappy_decompress_verify_batch(ctx, f.segs.data(), f.begin.data(), n, masked_crc.data(), buf.data(), cap,
+                                                off.data(), st.data());
+    if (rc != B2C_OK) fail(ctx, "b2c_snappy_decompress_verify_batch", rc);
+    for (uint32_t i = 0; i < n; i++) {
+        (*verdict)[i] = st[i] == B2C_OK ? Verdict::kOk : st[i] == B2C_CRC_MISMATCH ? Verdict::kCrcMismatch : Verdict::kCorrupt;
+        if (st[i] == B2C_OK) (*out)[i].assign(buf.data() + off[i], off[i + 1] - off[i]);
+    }
+}
+
+void SnappyDecompressToBlocksBatch(const std::vector<BlockList>& in, const std::vector<BlockList>& out,
+                                   std::vector<bool>* ok) {
+    b2c_ctx* ctx = Context::local().get();
+    const uint32_t n = (uint32_t)in.size();
+    ok->assign(n, false);
+    if (!n) return;
+    if (out.size() != n) fail(ctx, "SnappyDecompressToBlocksBatch: one block list per body", B2C_E_ARG);
+    Flat f(in), g(out);
+    std::vector<int32_t> st(n);
+    int rc = b2c_snappy_decompress_iov_batch(ctx, f.segs.data(), f.begin.data(), n, g.segs.data(), g.begin.data(), st.data());
+    if (rc != B2C_OK) fail(ctx, "b2c_snappy_decompress_iov_batch", rc);
+    for (uint32_t i = 0; i < n; i++) (*ok)[i] = st[i] == B2C_OK;
 }
 
 bool SnappyCompress(const BlockList& in, std::string* out) {
@@ -176,6 +234,16 @@ bool Uncompress(const char* compressed, size_t n, std::string* uncompressed) {
     if (ulen > (uint64_t)n * 64 / 3 + 64) return false;              // cannot be a valid stream (see b2c_api.cu)
     uncompressed->resize(ulen);
     return RawUncompress(compressed, n, ulen ? &(*uncompressed)[0] : nullptr);
+}
+
+bool RawUncompressToIOVec(const char* compressed, size_t n, const struct ::b2c_iovec* iov, size_t iov_cnt) {
+    b2c_ctx* ctx = Context::local().get();
+    b2c_iovec seg = {compressed, n};
+    const uint32_t begin[2] = {0, 1}, obegin[2] = {0, (uint32_t)iov_cnt};
+    int32_t st = 0;
+    int rc = b2c_snappy_decompress_iov_batch(ctx, &seg, begin, 1, iov, obegin, &st);
+    if (rc != B2C_OK) fail(ctx, "b2c_snappy_decompress_iov_batch", rc);
+    return st == B2C_OK;
 }
 
 bool IsValidCompressedBuffer(const char* compressed, size_t n) {

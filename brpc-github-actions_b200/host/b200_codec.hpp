@@ -45,6 +45,8 @@ size_t Compress(const char* input, size_t n, std::string* output);              
 bool RawUncompress(const char* compressed, size_t n, char* uncompressed);            // snappy.h:161
 bool Uncompress(const char* compressed, size_t n, std::string* uncompressed);        // snappy.h:79
 bool IsValidCompressedBuffer(const char* compressed, size_t n);                      // snappy.h:190
+// snappy.h:168-171: the decoded bytes fill iov[0], iov[1], ... in order; false when they do not fit
+bool RawUncompressToIOVec(const char* compressed, size_t n, const struct ::b2c_iovec* iov, size_t iov_cnt);
 }  // namespace snappy
 
 namespace crc32c {
@@ -66,6 +68,16 @@ bool SnappyDecompress(const BlockList& in, std::string* out);
 void SnappyCompressBatch(const std::vector<BlockList>& in, std::vector<std::string>* out);
 void SnappyDecompressBatch(const std::vector<BlockList>& in, std::vector<std::string>* out, std::vector<bool>* ok);
 void Crc32cBatch(const std::vector<BlockList>& in, const uint32_t* init /*nullable*/, std::vector<uint32_t>* crc);
+// One pass per side of a checksummed, compressed frame (b2c_snappy_compress_crc_batch /
+// b2c_snappy_decompress_verify_batch): masked_crc[i] = crc32c::Mask(crc32c::Value(body i)).
+void SnappyCompressCrcBatch(const std::vector<BlockList>& in, std::vector<std::string>* out,
+                            std::vector<uint32_t>* masked_crc);
+enum class Verdict { kOk, kCorrupt, kCrcMismatch };
+void SnappyDecompressVerifyBatch(const std::vector<BlockList>& in, const std::vector<uint32_t>& masked_crc,
+                                 std::vector<std::string>* out, std::vector<Verdict>* verdict);
+// RawUncompressToIOVec for n bodies: body i is laid over out[i]'s blocks.
+void SnappyDecompressToBlocksBatch(const std::vector<BlockList>& in, const std::vector<BlockList>& out,
+                                   std::vector<bool>* ok);
 }  // namespace policy
 
 }  // namespace b200

@@ -298,6 +298,65 @@ static void aggregator_many_threads() {
            (unsigned long long)st.batches, (unsigned long long)st.largest_batch);
 }
 
+// ---- one-pass sender / receiver calls and RawUncompressToIOVec ----
+static void fused_and_iovec_calls() {
+    std::vector<std::string> bodies;
+    for (int i = 0; i < 200; i++) {
+        std::string s((size_t)(i * 53 % 9000), '\0');
+        b2o_corpus_fill(B2O_WORDS, 1000 + i, reinterpret_cast<uint8_t*>(&s[0]), s.size());
+        bodies.push_back(s);
+    }
+    std::vector<BlockList> in;
+    for (const std::string& s : bodies) in.push_back(blocks_of(s, 8160));
+    std::vector<std::string> z, back;
+    std::vector<uint32_t> mcrc;
+    b200::policy::SnappyCompressCrcBatch(in, &z, &mcrc);
+    for (size_t i = 0; i < bodies.size(); i++) {
+        CHECK(z[i] == oracle_compress(bodies[i]));
+        CHECK(mcrc[i] == cpu_masked_crc(bodies[i]));
+    }
+    std::vector<BlockList> zin;
+    for (const std::string& s : z) zin.push_back(blocks_of(s, 512));
+    mcrc[3] ^= 0x10;
+    std::vector<b200::policy::Verdict> verdict;
+    b200::policy::SnappyDecompressVerifyBatch(zin, mcrc, &back, &verdict);
+    for (size_t i = 0; i < bodies.size(); i++) {
+        if (i == 3) {
+            CHECK(verdict[i] == b200::policy::Verdict::kCrcMismatch);
+        } else {
+            CHECK(verdict[i] == b200::policy::Verdict::kOk && back[i] == bodies[i]);
+        }
+    }
+    // RawUncompressToIOVec: the reference's unit test shape -- output over several small iovecs
+    {
+        const std::string& text = bodies[150];
+        const std::string& stream = z[150];
+        std::string sink(text.size() + 40, '#');
+        std::vector<b2c_iovec> iov;
+        size_t at = 0, piece = 1;
+        while (at < sink.size()) {  // 1, 2, 3, ... byte iovecs, then the rest
+            const size_t c = std::min(piece++, sink.size() - at);
+            iov.push_back({&sink[at], c});
+            at += c;
+        }
+        CHECK(b200::snappy::RawUncompressToIOVec(stream.data(), stream.size(), iov.data(), iov.size()));
+        CHECK(sink.compare(0, text.size(), text) == 0);
+        CHECK(sink.substr(text.size()) == std::string(40, '#'));
+        // one byte too little room: the reference's writer fails
+        std::string tight(text.size() - 1, '#');
+        b2c_iovec one = {&tight[0], tight.size()};
+        CHECK(!b200::snappy::RawUncompressToIOVec(stream.data(), stream.size(), &one, 1));
+    }
+    // batch form over 8160-byte output blocks
+    std::vector<std::string> sinks;
+    std::vector<BlockList> outs;
+    for (const std::string& s : bodies) sinks.push_back(std::string(s.size(), '#'));
+    for (std::string& s : sinks) outs.push_back(blocks_of(s, 8160));
+    std::vector<bool> ok;
+    b200::policy::SnappyDecompressToBlocksBatch(zin, outs, &ok);
+    for (size_t i = 0; i < bodies.size(); i++) CHECK(ok[i] && sinks[i] == bodies[i]);
+}
+
 int main() {
     crc_standard_results();
     crc_values_extend_mask();
@@ -307,6 +366,7 @@ int main() {
     mass_snappy_iobuf();
     batch_calls();
     framing_format();
+    fused_and_iovec_calls();
     aggregator_many_threads();
     if (g_fail) {
         fprintf(stderr, "%d check(s) failed\n", g_fail);
