@@ -546,6 +546,11 @@ __global__ void __launch_bounds__(1024 / LPW) snappy_decompress_small_kernel(Sma
         if (st == B2C_OK && expected > cap) st = B2C_TOO_SMALL;
         uint32_t op = 0;
         if (st == B2C_OK) {
+            // One code path for every tag: the three frequent kinds (short literal, copy with 1-byte offset, copy
+            // with 2-byte offset) decode with selects, and a literal is then simply a copy whose source is the
+            // stream instead of the slot.  The lanes of a warp decode different streams; separate branches per kind
+            // made them take turns (a literal path run for 1.9 of 8 lanes on `words`).
+            const uint8_t* const obg = ob;  // generic pointer to the slot, for the common source pointer
             for (;;) {
                 if (ip == n) {  // clean eof: snappy.cc:867
                     if (op != expected) st = B2C_CORRUPT;
@@ -554,52 +559,49 @@ __global__ void __launch_bounds__(1024 / LPW) snappy_decompress_small_kernel(Sma
                 const uint32_t x = ld32u(in + ip);  // tag byte + up to 3 trailer bytes
                 const uint32_t c = x & 0xff;
                 const uint32_t kind = c & 3;
-                if (kind == 1) {  // copy, 1-byte offset (by far the most frequent tag of text-like bodies)
-                    if (n - ip < 2) { st = B2C_CORRUPT; break; }
-                    const uint32_t len = ((c >> 2) & 7) + 4;
-                    const uint32_t offset = ((c >> 5) << 8) | ((x >> 8) & 0xff);
-                    ip += 2;
-                    if (offset == 0 || offset > op || expected - op < len) { st = B2C_CORRUPT; break; }
-                    slot_copy(ob + op, ob + op - offset, len, offset);
-                    op += len;
-                } else if (kind == 0) {
-                    uint32_t len = (c >> 2) + 1;
-                    uint32_t extra = 0;
-                    if (len >= 61) {
-                        extra = len - 60;
+                const bool is_lit = kind == 0;
+                uint32_t len = (c >> 2) + 1;                            // literal < 61, copy-2, copy-4
+                uint32_t used = kind + 1;                               // 1, 2, 3 (copy-4: fixed below)
+                uint32_t offset = (x >> 8) & 0xffffu;                   // copy-2
+                if (kind == 1) {
+                    len = ((c >> 2) & 7) + 4;
+                    offset = ((c >> 5) << 8) | ((x >> 8) & 0xff);
+                }
+                if (kind == 3 || (kind == 0 && c >= 0xf0u)) {  // rare: literal with a length trailer, 4-byte offset
+                    if (kind == 0) {
+                        const uint32_t extra = len - 60;
                         if (n - ip < extra + 1) { st = B2C_CORRUPT; break; }
                         uint32_t v = x >> 8;
                         if (extra == 4) v |= (uint32_t)in[ip + 4] << 24;
                         else v &= (1u << (8 * extra)) - 1u;
                         len = v + 1u;  // may wrap to 0 like the reference
+                        used = 1 + extra;
+                    } else {
+                        if (n - ip < 5) { st = B2C_CORRUPT; break; }
+                        offset = (x >> 8) | ((uint32_t)in[ip + 4] << 24);
+                        used = 5;
                     }
-                    ip += 1 + extra;
-                    if (n - ip < len || expected - op < len) { st = B2C_CORRUPT; break; }
-                    const uint8_t* __restrict__ s = in + ip;
-                    uint8_t* d = ob + op;
-                    uint32_t i = 0;
-                    for (; i + 4 <= len; i += 4) {  // 4 independent loads, then 4 stores
-                        const uint8_t b0 = s[i], b1 = s[i + 1], b2 = s[i + 2], b3 = s[i + 3];
+                }
+                if (n - ip < used) { st = B2C_CORRUPT; break; }
+                ip += used;
+                // literal: the bytes must be there; copy: offset in 1..op (offset - 1 wraps for 0)
+                const bool bad = is_lit ? n - ip < len : offset - 1 >= op;
+                if (bad || expected - op < len) { st = B2C_CORRUPT; break; }
+                const uint8_t* sp = is_lit ? in + ip : obg + op - offset;  // may overlap d: no restrict
+                uint8_t* d = ob + op;
+                uint32_t i = 0;
+                if (is_lit || offset >= 4) {  // the 4 source bytes of a round precede its first destination byte
+                    for (; i + 4 <= len; i += 4) {
+                        const uint8_t b0 = sp[i], b1 = sp[i + 1], b2 = sp[i + 2], b3 = sp[i + 3];
                         d[i] = b0;
                         d[i + 1] = b1;
                         d[i + 2] = b2;
                         d[i + 3] = b3;
                     }
-                    for (; i < len; i++) d[i] = s[i];
-                    op += len;
-                    ip += len;
-                } else {  // copy, 2- or 4-byte offset
-                    const uint32_t extra = kind == 2 ? 2u : 4u;
-                    if (n - ip < extra + 1) { st = B2C_CORRUPT; break; }
-                    const uint32_t len = (c >> 2) + 1;
-                    uint32_t offset = x >> 8;
-                    if (kind == 2) offset &= 0xffffu;
-                    else offset |= (uint32_t)in[ip + 4] << 24;
-                    ip += 1 + extra;
-                    if (offset == 0 || offset > op || expected - op < len) { st = B2C_CORRUPT; break; }
-                    slot_copy(ob + op, ob + op - offset, len, offset);
-                    op += len;
                 }
+                for (; i < len; i++) d[i] = sp[i];  // IncrementalCopy, snappy.cc:98-103
+                op += len;
+                if (is_lit) ip += len;
             }
         }
         P.status[m] = st;
