@@ -513,7 +513,7 @@ __device__ __forceinline__ void slot_copy(uint8_t* d, const uint8_t* s, uint32_t
 constexpr uint32_t kSmallSlotBytes = kSmallMax + 16;
 
 template <int LPW>
-__global__ void __launch_bounds__(1024 / LPW) snappy_decompress_small_kernel(SmallDecompressParams P) {
+__global__ void __launch_bounds__(1024 / LPW, 6) snappy_decompress_small_kernel(SmallDecompressParams P) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = threadIdx.x >> 5;
@@ -525,6 +525,7 @@ __global__ void __launch_bounds__(1024 / LPW) snappy_decompress_small_kernel(Sma
     if (live) {
         m = P.list ? P.list[idx] : idx;
         const uint8_t* in = P.in + P.in_off[m];
+        asm volatile("" : "+l"(in));  // one 64-bit register pair, not base + offset re-added on every tag
         const uint32_t n = P.in_len[m];
         const uint32_t cap = P.out_cap[m];
         uint8_t* ob = smem_raw + (size_t)slot * kSmallSlotBytes;
@@ -550,7 +551,8 @@ __global__ void __launch_bounds__(1024 / LPW) snappy_decompress_small_kernel(Sma
             // with 2-byte offset) decode with selects, and a literal is then simply a copy whose source is the
             // stream instead of the slot.  The lanes of a warp decode different streams; separate branches per kind
             // made them take turns (a literal path run for 1.9 of 8 lanes on `words`).
-            const uint8_t* const obg = ob;  // generic pointer to the slot, for the common source pointer
+            const uint8_t* obg = ob;  // generic pointer to the slot, for the common source pointer
+            asm volatile("" : "+l"(obg));  // converted once, kept
             for (;;) {
                 if (ip == n) {  // clean eof: snappy.cc:867
                     if (op != expected) st = B2C_CORRUPT;
