@@ -324,6 +324,7 @@ __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const u
             d0 = __funnelshift_r(w[0], w[1], 8);
             d1 = __funnelshift_r(w[1], w[2], 8);
         }
+        uint32_t h = hash_bytes_s(d0, shift);  // of the bytes at ip, carried like d0 / d1
         for (;;) {
             const uint32_t nxt = ip + max(1u, s >> 5);
             s++;
@@ -332,7 +333,8 @@ __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const u
             // shared-memory round trip off the dependent chain
             const uint32_t* wn = reinterpret_cast<const uint32_t*>(in_b + (nxt & ~3u));
             const uint32_t n0 = wn[0], n1 = wn[1], n2 = wn[2];
-            const uint32_t h = hash_bytes_s(d0, shift);
+            const uint32_t nd0 = __funnelshift_r(n0, n1, (nxt & 3) * 8);
+            const uint32_t nh = hash_bytes_s(nd0, shift);  // likewise: the next step's hash, ready if this one misses
             const uint32_t cand = tab_swap(tab_s + h * (2 * TSTRIDE), ip);
             const uint32_t* wa = reinterpret_cast<const uint32_t*>(in_b + (cand & ~3u));
             const uint32_t sa = (cand & 3) * 8;
@@ -381,13 +383,14 @@ __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const u
                     tab_store(tab_s + hash_bytes_s(p0, shift) * (2 * TSTRIDE), q);
                     d0 = __funnelshift_r(p0, p1, 8);
                     d1 = __funnelshift_r(p1, p2, 8);
+                    h = hash_bytes_s(d0, shift);
                 }
                 s = 31;
             } else {
                 ip = nxt;
-                const uint32_t sh = (ip & 3) * 8;
-                d0 = __funnelshift_r(n0, n1, sh);
-                d1 = __funnelshift_r(n1, n2, sh);
+                d0 = nd0;
+                d1 = __funnelshift_r(n1, n2, (ip & 3) * 8);
+                h = nh;
             }
         }
     }
