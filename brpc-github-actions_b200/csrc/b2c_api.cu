@@ -826,13 +826,22 @@ bool is_pinned_host(const void* p) {
     return a.type == cudaMemoryTypeHost;
 }
 
-// Message lengths (parallel), staging offsets and slab cuts (serial prefix).
+// Message lengths, staging offsets and slab cuts.  Staged mode: a message of >= 256 bytes takes a multiple of 64
+// bytes of staging (so runs of them start on 64-byte lines and the gather writes whole lines only), a shorter one
+// a multiple of 16; sizes are therefore independent of position, the offsets are a prefix sum done by the pool,
+// and a slab is the longest run of messages that fits the target (binary search on the prefix sums).
 int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, BatchPlan& p) {
-    if (p.off.size() < n) p.off.resize(n);
+    if (p.off.size() < (size_t)n + 1) p.off.resize((size_t)n + 1);
     if (p.len.size() < n) p.len.resize(n);
     std::atomic<bool> too_long(false);
+    const bool zc = ctx->input_pinned;
+    auto staged_size = [](uint32_t l) -> uint64_t { return l >= 256 ? align_up(l, 64) : align_up(l, 16); };
+    uint64_t part[64] = {0};
+    unsigned used = 1;
     pool(ctx).run(threads_for((uint64_t)n * 64), [&](unsigned t, unsigned T) {
+        if (t == 0) used = T;
         uint32_t lo = (uint32_t)((uint64_t)n * t / T), hi = (uint32_t)((uint64_t)n * (t + 1) / T);
+        uint64_t sum = 0;
         for (uint32_t i = lo; i < hi; i++) {
             uint64_t l = 0;
             for (uint32_t s = seg_begin[i]; s < seg_begin[i + 1]; s++) l += segs[s].iov_len;
@@ -841,28 +850,66 @@ int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, u
                 l = 0;
             }
             p.len[i] = (uint32_t)l;
+            sum += staged_size((uint32_t)l);
         }
+        part[t] = sum;
     });
     if (too_long) return set_err(ctx, B2C_E_ARG, "message longer than 4 GiB - 1", cudaSuccess);
     const uint64_t target = ctx->slab_bytes;
     const uint32_t max_msgs = 1u << 18;
+    if (!zc) {
+        uint64_t base[65];
+        base[0] = 0;
+        for (unsigned t = 0; t < used; t++) base[t + 1] = base[t] + part[t];
+        uint64_t* g = p.off.data();  // g[i] = staging position of message i if the batch were one slab
+        pool(ctx).run(used, [&](unsigned t, unsigned T) {
+            uint32_t lo = (uint32_t)((uint64_t)n * t / T), hi = (uint32_t)((uint64_t)n * (t + 1) / T);
+            uint64_t pos = base[t];
+            for (uint32_t i = lo; i < hi; i++) {
+                g[i] = pos;
+                pos += staged_size(p.len[i]);
+            }
+        });
+        g[n] = base[used];
+        for (uint32_t s = 0; s < n;) {
+            // the first two slabs are smaller: the pipeline (gather -> H2D -> kernels -> D2H) fills sooner
+            const uint64_t tgt = p.slabs.empty() ? target / 4 : p.slabs.size() == 1 ? target / 2 : target;
+            const uint32_t lim = (uint32_t)std::min<uint64_t>(n, (uint64_t)s + max_msgs);
+            uint32_t e = (uint32_t)(std::upper_bound(g + s + 1, g + lim + 1, g[s] + tgt) - g) - 1;
+            if (e < s + 1) e = s + 1;  // a message larger than the target is a slab of its own
+            p.slabs.push_back({s, e, g[e] - g[s], 0});
+            s = e;
+        }
+        // offsets relative to each slab's start, and the slab's payload
+        std::vector<Slab>& slabs = p.slabs;
+        pool(ctx).run((unsigned)std::min<size_t>(slabs.size(), 64), [&](unsigned t, unsigned T) {
+            for (size_t k = t; k < slabs.size(); k += T) {
+                const uint64_t start = g[slabs[k].m0];
+                uint64_t payload = 0;
+                for (uint32_t i = slabs[k].m0; i < slabs[k].m1; i++) {
+                    g[i] -= start;
+                    payload += p.len[i];
+                }
+                slabs[k].payload = payload;
+            }
+        });
+        for (const Slab& sl : slabs) p.payload += sl.payload;
+        return B2C_OK;
+    }
     Slab cur = {0, 0, 0, 0};
-    const bool zc = ctx->input_pinned;
     for (uint32_t i = 0; i < n; i++) {
         // zero-copy: give the message the same phase modulo 16 as its first block has in host memory, so the
         // device-side gather moves whole aligned 16-byte pieces over PCIe
-        const uint32_t skew = zc && seg_begin[i] < seg_begin[i + 1]
+        const uint32_t skew = seg_begin[i] < seg_begin[i + 1]
                                   ? (uint32_t)(reinterpret_cast<uintptr_t>(segs[seg_begin[i]].iov_base) & 15)
                                   : 0u;
-        // staged: a message of >= 256 bytes starts on a 64-byte line, so the gather writes whole lines only
-        const uint64_t pad = (!zc && p.len[i] >= 256) ? align_up(cur.bytes, 64) - cur.bytes : 0;
-        const uint64_t a = pad + align_up((uint64_t)skew + p.len[i], 16);
+        const uint64_t a = align_up((uint64_t)skew + p.len[i], 16);
         if (cur.m1 > cur.m0 && (cur.bytes + a > target || cur.m1 - cur.m0 >= max_msgs)) {
             p.slabs.push_back(cur);
             cur = {i, i, 0, 0};
         }
-        p.off[i] = cur.bytes + (cur.bytes ? pad : 0) + skew;
-        cur.bytes += cur.bytes ? a : a - pad;
+        p.off[i] = cur.bytes + skew;
+        cur.bytes += a;
         cur.payload += p.len[i];
         cur.m1 = i + 1;
         p.payload += p.len[i];

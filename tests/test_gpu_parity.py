@@ -579,3 +579,57 @@ def test_e2e_zero_copy_gather_from_pinned_blocks(codec, cpu):
         for i in range(0, len(ln), 37):
             a, b = int(off[i]), int(off[i]) + int(ln[i])
             assert_bytes_equal(back[int(b_off[i]):int(b_off[i + 1])].tobytes(), arena[a:b].tobytes(), f"zc back {i}")
+
+
+# ---------------------------------------------------------------- alternate kernel paths stay exact
+@pytest.mark.parametrize("env", [
+    {"B2C_WINDOW": "7"},                                   # window-parallel compressor on every fragment class
+    {"B2C_SMALL2": "0"},                                   # one-phase small-body compressor
+    {"B2C_SMALL2": "1", "B2C_SMALL_LPW_C": "2"},           # two bodies per warp
+    {"B2C_SMALL_KERNELS": "0"},                            # warp kernels for small bodies too
+    {"B2C_GTAB_WPS": "0", "B2C_BATCH_DECODE": "0"},        # shared-memory tables; one tag per step
+    {"B2C_BATCH_DECODE_SMALL": "1", "B2C_RING_DECODE": "1", "B2C_BLOCK_DECODE": "0"},
+    {"B2C_ASYNC_GATHER": "0", "B2C_NT_GATHER": "0", "B2C_SLAB_MB": "1", "B2C_HOST_THREADS": "3"},
+])
+def test_alternate_kernel_paths_agree(cpu, env):
+    """Every tunable path (the defaults are the fastest measured, the others stay selectable) is byte-exact too."""
+    import os
+    import brpc_b200
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        c = brpc_b200.Codec(0)  # the ctx reads its tunables when it is created
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    try:
+        rng = np.random.default_rng(9)
+        lens = np.concatenate([rng.integers(0, 1500, 600), rng.integers(1500, 9000, 60),
+                               [65536, 65537, 200000, 0, 14, 15]]).astype(np.uint32)
+        for kind in ("words", "az09", "rand62"):
+            arena, off, ln = O.corpus_batch(kind, lens, first_index=5)
+            packed, c_off = c.compress(arena, off, ln)
+            w_out, w_off, w_len, _ = cpu.batch_compress(arena, off, ln, threads=4)
+            assert (np.diff(c_off).astype(np.uint32) == w_len).all(), (env, kind)
+            for i in range(len(ln)):
+                assert_bytes_equal(packed[int(c_off[i]):int(c_off[i + 1])].tobytes(),
+                                   w_out[int(w_off[i]):int(w_off[i]) + int(w_len[i])].tobytes(), f"{env} {kind} msg {i}")
+            back, ulen, status = c.decompress(packed, c_off[:-1], np.diff(c_off).astype(np.uint32), off, ln)
+            assert (status == 0).all() and (ulen == ln).all()
+            for i in range(len(ln)):
+                a, b = int(off[i]), int(off[i]) + int(ln[i])
+                assert_bytes_equal(back[a:b].tobytes(), arena[a:b].tobytes(), f"{env} {kind} back {i}")
+        # host-buffer calls on the same ctx
+        arena, off, ln = O.corpus_batch("words", lens, first_index=5)
+        segs, sb = brpc_b200.make_iovecs(arena, off, ln, seg_bytes=8160)
+        out = np.empty(int(sum(32 + int(l) + int(l) // 6 + 5 for l in ln)), dtype=np.uint8)
+        o_off, crc = c.compress_crc_batch(segs, sb, out, masked=False)
+        want_crc, _ = cpu.batch_crc32c(arena, off, ln, threads=4)
+        assert (crc == want_crc).all()
+        w_out, w_off, w_len, _ = cpu.batch_compress(arena, off, ln, threads=4)
+        assert (np.diff(o_off).astype(np.uint32) == w_len).all()
+    finally:
+        c.close()
