@@ -514,6 +514,7 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     if (const char* s = getenv("B2C_SMALL_KERNELS")) ctx->small_kernels = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL_LPW_C")) ctx->small_lpw_compress = atoi(s);
     if (const char* s = getenv("B2C_WINDOW")) ctx->window_mask = atoi(s);
+    if (const char* s = getenv("B2C_WINDOW_STAGE")) ctx->window_stage = atoi(s) != 0;
     if (const char* s = getenv("B2C_ASYNC_GATHER")) ctx->async_gather = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL2")) ctx->small_two_phase = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL_LPW_D")) ctx->small_lpw_decompress = atoi(s);

@@ -139,7 +139,8 @@ struct b2c_ctx {
     bool nt_gather = true;  // B2C_NT_GATHER=0: plain memcpy into staging
     bool async_gather = true;  // B2C_ASYNC_GATHER=0: the submitting thread waits for each slab's gather before anything else
     bool small_two_phase = true;  // B2C_SMALL2=0 restores the one-phase kernel; <=1 KiB bodies compress as find (lane per body) then encode (warp per body)
-    int window_mask = 0;    // B2C_WINDOW: bit c set = fragment class c compresses with the window-parallel kernel
+    bool window_stage = true;  // B2C_WINDOW_STAGE=0: the window compressor reads <=4 KiB fragments from HBM instead of staging them
+    int window_mask = 6;    // B2C_WINDOW: bit c set = fragment class c (0: <=1 KiB, 1: <=4 KiB, 2: <=64 KiB) compresses with the orbit kernel (snappy_window.cu)
 };
 
 struct b2c_layout {

@@ -583,7 +583,9 @@ def test_e2e_zero_copy_gather_from_pinned_blocks(codec, cpu):
 
 # ---------------------------------------------------------------- alternate kernel paths stay exact
 @pytest.mark.parametrize("env", [
-    {"B2C_WINDOW": "7"},                                   # window-parallel compressor on every fragment class
+    {"B2C_WINDOW": "7"},                                   # orbit compressor on every fragment class
+    {"B2C_WINDOW": "0"},                                   # 32-probe warp kernels for fragments > 1 KiB
+    {"B2C_WINDOW": "7", "B2C_WINDOW_STAGE": "0", "B2C_GTAB_WPS": "0"},
     {"B2C_SMALL2": "0"},                                   # one-phase small-body compressor
     {"B2C_SMALL2": "1", "B2C_SMALL_LPW_C": "2"},           # two bodies per warp
     {"B2C_SMALL_KERNELS": "0"},                            # warp kernels for small bodies too
