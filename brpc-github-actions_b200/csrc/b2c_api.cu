@@ -508,6 +508,7 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     if (const char* s = getenv("B2C_BATCH_DECODE")) ctx->batch_decode = atoi(s) != 0;
     if (const char* s = getenv("B2C_RING_DECODE")) ctx->ring_decode = atoi(s) != 0;
     if (const char* s = getenv("B2C_BLOCK_DECODE")) ctx->block_decode = atoi(s) != 0;
+    if (const char* s = getenv("B2C_LIFT_SCAN")) ctx->lift_scan = atoi(s) != 0;
     if (const char* s = getenv("B2C_BATCH_DECODE_SMALL")) ctx->batch_decode_small = atoi(s) != 0;
     if (const char* s = getenv("B2C_NT_GATHER")) ctx->nt_gather = atoi(s) != 0;
     if (const char* s = getenv("B2C_GTAB_WPS")) ctx->gtab_warps_per_sm = atoi(s);
@@ -515,6 +516,7 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     if (const char* s = getenv("B2C_SMALL_LPW_C")) ctx->small_lpw_compress = atoi(s);
     if (const char* s = getenv("B2C_WINDOW")) ctx->window_mask = atoi(s);
     if (const char* s = getenv("B2C_WINDOW_STAGE")) ctx->window_stage = atoi(s) != 0;
+    if (const char* s = getenv("B2C_WINDOW_WPS")) ctx->window_warps_per_sm = atoi(s);
     if (const char* s = getenv("B2C_ASYNC_GATHER")) ctx->async_gather = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL2")) ctx->small_two_phase = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL_LPW_D")) ctx->small_lpw_decompress = atoi(s);

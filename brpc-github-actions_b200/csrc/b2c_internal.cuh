@@ -132,6 +132,7 @@ struct b2c_ctx {
     bool trace = false;
     bool input_pinned = false;  // B2C_OPT_INPUT_PINNED: *_batch inputs are page-locked, gather them on the device
     bool ring_decode = false;        // B2C_RING_DECODE=1: unsplittable large slots decode through a 64 KiB smem ring
+    bool lift_scan = true;           // B2C_LIFT_SCAN=0: find the 64 KiB block boundaries with the tag-by-tag scan
     bool block_decode = true;        // B2C_BLOCK_DECODE=0: never split large streams into 64 KiB blocks
     bool ring_attr_done = false;
     bool batch_decode = true;        // B2C_BATCH_DECODE=0: one tag per step in the warp decoder
@@ -139,6 +140,7 @@ struct b2c_ctx {
     bool nt_gather = true;  // B2C_NT_GATHER=0: plain memcpy into staging
     bool async_gather = true;  // B2C_ASYNC_GATHER=0: the submitting thread waits for each slab's gather before anything else
     bool small_two_phase = true;  // B2C_SMALL2=0 restores the one-phase kernel; <=1 KiB bodies compress as find (lane per body) then encode (warp per body)
+    int window_warps_per_sm = 40;  // B2C_WINDOW_WPS: resident warps per SM of the orbit kernel on 64 KiB fragments (tables in HBM/L2; B2C_GTAB_WPS=0 keeps them in shared memory)
     bool window_stage = true;  // B2C_WINDOW_STAGE=0: the window compressor reads <=4 KiB fragments from HBM instead of staging them
     int window_mask = 6;    // B2C_WINDOW: bit c set = fragment class c (0: <=1 KiB, 1: <=4 KiB, 2: <=64 KiB) compresses with the orbit kernel (snappy_window.cu)
 };

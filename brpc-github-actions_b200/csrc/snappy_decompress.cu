@@ -502,6 +502,184 @@ __global__ void __launch_bounds__(256) snappy_scan_kernel(DecompressParams P) {
     }
 }
 
+// ---------------------------------------------------------------------------
+// Pass 1, faster: block boundaries by POINTER LIFTING instead of a tag-by-tag walk.
+// ---------------------------------------------------------------------------
+// Where the next tag starts is a function of the bytes at a position alone: next(p) = p + (bytes the element at p
+// occupies in the stream), and so is the output it produces.  So for a 256-byte window of the stream the warp
+// evaluates next() and out() at ALL 256 positions at once (as if a tag started at each), then squares the pair
+// (next, out-sum) seven times: after level k entry p holds where the chain is 2^k elements on and what they produced
+// (an element is >= 2 bytes, so 128 hops leave the window).  One shared-memory read at the window's true entry position
+// then yields where the chain leaves the window and how much output the window accounts for: ~7 dependent
+// shared-memory rounds per 256 stream bytes instead of ~90 dependent tag steps.  Only a window in which the output
+// count crosses a multiple of 64 KiB is walked tag by tag, to find the tag that starts the block (or to learn that an
+// element straddles the boundary).  This pass validates nothing beyond "the chain ends exactly at the stream's end with
+// the announced output": every block is validated when it is decoded, and a block that fails hands its stream to the
+// whole-stream decoder (which alone decides between corrupt and merely unsplittable).
+constexpr uint32_t kLiftWin = 256;
+constexpr uint32_t kLiftBad = 0xfffffff0u;  // element cut short by the end of the stream (or position past the end)
+
+struct LiftScratch {
+    uint32_t N[kLiftWin];
+    uint32_t S[kLiftWin];
+    uint32_t words[kLiftWin / 4 + 4];
+};
+
+// element at window-relative position p: stream bytes it occupies (0 = invalid / cut short) and output bytes
+__device__ __forceinline__ uint64_t lift_element(uint32_t b4, uint32_t b5th, uint32_t left /* n - abs, >= 1 */, uint32_t* out) {
+    const uint32_t c = b4 & 0xff, kind = c & 3;
+    if (kind == 0) {
+        uint32_t l = c >> 2, hdr = 1, len = l + 1;
+        if (l >= 60) {
+            const uint32_t extra = l - 59;
+            hdr = 1 + extra;
+            if (left < hdr) return 0;
+            uint32_t v = b4 >> 8;
+            if (extra == 4) v |= b5th << 24;
+            else v &= (1u << (8 * extra)) - 1u;
+            len = v + 1u;  // may wrap to 0 like the reference
+        }
+        *out = len;
+        const uint64_t size = (uint64_t)hdr + len;
+        return size <= left ? size : 0;
+    }
+    const uint32_t size = kind == 1 ? 2u : kind == 2 ? 3u : 5u;
+    *out = kind == 1 ? ((c >> 2) & 7) + 4 : (c >> 2) + 1;
+    return size <= left ? size : 0;
+}
+
+__global__ void __launch_bounds__(256) snappy_scan_lift_kernel(DecompressParams P) {
+    __shared__ LiftScratch scratch[8];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t wib = threadIdx.x >> 5;
+    const uint32_t w = blockIdx.x * (blockDim.x >> 5) + wib;
+    if (w >= P.n_list) return;
+    const uint32_t m = P.list ? P.list[w] : w;
+    const uint32_t cap = P.out_cap[m];
+    if (cap <= kFragBytes) {  // single block: nothing to split
+        if (lane == 0) P.mode[m] = kModeWhole;
+        return;
+    }
+    const uint8_t* in = P.in + P.in_off[m];
+    const uint32_t n = P.in_len[m];
+    uint32_t expected = 0;
+    const uint32_t k = read_preamble(in, n, &expected);
+    int st = B2C_OK;
+    uint32_t mode = kModeDone;
+    if (k == 0) {
+        st = B2C_CORRUPT;
+    } else if (expected > cap) {
+        st = B2C_TOO_SMALL;
+    } else if (expected <= kFragBytes) {
+        mode = kModeWhole;
+    } else {
+        LiftScratch& sc = scratch[wib];
+        const uint8_t* wb = reinterpret_cast<const uint8_t*>(sc.words);
+        const uint32_t f0 = P.out_frag_first[m];
+        const uint32_t nblk = (expected + kFragBytes - 1) / kFragBytes;
+        if (lane == 0) P.blk_ip[f0] = k;
+        uint32_t pos = k, cum = 0, next_blk = 1;
+        bool ok = true;
+        while (ok && pos < n) {
+            const uint32_t wbase = pos & ~(kLiftWin - 1);
+            __syncwarp();
+            // ---- the window's bytes (+ the look-ahead a tag at its last position needs) ----
+            for (uint32_t wi = lane; wi < kLiftWin / 4 + 4; wi += 32) {
+                const uint32_t at = wbase + 4 * wi;
+                sc.words[wi] = at < n ? ld32u(in + at) : 0u;
+            }
+            __syncwarp();
+            // ---- next() and out() at the 8 positions of this lane ----
+            uint32_t Nr[8], Sr[8];
+            {
+                const uint32_t w0 = sc.words[2 * lane], w1 = sc.words[2 * lane + 1], w2 = sc.words[2 * lane + 2];
+#pragma unroll
+                for (uint32_t j = 0; j < 8; j++) {
+                    const uint32_t p = lane * 8 + j, abs = wbase + p;
+                    const uint32_t lo = j < 4 ? w0 : w1, hi = j < 4 ? w1 : w2;
+                    const uint32_t b4 = __funnelshift_r(lo, hi, (j & 3) * 8);
+                    uint32_t o = 0;
+                    uint64_t size = 0;
+                    if (abs < n) size = lift_element(b4, wb[p + 4], n - abs, &o);
+                    // the stream's end is a fixed point (a chain that reaches it stays there and leaves the loop below)
+                    Nr[j] = size ? (uint32_t)min((unsigned long long)(p + size), (unsigned long long)(kLiftBad - 1))
+                                 : (abs == n ? p : kLiftBad);
+                    Sr[j] = size ? o : 0u;
+                    sc.N[p] = Nr[j];
+                    sc.S[p] = Sr[j];
+                }
+            }
+            __syncwarp();
+            // ---- square (next, sum) seven times ----
+#pragma unroll 1
+            for (int lev = 0; lev < 7; lev++) {
+                uint32_t nq[8], sq[8];
+#pragma unroll
+                for (uint32_t j = 0; j < 8; j++) {
+                    const uint32_t q = Nr[j];
+                    nq[j] = q < kLiftWin ? sc.N[q] : q;
+                    sq[j] = q < kLiftWin ? sc.S[q] : 0u;
+                }
+                __syncwarp();
+#pragma unroll
+                for (uint32_t j = 0; j < 8; j++) {
+                    if (Nr[j] < kLiftWin) {
+                        Nr[j] = nq[j];
+                        const uint32_t t = Sr[j] + sq[j];
+                        Sr[j] = t < Sr[j] ? 0xffffffffu : t;  // saturate
+                        sc.N[lane * 8 + j] = Nr[j];
+                        sc.S[lane * 8 + j] = Sr[j];
+                    }
+                }
+                __syncwarp();
+            }
+            const uint32_t e = pos - wbase;
+            const uint32_t exit_rel = sc.N[e], add = sc.S[e];
+            if (exit_rel == kLiftBad || add > expected - cum) {  // cut short, or more output than announced
+                ok = false;
+                break;
+            }
+            // ---- a block starts inside this window (or right at its exit): find the tag, one hop at a time ----
+            if (next_blk < nblk && (uint64_t)cum + add >= (uint64_t)next_blk * kFragBytes) {
+                uint32_t p = e, c = cum;
+                for (;;) {
+                    const uint32_t target = next_blk * kFragBytes;
+                    if (c == target) {
+                        if (lane == 0) P.blk_ip[f0 + next_blk] = wbase + p;
+                        next_blk++;
+                        if (next_blk == nblk || (uint64_t)cum + add < (uint64_t)next_blk * kFragBytes) break;
+                    }
+                    if (p >= kLiftWin) {  // the chain has left the window without meeting the boundary: an element straddles it
+                        ok = false;
+                        break;
+                    }
+                    const uint32_t b4 = __funnelshift_r(sc.words[p >> 2], sc.words[(p >> 2) + 1], (p & 3) * 8);
+                    uint32_t o = 0;
+                    const uint64_t size = lift_element(b4, wb[p + 4], n - (wbase + p), &o);
+                    if (size == 0 || (c < target && c + o > target)) {
+                        ok = false;
+                        break;
+                    }
+                    c += o;
+                    p += (uint32_t)min((unsigned long long)size, (unsigned long long)kLiftBad);
+                }
+                if (!ok) break;
+            }
+            cum += add;
+            pos = wbase + exit_rel;  // exit_rel < kLiftBad - 1 + ...: an element never ends past n (checked per element)
+        }
+        mode = (ok && pos == n && cum == expected && next_blk == nblk) ? kModeBlocks : kModeWhole;
+    }
+    if (lane == 0) {
+        P.mode[m] = mode;
+        P.ulen_tmp[m] = expected;
+        if (mode != kModeWhole) {
+            P.status[m] = st;
+            if (P.ulen) P.ulen[m] = expected;
+        }
+    }
+}
+
 // Pass 2 for large slots: every 64 KiB block of a splittable stream is decoded by its own warp.
 __global__ void __launch_bounds__(256) snappy_decompress_blocks_kernel(DecompressParams P) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -521,7 +699,9 @@ __global__ void __launch_bounds__(256) snappy_decompress_blocks_kernel(Decompres
     LinearOut lo{P.out + P.out_off[m] + begin};
     BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * 1024);
     const int st = decode_message_batched(P.in + P.in_off[m], ip1, ip0, lo, block_len, lane, sc);
-    if (st != B2C_OK && lane == 0) atomicMax(reinterpret_cast<int*>(&P.status[m]), st);
+    // a block that does not decode on its own: the stream is corrupt, or merely not splittable (a copy that reaches
+    // back across the block's start); the whole-stream decoder, launched next, redoes it and decides
+    if (st != B2C_OK && lane == 0) P.mode[m] = kModeWhole;
 }
 
 
@@ -728,7 +908,10 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
             // only large-slot messages get a mode from the scan; everything else must read as "whole"
             B2C_CUDA(ctx, cudaMemsetAsync(P.mode, 0, (size_t)out.n * 4, lane.stream));
             const uint32_t sblocks = (P.n_list + 7) / 8;
-            snappy_scan_kernel<<<sblocks, 256, 8 * 1024, lane.stream>>>(P);
+            if (ctx->lift_scan)
+                snappy_scan_lift_kernel<<<sblocks, 256, 0, lane.stream>>>(P);
+            else
+                snappy_scan_kernel<<<sblocks, 256, 8 * 1024, lane.stream>>>(P);
             const uint32_t bblocks = (P.n_blocks + 7) / 8;
             snappy_decompress_blocks_kernel<<<bblocks, 256, 8 * 1024, lane.stream>>>(P);
             ctx->launches += 2;

@@ -324,8 +324,11 @@ int launch_compress_window(b2c_ctx* ctx, Lane& lane, const LayoutView& L, int c,
     uint32_t wpb = warps[c];
     uint32_t resident;  // CTAs per SM the launch is sized for
     if (c == 2 && ctx->gtab_warps_per_sm > 0) {  // 64 KiB fragments: tables in HBM/L2, many resident warps
+        // A round is a chain of 2-3 L2 round trips, so throughput follows the number of resident warps: measured on
+        // C5/words 68.9 / 38.9 / 31.6 / 26.9 / 23.7 ms per GiB at 8 / 16 / 24 / 32 / 40 warps per SM (40 = the
+        // register limit; tables in shared memory allow 6: 80 ms).
         wpb = 8;
-        resident = std::max(1, ctx->gtab_warps_per_sm / 8);
+        resident = std::max(1, ctx->window_warps_per_sm / 8);
         P.table_entries = 0;
     } else {
         const size_t pw = kQueue * sizeof(uint2) + (size_t)P.table_entries * 2 + P.in_stride;
