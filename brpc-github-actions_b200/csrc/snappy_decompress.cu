@@ -548,135 +548,259 @@ __device__ __forceinline__ uint64_t lift_element(uint32_t b4, uint32_t b5th, uin
     return size <= left ? size : 0;
 }
 
-__global__ void __launch_bounds__(256) snappy_scan_lift_kernel(DecompressParams P) {
-    __shared__ LiftScratch scratch[8];
-    const uint32_t lane = threadIdx.x & 31;
-    const uint32_t wib = threadIdx.x >> 5;
-    const uint32_t w = blockIdx.x * (blockDim.x >> 5) + wib;
+// next() and out() at all 256 positions of the window at wbase, squared seven times: on return N[e] / S[e] say where
+// a chain entering the window at e leaves it (window-relative; kLiftBad: cut short; a fixed point N[e] == e: the
+// stream's end) and how much output it produces on the way.  Whole warp; N, S, words are the warp's shared memory.
+__device__ __forceinline__ void lift_window(const uint8_t* __restrict__ in, const uint32_t n, const uint32_t wbase,
+                                            uint32_t* N, uint32_t* S, uint32_t* words, const uint32_t lane) {
+    const uint8_t* wb = reinterpret_cast<const uint8_t*>(words);
+    __syncwarp();
+    for (uint32_t wi = lane; wi < kLiftWin / 4 + 4; wi += 32) {  // the bytes (+ the look-ahead of a tag at the last position)
+        const uint32_t at = wbase + 4 * wi;
+        words[wi] = at < n ? ld32u(in + at) : 0u;
+    }
+    __syncwarp();
+    uint32_t Nr[8], Sr[8];
+    {
+        const uint32_t w0 = words[2 * lane], w1 = words[2 * lane + 1], w2 = words[2 * lane + 2];
+#pragma unroll
+        for (uint32_t j = 0; j < 8; j++) {
+            const uint32_t p = lane * 8 + j, abs = wbase + p;
+            const uint32_t lo = j < 4 ? w0 : w1, hi = j < 4 ? w1 : w2;
+            const uint32_t b4 = __funnelshift_r(lo, hi, (j & 3) * 8);
+            uint32_t o = 0;
+            uint64_t size = 0;
+            if (abs < n) size = lift_element(b4, wb[p + 4], n - abs, &o);
+            // the stream's end is a fixed point (a chain that reaches it stays there)
+            Nr[j] = size ? (uint32_t)min((unsigned long long)(p + size), (unsigned long long)(kLiftBad - 1))
+                         : (abs == n ? p : kLiftBad);
+            Sr[j] = size ? o : 0u;
+            N[p] = Nr[j];
+            S[p] = Sr[j];
+        }
+    }
+    __syncwarp();
+#pragma unroll 1
+    for (int lev = 0; lev < 7; lev++) {
+        uint32_t nq[8], sq[8];
+#pragma unroll
+        for (uint32_t j = 0; j < 8; j++) {
+            const uint32_t q = Nr[j];
+            nq[j] = q < kLiftWin ? N[q] : q;
+            sq[j] = q < kLiftWin ? S[q] : 0u;
+        }
+        __syncwarp();
+#pragma unroll
+        for (uint32_t j = 0; j < 8; j++) {
+            if (Nr[j] < kLiftWin) {
+                Nr[j] = nq[j];
+                const uint32_t t = Sr[j] + sq[j];
+                Sr[j] = t < Sr[j] ? 0xffffffffu : t;  // saturate
+                N[lane * 8 + j] = Nr[j];
+                S[lane * 8 + j] = Sr[j];
+            }
+        }
+        __syncwarp();
+    }
+}
+
+// One stream, one warp, window after window from `pos` (with `cum` bytes of output before it) until the chain
+// leaves [pos, stop) or ends; returns false when the stream is irregular.  When `want` is a block boundary inside the
+// stretch, *found receives the stream offset of the tag that starts that block.
+__device__ bool lift_walk(const uint8_t* __restrict__ in, const uint32_t n, const uint32_t expected, uint32_t& pos,
+                          uint32_t& cum, const uint64_t stop, const uint32_t want, uint32_t* found, LiftScratch& sc,
+                          const uint32_t lane) {
+    const uint8_t* wb = reinterpret_cast<const uint8_t*>(sc.words);
+    while (pos < n && pos < stop) {
+        const uint32_t wbase = pos & ~(kLiftWin - 1);
+        lift_window(in, n, wbase, sc.N, sc.S, sc.words, lane);
+        const uint32_t e = pos - wbase;
+        const uint32_t exit_rel = sc.N[e], add = sc.S[e];
+        if (exit_rel == kLiftBad || add > expected - cum) return false;  // cut short, or more output than announced
+        if (found && cum <= want && (uint64_t)cum + add >= want) {
+            // the block starts inside this window (or right at its exit): find the tag, one hop at a time
+            uint32_t p = e, c = cum;
+            for (;;) {
+                if (c == want) {
+                    *found = wbase + p;
+                    return true;
+                }
+                if (p >= kLiftWin) return false;
+                const uint32_t b4 = __funnelshift_r(sc.words[p >> 2], sc.words[(p >> 2) + 1], (p & 3) * 8);
+                uint32_t o = 0;
+                const uint64_t size = lift_element(b4, wb[p + 4], n - (wbase + p), &o);
+                if (size == 0 || c + o > want) return false;  // cut short, or an element straddles the boundary
+                c += o;
+                p += (uint32_t)min((unsigned long long)size, (unsigned long long)kLiftBad);
+            }
+        }
+        cum += add;
+        if (exit_rel == e) {  // fixed point: the stream's end
+            pos = n;
+            break;
+        }
+        pos = wbase + exit_rel;
+    }
+    return true;
+}
+
+constexpr uint32_t kSegBytes = 8192;  // stream bytes per segment (32 windows)
+constexpr uint32_t kSegWins = kSegBytes / kLiftWin;
+
+struct SegScanParams {
+    DecompressParams D;
+    uint32_t* seg_cnt;        // [n_list]    segments of the w-th listed stream (0: not scanned)
+    const uint64_t* seg_base; // [n_list+1]  exclusive scan of seg_cnt
+    uint2* seg_tab;           // [segments][256]  (absolute exit position or kLiftBad, output sum) per entry offset
+    uint2* bnd;               // [output blocks]  where to start looking for the block's first tag: (stream pos, output before it)
+    uint32_t seg_cap;         // capacity of seg_tab in segments
+};
+
+// K0: which streams are scanned, and how many segments each has.
+__global__ void snappy_seg_count_kernel(SegScanParams Q) {
+    const DecompressParams& P = Q.D;
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= P.n_list) return;
     const uint32_t m = P.list ? P.list[w] : w;
     const uint32_t cap = P.out_cap[m];
-    if (cap <= kFragBytes) {  // single block: nothing to split
-        if (lane == 0) P.mode[m] = kModeWhole;
-        return;
-    }
     const uint8_t* in = P.in + P.in_off[m];
     const uint32_t n = P.in_len[m];
-    uint32_t expected = 0;
-    const uint32_t k = read_preamble(in, n, &expected);
+    uint32_t expected = 0, cnt = 0, mode = kModeWhole;
     int st = B2C_OK;
-    uint32_t mode = kModeDone;
-    if (k == 0) {
-        st = B2C_CORRUPT;
-    } else if (expected > cap) {
-        st = B2C_TOO_SMALL;
-    } else if (expected <= kFragBytes) {
-        mode = kModeWhole;
-    } else {
-        LiftScratch& sc = scratch[wib];
-        const uint8_t* wb = reinterpret_cast<const uint8_t*>(sc.words);
-        const uint32_t f0 = P.out_frag_first[m];
-        const uint32_t nblk = (expected + kFragBytes - 1) / kFragBytes;
-        if (lane == 0) P.blk_ip[f0] = k;
-        uint32_t pos = k, cum = 0, next_blk = 1;
-        bool ok = true;
-        while (ok && pos < n) {
-            const uint32_t wbase = pos & ~(kLiftWin - 1);
-            __syncwarp();
-            // ---- the window's bytes (+ the look-ahead a tag at its last position needs) ----
-            for (uint32_t wi = lane; wi < kLiftWin / 4 + 4; wi += 32) {
-                const uint32_t at = wbase + 4 * wi;
-                sc.words[wi] = at < n ? ld32u(in + at) : 0u;
-            }
-            __syncwarp();
-            // ---- next() and out() at the 8 positions of this lane ----
-            uint32_t Nr[8], Sr[8];
-            {
-                const uint32_t w0 = sc.words[2 * lane], w1 = sc.words[2 * lane + 1], w2 = sc.words[2 * lane + 2];
-#pragma unroll
-                for (uint32_t j = 0; j < 8; j++) {
-                    const uint32_t p = lane * 8 + j, abs = wbase + p;
-                    const uint32_t lo = j < 4 ? w0 : w1, hi = j < 4 ? w1 : w2;
-                    const uint32_t b4 = __funnelshift_r(lo, hi, (j & 3) * 8);
-                    uint32_t o = 0;
-                    uint64_t size = 0;
-                    if (abs < n) size = lift_element(b4, wb[p + 4], n - abs, &o);
-                    // the stream's end is a fixed point (a chain that reaches it stays there and leaves the loop below)
-                    Nr[j] = size ? (uint32_t)min((unsigned long long)(p + size), (unsigned long long)(kLiftBad - 1))
-                                 : (abs == n ? p : kLiftBad);
-                    Sr[j] = size ? o : 0u;
-                    sc.N[p] = Nr[j];
-                    sc.S[p] = Sr[j];
-                }
-            }
-            __syncwarp();
-            // ---- square (next, sum) seven times ----
-#pragma unroll 1
-            for (int lev = 0; lev < 7; lev++) {
-                uint32_t nq[8], sq[8];
-#pragma unroll
-                for (uint32_t j = 0; j < 8; j++) {
-                    const uint32_t q = Nr[j];
-                    nq[j] = q < kLiftWin ? sc.N[q] : q;
-                    sq[j] = q < kLiftWin ? sc.S[q] : 0u;
-                }
-                __syncwarp();
-#pragma unroll
-                for (uint32_t j = 0; j < 8; j++) {
-                    if (Nr[j] < kLiftWin) {
-                        Nr[j] = nq[j];
-                        const uint32_t t = Sr[j] + sq[j];
-                        Sr[j] = t < Sr[j] ? 0xffffffffu : t;  // saturate
-                        sc.N[lane * 8 + j] = Nr[j];
-                        sc.S[lane * 8 + j] = Sr[j];
-                    }
-                }
-                __syncwarp();
-            }
-            const uint32_t e = pos - wbase;
-            const uint32_t exit_rel = sc.N[e], add = sc.S[e];
-            if (exit_rel == kLiftBad || add > expected - cum) {  // cut short, or more output than announced
+    if (cap > kFragBytes) {
+        const uint32_t k = read_preamble(in, n, &expected);
+        if (k == 0) {
+            st = B2C_CORRUPT;
+            mode = kModeDone;
+        } else if (expected > cap) {
+            st = B2C_TOO_SMALL;
+            mode = kModeDone;
+        } else if (expected > kFragBytes) {
+            cnt = (n + kSegBytes - 1) / kSegBytes;
+        }
+    }
+    Q.seg_cnt[w] = cnt;
+    P.mode[m] = mode;  // scanned streams: upgraded to kModeBlocks by the chain kernel
+    P.ulen_tmp[m] = expected;
+    if (mode == kModeDone) {
+        P.status[m] = st;
+        if (P.ulen) P.ulen[m] = expected;
+    }
+}
+
+// KA: one CTA per segment.  Its 8 warps lift the segment's 32 windows; then thread t follows the chain that enters the
+// segment at offset t (< 256) through the window tables until it leaves the segment.
+__global__ void __launch_bounds__(256) snappy_seg_tables_kernel(SegScanParams Q) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    uint32_t* TN = reinterpret_cast<uint32_t*>(smem_raw);             // [32][256]
+    uint32_t* TS = TN + kSegWins * kLiftWin;                           // [32][256]
+    uint32_t* words = TS + kSegWins * kLiftWin;                        // [8][72]
+    const DecompressParams& P = Q.D;
+    const uint64_t g = blockIdx.x;
+    if (g >= Q.seg_base[P.n_list] || g >= Q.seg_cap) return;
+    uint32_t lo = 0, hi = P.n_list;  // the listed stream w with seg_base[w] <= g < seg_base[w+1]
+    while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (Q.seg_base[mid] <= g) lo = mid;
+        else hi = mid;
+    }
+    const uint32_t w = lo, seg = (uint32_t)(g - Q.seg_base[w]);
+    const uint32_t m = P.list ? P.list[w] : w;
+    const uint8_t* in = P.in + P.in_off[m];
+    const uint32_t n = P.in_len[m];
+    const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const uint32_t sbase = seg * kSegBytes;
+    for (uint32_t wi = wib; wi < kSegWins; wi += 8)
+        lift_window(in, n, sbase + wi * kLiftWin, TN + wi * kLiftWin, TS + wi * kLiftWin, words + wib * 72, lane);
+    __syncthreads();
+    uint32_t pos = threadIdx.x, sum = 0;  // segment-relative
+    bool bad = false;
+    for (uint32_t it = 0; it < kSegWins + 1 && pos < kSegBytes; it++) {
+        const uint32_t wi = pos >> 8, e = pos & (kLiftWin - 1);
+        const uint32_t N = TN[wi * kLiftWin + e], S = TS[wi * kLiftWin + e];
+        if (N == kLiftBad) {
+            bad = true;
+            break;
+        }
+        sum = sum + S < sum ? 0xffffffffu : sum + S;
+        if (N == e) {  // the stream's end
+            pos = n - sbase;
+            break;
+        }
+        pos = (wi << 8) + N;  // an element never ends past n, so this stays below 2^32
+    }
+    Q.seg_tab[g * kLiftWin + threadIdx.x] = make_uint2(bad ? kLiftBad : sbase + pos, sum);
+}
+
+// KB: one warp per scanned stream hops from segment to segment through the tables (a chain that enters a segment
+// beyond its first window -- after a long literal -- is walked window by window to the segment's end instead), checks
+// that it ends at the stream's end with the announced output, and notes for every block boundary where to look for it.
+__global__ void __launch_bounds__(256) snappy_seg_chain_kernel(SegScanParams Q) {
+    __shared__ LiftScratch scratch[8];
+    const DecompressParams& P = Q.D;
+    const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const uint32_t w = blockIdx.x * (blockDim.x >> 5) + wib;
+    if (w >= P.n_list) return;
+    const uint64_t g0 = Q.seg_base[w];
+    if (Q.seg_base[w + 1] == g0) return;  // not scanned
+    const uint32_t m = P.list ? P.list[w] : w;
+    const uint8_t* in = P.in + P.in_off[m];
+    const uint32_t n = P.in_len[m];
+    const uint32_t expected = P.ulen_tmp[m];
+    uint32_t tmp = 0;
+    const uint32_t k = read_preamble(in, n, &tmp);
+    const uint32_t f0 = P.out_frag_first[m];
+    const uint32_t nblk = (expected + kFragBytes - 1) / kFragBytes;
+    if (lane == 0) P.blk_ip[f0] = k;
+    uint32_t pos = k, cum = 0, nb = 1;
+    bool ok = Q.seg_base[w + 1] <= Q.seg_cap;
+    while (ok && pos < n) {
+        const uint32_t seg = pos / kSegBytes, e = pos - seg * kSegBytes;
+        const uint32_t pos0 = pos, cum0 = cum;
+        if (e < kLiftWin) {
+            const uint2 t = Q.seg_tab[(g0 + seg) * kLiftWin + e];
+            if (t.x == kLiftBad || t.y > expected - cum) {
                 ok = false;
                 break;
             }
-            // ---- a block starts inside this window (or right at its exit): find the tag, one hop at a time ----
-            if (next_blk < nblk && (uint64_t)cum + add >= (uint64_t)next_blk * kFragBytes) {
-                uint32_t p = e, c = cum;
-                for (;;) {
-                    const uint32_t target = next_blk * kFragBytes;
-                    if (c == target) {
-                        if (lane == 0) P.blk_ip[f0 + next_blk] = wbase + p;
-                        next_blk++;
-                        if (next_blk == nblk || (uint64_t)cum + add < (uint64_t)next_blk * kFragBytes) break;
-                    }
-                    if (p >= kLiftWin) {  // the chain has left the window without meeting the boundary: an element straddles it
-                        ok = false;
-                        break;
-                    }
-                    const uint32_t b4 = __funnelshift_r(sc.words[p >> 2], sc.words[(p >> 2) + 1], (p & 3) * 8);
-                    uint32_t o = 0;
-                    const uint64_t size = lift_element(b4, wb[p + 4], n - (wbase + p), &o);
-                    if (size == 0 || (c < target && c + o > target)) {
-                        ok = false;
-                        break;
-                    }
-                    c += o;
-                    p += (uint32_t)min((unsigned long long)size, (unsigned long long)kLiftBad);
-                }
-                if (!ok) break;
-            }
-            cum += add;
-            pos = wbase + exit_rel;  // exit_rel < kLiftBad - 1 + ...: an element never ends past n (checked per element)
+            pos = t.x;
+            cum += t.y;
+        } else {
+            ok = lift_walk(in, n, expected, pos, cum, (uint64_t)(seg + 1) * kSegBytes, 0u, nullptr, scratch[wib], lane);
+            if (!ok) break;
         }
-        mode = (ok && pos == n && cum == expected && next_blk == nblk) ? kModeBlocks : kModeWhole;
+        while (nb < nblk && (uint64_t)cum >= (uint64_t)nb * kFragBytes) {  // boundary in (cum0, cum]
+            if (lane == 0) Q.bnd[f0 + nb] = make_uint2(pos0, cum0);
+            nb++;
+        }
     }
+    if (lane == 0 && ok && pos == n && cum == expected && nb == nblk) {
+        P.mode[m] = kModeBlocks;
+        P.status[m] = B2C_OK;
+        if (P.ulen) P.ulen[m] = expected;
+    }
+}
+
+// KC: one warp per block boundary walks from the noted position to the tag that starts the block.
+__global__ void __launch_bounds__(256) snappy_seg_boundary_kernel(SegScanParams Q) {
+    __shared__ LiftScratch scratch[8];
+    const DecompressParams& P = Q.D;
+    const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const uint32_t f = blockIdx.x * (blockDim.x >> 5) + wib;
+    if (f >= P.n_blocks) return;
+    const uint32_t m = P.out_frag_msg[f];
+    if (P.mode[m] != kModeBlocks) return;
+    const uint32_t kb = f - P.out_frag_first[m];
+    if (kb == 0) return;
+    const uint32_t expected = P.ulen_tmp[m];
+    if ((uint64_t)kb * kFragBytes >= expected) return;
+    const uint2 start = Q.bnd[f];
+    uint32_t pos = start.x, cum = start.y, found = 0xffffffffu;
+    const bool ok = lift_walk(P.in + P.in_off[m], P.in_len[m], expected, pos, cum, ~0ull, kb * kFragBytes, &found,
+                              scratch[wib], lane);
     if (lane == 0) {
-        P.mode[m] = mode;
-        P.ulen_tmp[m] = expected;
-        if (mode != kModeWhole) {
-            P.status[m] = st;
-            if (P.ulen) P.ulen[m] = expected;
-        }
+        if (ok && found != 0xffffffffu) P.blk_ip[f] = found;
+        else P.mode[m] = kModeWhole;  // an element straddles the boundary: not splittable
     }
 }
 
@@ -908,10 +1032,37 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
             // only large-slot messages get a mode from the scan; everything else must read as "whole"
             B2C_CUDA(ctx, cudaMemsetAsync(P.mode, 0, (size_t)out.n * 4, lane.stream));
             const uint32_t sblocks = (P.n_list + 7) / 8;
-            if (ctx->lift_scan)
-                snappy_scan_lift_kernel<<<sblocks, 256, 0, lane.stream>>>(P);
-            else
+            if (ctx->lift_scan) {
+                // segment tables for every scanned stream, a hop-per-segment chain per stream, a walk per boundary
+                SegScanParams Q;
+                Q.D = P;
+                const size_t seg_cap = (size_t)(in.payload / kSegBytes) + P.n_list + 1;
+                const size_t scan_tmp = ((size_t)(P.n_list + 1023) / 1024 + 2) * 8;
+                const size_t tab_bytes = seg_cap * kLiftWin * sizeof(uint2);
+                const size_t need = tab_bytes + (size_t)out.n_frags * sizeof(uint2) + ((size_t)P.n_list + 1) * 8 +
+                                    (size_t)P.n_list * 4 + scan_tmp + 256;
+                if ((rc = ws_reserve(ctx, lane, lane.ws_tab, need))) return rc;
+                uint8_t* wsb = static_cast<uint8_t*>(lane.ws_tab.p);
+                Q.seg_tab = reinterpret_cast<uint2*>(wsb);
+                Q.bnd = reinterpret_cast<uint2*>(wsb + tab_bytes);
+                uint64_t* seg_base = reinterpret_cast<uint64_t*>(wsb + tab_bytes + (size_t)out.n_frags * sizeof(uint2));
+                Q.seg_base = seg_base;
+                void* tmp = seg_base + P.n_list + 1;
+                Q.seg_cnt = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(tmp) + scan_tmp);
+                Q.seg_cap = (uint32_t)std::min<size_t>(seg_cap, 0xffffffffu);
+                snappy_seg_count_kernel<<<(P.n_list + 255) / 256, 256, 0, lane.stream>>>(Q);
+                ctx->launches++;
+                if ((rc = launch_scan_u32_u64(ctx, lane, Q.seg_cnt, P.n_list, seg_base, tmp))) return rc;
+                const int tab_smem = (int)(2 * kSegWins * kLiftWin * 4 + 8 * 72 * 4);
+                B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_seg_tables_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                   tab_smem));
+                snappy_seg_tables_kernel<<<(uint32_t)Q.seg_cap, 256, tab_smem, lane.stream>>>(Q);
+                snappy_seg_chain_kernel<<<sblocks, 256, 0, lane.stream>>>(Q);
+                snappy_seg_boundary_kernel<<<(P.n_blocks + 7) / 8, 256, 0, lane.stream>>>(Q);
+                ctx->launches += 2;  // + the chain kernel counted with the blocks kernel below
+            } else {
                 snappy_scan_kernel<<<sblocks, 256, 8 * 1024, lane.stream>>>(P);
+            }
             const uint32_t bblocks = (P.n_blocks + 7) / 8;
             snappy_decompress_blocks_kernel<<<bblocks, 256, 8 * 1024, lane.stream>>>(P);
             ctx->launches += 2;
