@@ -609,9 +609,13 @@ __device__ __forceinline__ void lift_window(const uint8_t* __restrict__ in, cons
 // stretch, *found receives the stream offset of the tag that starts that block.
 __device__ bool lift_walk(const uint8_t* __restrict__ in, const uint32_t n, const uint32_t expected, uint32_t& pos,
                           uint32_t& cum, const uint64_t stop, const uint32_t want, uint32_t* found, LiftScratch& sc,
-                          const uint32_t lane) {
+                          const uint32_t lane, uint32_t* budget = nullptr) {
     const uint8_t* wb = reinterpret_cast<const uint8_t*>(sc.words);
     while (pos < n && pos < stop) {
+        if (budget) {  // a caller that only wants short chains: give up after so many windows
+            if (*budget == 0) return false;
+            --*budget;
+        }
         const uint32_t wbase = pos & ~(kLiftWin - 1);
         lift_window(in, n, wbase, sc.N, sc.S, sc.words, lane);
         const uint32_t e = pos - wbase;
@@ -656,10 +660,15 @@ struct SegScanParams {
     uint32_t seg_cap;         // capacity of seg_tab in segments
 };
 
-// K0: which streams are scanned, and how many segments each has.
-__global__ void snappy_seg_count_kernel(SegScanParams Q) {
+// K0: one warp per large-slot stream.  Reads the preamble and tries the chain window by window with a small budget:
+// a stream of few, long elements (incompressible data is one 64 KiB literal per block) is finished here, boundaries
+// included, and takes no part in the segment pass, whose cost is per stream byte.  The others get their segment count.
+
+__global__ void __launch_bounds__(256) snappy_seg_count_kernel(SegScanParams Q) {
+    __shared__ LiftScratch scratch[8];
     const DecompressParams& P = Q.D;
-    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const uint32_t w = blockIdx.x * (blockDim.x >> 5) + wib;
     if (w >= P.n_list) return;
     const uint32_t m = P.list ? P.list[w] : w;
     const uint32_t cap = P.out_cap[m];
@@ -676,15 +685,36 @@ __global__ void snappy_seg_count_kernel(SegScanParams Q) {
             st = B2C_TOO_SMALL;
             mode = kModeDone;
         } else if (expected > kFragBytes) {
-            cnt = (n + kSegBytes - 1) / kSegBytes;
+            const uint32_t f0 = P.out_frag_first[m];
+            const uint32_t nblk = (expected + kFragBytes - 1) / kFragBytes;
+            if (lane == 0) P.blk_ip[f0] = k;
+            uint32_t pos = k, cum = 0, budget = n / 32768 + 8;  // enough for one element (and one boundary) per 64 KiB of stream
+            bool ok = true;
+            for (uint32_t nb = 1; ok && nb < nblk; nb++) {
+                uint32_t found = 0xffffffffu;
+                ok = lift_walk(in, n, expected, pos, cum, ~0ull, nb * kFragBytes, &found, scratch[wib], lane, &budget) &&
+                     found != 0xffffffffu;
+                if (ok && lane == 0) {
+                    P.blk_ip[f0 + nb] = found;
+                    Q.bnd[f0 + nb] = make_uint2(found, nb * kFragBytes);  // the boundary kernel will find it where it is
+                }
+            }
+            if (ok) ok = lift_walk(in, n, expected, pos, cum, ~0ull, 0u, nullptr, scratch[wib], lane, &budget);
+            if (ok && pos == n && cum == expected) {
+                mode = kModeBlocks;  // done: status below
+            } else if (budget == 0) {
+                cnt = (n + kSegBytes - 1) / kSegBytes;  // a long chain: the segment pass takes it
+            }                                           // else irregular: the whole-stream decoder decides
         }
     }
-    Q.seg_cnt[w] = cnt;
-    P.mode[m] = mode;  // scanned streams: upgraded to kModeBlocks by the chain kernel
-    P.ulen_tmp[m] = expected;
-    if (mode == kModeDone) {
-        P.status[m] = st;
-        if (P.ulen) P.ulen[m] = expected;
+    if (lane == 0) {
+        Q.seg_cnt[w] = cnt;
+        P.mode[m] = mode;  // streams in the segment pass: upgraded to kModeBlocks by the chain kernel
+        P.ulen_tmp[m] = expected;
+        if (mode != kModeWhole) {
+            P.status[m] = st;
+            if (P.ulen) P.ulen[m] = expected;
+        }
     }
 }
 
@@ -1050,7 +1080,7 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
                 void* tmp = seg_base + P.n_list + 1;
                 Q.seg_cnt = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(tmp) + scan_tmp);
                 Q.seg_cap = (uint32_t)std::min<size_t>(seg_cap, 0xffffffffu);
-                snappy_seg_count_kernel<<<(P.n_list + 255) / 256, 256, 0, lane.stream>>>(Q);
+                snappy_seg_count_kernel<<<sblocks, 256, 0, lane.stream>>>(Q);
                 ctx->launches++;
                 if ((rc = launch_scan_u32_u64(ctx, lane, Q.seg_cnt, P.n_list, seg_base, tmp))) return rc;
                 const int tab_smem = (int)(2 * kSegWins * kLiftWin * 4 + 8 * 72 * 4);

@@ -591,6 +591,7 @@ def test_e2e_zero_copy_gather_from_pinned_blocks(codec, cpu):
     {"B2C_SMALL_KERNELS": "0"},                            # warp kernels for small bodies too
     {"B2C_GTAB_WPS": "0", "B2C_BATCH_DECODE": "0"},        # shared-memory tables; one tag per step
     {"B2C_BATCH_DECODE_SMALL": "1", "B2C_RING_DECODE": "1", "B2C_BLOCK_DECODE": "0"},
+    {"B2C_LIFT_SCAN": "0"},                                # tag-by-tag block-boundary scan
     {"B2C_ASYNC_GATHER": "0", "B2C_NT_GATHER": "0", "B2C_SLAB_MB": "1", "B2C_HOST_THREADS": "3"},
 ])
 def test_alternate_kernel_paths_agree(cpu, env):
