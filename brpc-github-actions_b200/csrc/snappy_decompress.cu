@@ -139,11 +139,16 @@ __device__ int decode_message_warp(const uint8_t* __restrict__ in, const uint32_
 //      run yet (back-references inside the batch resolve in shared memory / L1).
 // ---------------------------------------------------------------------------
 constexpr uint32_t kWin = 256;
+constexpr uint32_t kStop = 0xFFFFu;     // no further tag of this batch from here
+constexpr uint32_t kScratchSlot = 3072;  // shared memory per warp for BatchScratch
 struct BatchScratch {
     uint32_t win32[kWin / 4 + 4];  // stream bytes [wbase, wbase + 256) + 16 bytes of padding
-    uint16_t jmp[kWin];            // next tag position (window-relative, saturated) if a tag starts here
+    // jmp[k][p]: where the chain stands 2^k tags after a tag at p (window-relative), kStop once it meets a tag the
+    // batch cannot take: one that is not fully inside the window, lies past the stream's end, or is a literal of more
+    // than 1 KiB (it gets a batch of its own)
+    uint16_t jmp[5][kWin];
 };
-static_assert(sizeof(BatchScratch) <= 1024, "BatchScratch must fit its 1 KiB slot");
+static_assert(sizeof(BatchScratch) <= kScratchSlot, "BatchScratch must fit its slot");
 
 __device__ __forceinline__ uint64_t warp_incl_scan_u64(uint64_t v, uint32_t lane) {
 #pragma unroll
@@ -294,27 +299,32 @@ __device__ int decode_message_batched(const uint8_t* __restrict__ in, const uint
                     L = kind == 1 ? 2 : kind == 2 ? 3 : 5;
                 }
                 const uint64_t to = p + L;
-                sc.jmp[p] = (uint16_t)(to > 0xFFFFu ? 0xFFFFu : to);
+                const bool takes = p + 5 <= kWin && wbase + p < n && L <= 1030u;
+                sc.jmp[0][p] = (uint16_t)(takes ? to : kStop);
             }
             __syncwarp();
-        }
-        // ---- 2. follow the chain: tag t of this batch goes to lane t
-        uint32_t cur = ip - wbase, my_pos = 0, count = 0;
-        for (uint32_t t = 0; t < 32; t++) {
-            if (cur + 5 > kWin) break;       // tag might not be fully inside the window: next batch reloads
-            if (wbase + cur >= n) break;     // end of stream (or an overrun the owning lane reports)
-            const uint32_t nxt = sc.jmp[cur];
-            if (nxt - cur > 1030u) {         // a literal of more than 1 KiB: it gets a batch of its own,
-                if (t == 0) {                // so that one batch never outgrows the output ring
-                    if (lane == 0) my_pos = cur;
-                    count = 1;
+#pragma unroll 1
+            for (uint32_t k = 1; k < 5; k++) {  // square the jump table: 2, 4, 8, 16 tags ahead
+#pragma unroll
+                for (uint32_t j = 0; j < 8; j++) {
+                    const uint32_t p = lane * 8 + j;
+                    const uint32_t q = sc.jmp[k - 1][p];
+                    sc.jmp[k][p] = (uint16_t)(q < kWin ? sc.jmp[k - 1][q] : kStop);
                 }
-                break;
+                __syncwarp();
             }
-            if (lane == t) my_pos = cur;
-            count = t + 1;
-            cur = nxt;
         }
+        // ---- 2. follow the chain: tag t of this batch goes to lane t, which composes the powers of the jump table
+        //         that make up t (at most 5 dependent shared-memory reads instead of a 32-step walk)
+        uint32_t my_pos = ip - wbase;
+#pragma unroll
+        for (uint32_t k = 0; k < 5; k++)
+            if (((lane >> k) & 1u) && my_pos < kWin) my_pos = sc.jmp[k][my_pos];
+        // the batch takes tag 0 always (the window was refilled so that it fits; a long literal is taken alone) and tag t
+        // while the chain has not met a tag it cannot take
+        const bool take = lane == 0 || (my_pos < kWin && sc.jmp[0][my_pos] != kStop);
+        const uint32_t taken = __ballot_sync(kFull, take);
+        const uint32_t count = taken == kFull ? 32u : (uint32_t)__ffs(~taken) - 1;
         // ---- 3. decode in parallel
         const bool act = lane < count;
         uint32_t kind = 0, len = 0, offset = 0, lit_src = 0, adv = 0;
@@ -415,7 +425,21 @@ __device__ int decode_message_batched(const uint8_t* __restrict__ in, const uint
                 const uint32_t frontier = __shfl_sync(kFull, out_pos, first);
                 const bool ready = ((pending >> lane) & 1u) && (lane == first || src_end <= frontier);
                 if (ready) {
-                    if (offset >= len) {
+                    if (offset >= 4) {
+                        // the 4 source bytes of a round precede its first destination byte (also when the copy overlaps
+                        // itself: IncrementalCopy reads what it wrote `offset` bytes ago, snappy.cc:98-103), so they are
+                        // loaded together: one memory round trip per 4 bytes instead of per byte
+                        uint32_t i = 0;
+                        for (; i + 4 <= len; i += 4) {
+                            const uint8_t b0 = out.ld(src_pos + i), b1 = out.ld(src_pos + i + 1), b2 = out.ld(src_pos + i + 2),
+                                          b3 = out.ld(src_pos + i + 3);
+                            out.st(out_pos + i, b0);
+                            out.st(out_pos + i + 1, b1);
+                            out.st(out_pos + i + 2, b2);
+                            out.st(out_pos + i + 3, b3);
+                        }
+                        for (; i < len; i++) out.st(out_pos + i, out.ld(src_pos + i));
+                    } else if (offset >= len) {
                         for (uint32_t i = 0; i < len; i++) out.st(out_pos + i, out.ld(src_pos + i));
                     } else {  // pattern of `offset` bytes repeated, as IncrementalCopy (snappy.cc:98-103)
                         uint32_t j = 0;
@@ -488,7 +512,7 @@ __global__ void __launch_bounds__(256) snappy_scan_kernel(DecompressParams P) {
         const uint32_t f0 = P.out_frag_first[m];
         ScanOut so{P.blk_ip + f0, (expected + kFragBytes - 1) / kFragBytes, 0u};
         if (lane == 0) P.blk_ip[f0] = k;
-        BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * 1024);
+        BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * kScratchSlot);
         st = decode_message_batched(in, n, k, so, expected, lane, sc);
         if (st == B2C_OK) mode = __any_sync(kFull, so.bad) ? kModeWhole : kModeBlocks;
     }
@@ -851,7 +875,7 @@ __global__ void __launch_bounds__(256) snappy_decompress_blocks_kernel(Decompres
     const uint32_t ip0 = P.blk_ip[f];
     const uint32_t ip1 = begin + kFragBytes < expected ? P.blk_ip[f + 1] : P.in_len[m];
     LinearOut lo{P.out + P.out_off[m] + begin};
-    BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * 1024);
+    BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * kScratchSlot);
     const int st = decode_message_batched(P.in + P.in_off[m], ip1, ip0, lo, block_len, lane, sc);
     // a block that does not decode on its own: the stream is corrupt, or merely not splittable (a copy that reaches
     // back across the block's start); the whole-stream decoder, launched next, redoes it and decides
@@ -879,7 +903,7 @@ __global__ void __launch_bounds__(256) snappy_decompress_kernel(DecompressParams
     } else if (expected > cap) {
         st = B2C_TOO_SMALL;
     } else if (P.smem_per_warp && expected <= P.smem_per_warp) {
-        uint8_t* sbuf = smem_raw + (size_t)wib * (P.smem_per_warp + 1024);
+        uint8_t* sbuf = smem_raw + (size_t)wib * (P.smem_per_warp + kScratchSlot);
         BatchScratch& sc = *reinterpret_cast<BatchScratch*>(sbuf + P.smem_per_warp);
         LinearOut lo{sbuf};
         st = P.batched ? decode_message_batched(in, n, k, lo, expected, lane, sc)
@@ -912,9 +936,9 @@ __global__ void __launch_bounds__(256) snappy_decompress_kernel(DecompressParams
             if (lane < expected - done) gout[done + lane] = sbuf[done + lane];
         }
     } else {
-        BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * (P.smem_per_warp + 1024) + P.smem_per_warp);
+        BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * (P.smem_per_warp + kScratchSlot) + P.smem_per_warp);
         if (P.ring) {
-            RingOut ro{smem_raw + (size_t)wib * (65536 + 1024), gout, 0u, 0u, 0u};
+            RingOut ro{smem_raw + (size_t)wib * (65536 + kScratchSlot), gout, 0u, 0u, 0u};
             BatchScratch& rsc = *reinterpret_cast<BatchScratch*>(ro.ring + 65536);
             st = decode_message_batched(in, n, k, ro, expected, lane, rsc);
         } else {
@@ -957,7 +981,7 @@ __global__ void __launch_bounds__(256) snappy_validate_kernel(const uint8_t* __r
     int st = B2C_CORRUPT;
     if (k) {
         ScanOut so{nullptr, 0u, 0u};
-        BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * 1024);
+        BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * kScratchSlot);
         st = decode_message_batched(src, n, k, so, expected, lane, sc);
     }
     if (lane == 0) {
@@ -980,7 +1004,7 @@ __global__ void snappy_verify_crc_kernel(const uint32_t* __restrict__ crc, const
 int launch_validate(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint32_t* d_ulen,
                     int32_t* d_status) {
     if (L.n == 0) return B2C_OK;
-    snappy_validate_kernel<<<(L.n + 7) / 8, 256, 8 * 1024, lane.stream>>>(d_in, L.d_off, L.d_len, L.n, d_ulen, d_status);
+    snappy_validate_kernel<<<(L.n + 7) / 8, 256, 8 * kScratchSlot, lane.stream>>>(d_in, L.d_off, L.d_len, L.n, d_ulen, d_status);
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
     return B2C_OK;
@@ -1091,19 +1115,19 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
                 snappy_seg_boundary_kernel<<<(P.n_blocks + 7) / 8, 256, 0, lane.stream>>>(Q);
                 ctx->launches += 2;  // + the chain kernel counted with the blocks kernel below
             } else {
-                snappy_scan_kernel<<<sblocks, 256, 8 * 1024, lane.stream>>>(P);
+                snappy_scan_kernel<<<sblocks, 256, 8 * kScratchSlot, lane.stream>>>(P);
             }
             const uint32_t bblocks = (P.n_blocks + 7) / 8;
-            snappy_decompress_blocks_kernel<<<bblocks, 256, 8 * 1024, lane.stream>>>(P);
+            snappy_decompress_blocks_kernel<<<bblocks, 256, 8 * kScratchSlot, lane.stream>>>(P);
             ctx->launches += 2;
             B2C_CUDA(ctx, cudaGetLastError());
         }
         P.ring = (c == 2 && ctx->batch_decode && ctx->ring_decode) ? 1u : 0u;
         uint32_t wpb = class_warps[c];
-        size_t smem = (size_t)wpb * (class_smem[c] + 1024);
+        size_t smem = (size_t)wpb * (class_smem[c] + kScratchSlot);
         if (P.ring) {
             wpb = 1;
-            smem = 65536 + 1024;
+            smem = 65536 + kScratchSlot;
             if (!ctx->ring_attr_done) {
                 B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_decompress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                    (int)smem));
