@@ -502,7 +502,10 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     b2c_ctx* ctx = new (std::nothrow) b2c_ctx();
     if (!ctx) return B2C_E_NOMEM;
     ctx->device = device;
-    if (const char* s = getenv("B2C_SLAB_MB")) ctx->slab_bytes = std::max<size_t>(1, (size_t)atol(s)) << 20;
+    if (const char* s = getenv("B2C_SLAB_MB")) {
+        ctx->slab_bytes = std::max<size_t>(1, (size_t)atol(s)) << 20;
+        ctx->slab_fixed = true;
+    }
     if (const char* s = getenv("B2C_HOST_THREADS")) ctx->host_threads = (unsigned)std::max(1L, atol(s));
     if (const char* s = getenv("B2C_TRACE")) ctx->trace = atoi(s) != 0;
     if (const char* s = getenv("B2C_BATCH_DECODE")) ctx->batch_decode = atoi(s) != 0;
@@ -858,7 +861,15 @@ int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, u
         part[t] = sum;
     });
     if (too_long) return set_err(ctx, B2C_E_ARG, "message longer than 4 GiB - 1", cudaSuccess);
-    const uint64_t target = ctx->slab_bytes;
+    // Slab size: ~32 MiB keeps gather, copies and kernels of different slabs overlapped; batches of large messages get
+    // up to 128 MiB, because a 64 KiB fragment occupies a warp for milliseconds and a 32 MiB slab holds only 512 of them
+    // (measured end to end, 32 -> 128 MiB: C5 10.4 -> 15.2, C4 8.3 -> 13.1 GB/s).  B2C_SLAB_MB fixes the size.
+    uint64_t target = ctx->slab_bytes;
+    if (!ctx->slab_fixed && n) {
+        uint64_t total = 0;
+        for (unsigned t = 0; t < used; t++) total += part[t];
+        target = std::min<uint64_t>(128ull << 20, std::max<uint64_t>(target, total / n * 8192));
+    }
     const uint32_t max_msgs = 1u << 18;
     if (!zc) {
         uint64_t base[65];

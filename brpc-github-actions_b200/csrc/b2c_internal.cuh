@@ -128,6 +128,7 @@ struct b2c_ctx {
     int small_lpw_compress = 4, small_lpw_decompress = 8;  // bodies per warp (B2C_SMALL_LPW_C / _D: 4, 8, 16, 32)
     // tunables (environment: B2C_SLAB_MB, B2C_HOST_THREADS, B2C_TRACE)
     size_t slab_bytes = 32u << 20;
+    bool slab_fixed = false;  // B2C_SLAB_MB given: no adaptation to the batch's message sizes
     unsigned host_threads = 0;
     bool trace = false;
     bool input_pinned = false;  // B2C_OPT_INPUT_PINNED: *_batch inputs are page-locked, gather them on the device
