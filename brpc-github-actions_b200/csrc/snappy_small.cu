@@ -1,20 +1,19 @@
 // snappy_small.cu — thread-per-message snappy kernels for bodies of at most 1 KiB
 // (BASELINE configs[1]: 2^20 x 1 KiB RPC bodies).
 //
-// The warp-per-fragment kernels (snappy_compress.cu / snappy_decompress.cu) spend a
-// whole warp's issue slots on one serial chain; ncu showed them issue-bound (88-92 %
-// issue-active, 25 k / 15 k warp-instructions per 1 KiB body).  For small bodies the
-// better shape is ONE LANE PER BODY: every lane runs the reference's scalar algorithm
-// (CompressFragment, snappy.cc:329-453 / DecompressAllTags, snappy.cc:716-787) on its
-// own body, so one warp instruction advances 32 bodies.
-//
-// Shared memory is laid out so that lanes never collide on a bank:
-//   compress:   u16 hash table [entry][lane] (64 KiB per warp) + the input as
-//               32-bit words [word][lane] (33 KiB per warp); both CTAs of an SM = 64 bodies in flight;
-//   decompress: the output as words [word][lane] (32 KiB per warp, 6 warps per SM),
-//               so back-references resolve at shared-memory latency.
-// Output bytes of the compressor are funnelled through a 64-bit register and stored
-// as aligned words.
+// A warp that cooperates on one body spends 32 lanes' issue slots on one serial chain.  For
+// small bodies the better shape is ONE LANE PER BODY: every lane runs the reference's scalar
+// algorithm (CompressFragment, snappy.cc:329-453 / DecompressAllTags, snappy.cc:716-787) on its
+// own body, a few bodies per warp (LPW), all state in shared memory:
+//   compress:   u16 hash table [entry][slot] (64 KiB per CTA of 32 bodies) + each body in a
+//               contiguous slot fetched by one TMA bulk copy (33 KiB per CTA); two CTAs per SM =
+//               64 bodies in flight.  Default: snappy_compress_small2_kernel — lanes FIND matches
+//               and record them, warps ENCODE the records (see the comment above that kernel);
+//               snappy_compress_small_kernel (B2C_SMALL2=0) encodes from the lane's own loop
+//               through a 64-bit register funnel;
+//   decompress: each stream's output in a contiguous byte-addressed slot (33 KiB per CTA, 6 CTAs
+//               per SM), so back-references resolve at shared-memory latency; flushed with
+//               coalesced 16-byte stores.
 #include <algorithm>
 
 #include "snappy_emit.cuh"
