@@ -260,6 +260,26 @@ def run_ours(args, rank, local_rank, world):
         ms = brpc_b200.sharding.max_over_ranks(ms, device="cuda")  # device time, max over ranks
         dist.barrier()
 
+    # ---- the fused receiver op on device-resident data (decompress + CRC32C of the output compared
+    #      with the stored masked CRC, snappy-framing semantics), timed on its own ----
+    verify_ms = None
+    if args.workload == "c5":
+        crc_host = codec.d2h(d_crc, 4 * n_msgs, np.uint32)
+        masked = ((crc_host >> np.uint32(15)) | (crc_host << np.uint32(17))) + np.uint32(0xa282ead8)  # crc32c.h:44-48
+        d_masked = codec.to_device(masked.astype(np.uint32))
+        codec.decompress_verify_dev(clay, d_comp, lay, d_back, d_masked, d_st)
+        codec.sync()
+        assert (codec.d2h(d_st, 4 * n_msgs, np.int32) == 0).all(), "decompress+verify reported errors"
+        v0, v1 = codec.event(), codec.event()
+        v0.record()
+        for _ in range(args.steps):
+            codec.decompress_verify_dev(clay, d_comp, lay, d_back, d_masked, d_st)
+        v1.record()
+        codec.sync()
+        verify_ms = v1.elapsed_ms_since(v0) / args.steps
+        if dist is not None:
+            verify_ms = brpc_b200.sharding.max_over_ranks(verify_ms, device="cuda")
+
     # ---- end to end through the host-buffer ABI (iovec block lists, PCIe inside) ----
     rng = np.random.default_rng(2024 + rank)
     if args.workload == "c2":  # 1-2 blocks per body at a seeded random cut
@@ -399,6 +419,8 @@ def run_ours(args, rank, local_rank, world):
                                  "not HBM bound (see DESIGN.md)"},
             "ops": per_op, "compression_ratio": comp_bytes / payload,
             "messages_per_s": n_msgs * world * args.steps / (ms * 1e-3),
+            **({"decompress_verify": {"ms_per_step": verify_ms, "payload_gbs": payload * world / (verify_ms * 1e-3) / 1e9}}
+               if verify_ms else {}),
             "cpu_baseline": {"value": cpu_gbs, "unit": "GB/s", "cores": cores, "kind": cpu.kind,
                              "sample": f"full batch ({n_msgs} bodies, {payload} B) x {reps} passes of crc32c + RawCompress + "
                                        f"RawUncompress, static split over {cores} threads"},
