@@ -19,6 +19,7 @@
 #include <thread>
 
 #include "b200_aggregator.hpp"
+#include "b200_block_pool.hpp"
 #include "b200_codec.hpp"
 #include "b200_framing.hpp"
 #include "b2o.h"
@@ -357,6 +358,98 @@ static void fused_and_iovec_calls() {
     for (size_t i = 0; i < bodies.size(); i++) CHECK(ok[i] && sinks[i] == bodies[i]);
 }
 
+// ---- page-locked IOBuf block pool (the blockmem_allocate / blockmem_deallocate hook) ----
+static void block_pool() {
+    b2c_ctx* ctx = b200::Context::local().get();
+    {
+        b200::PinnedBlockPool pool(ctx, 8192, 1u << 20);  // 128 blocks per region
+        std::vector<void*> blocks;
+        for (int i = 0; i < 300; i++) blocks.push_back(pool.Allocate(8192));
+        std::vector<void*> sorted = blocks;
+        std::sort(sorted.begin(), sorted.end());
+        CHECK(std::adjacent_find(sorted.begin(), sorted.end()) == sorted.end());
+        for (void* b : blocks) CHECK(b && (reinterpret_cast<uintptr_t>(b) & 63) == 0 && pool.Owns(b));
+        CHECK(pool.stats().regions == 3);
+        // bodies laid into blocks the way IOBuf does it: a 32-byte Block header, then up to 8160 payload bytes
+        std::vector<std::string> bodies;
+        std::vector<BlockList> in;
+        size_t next_block = 0;
+        for (int i = 0; i < 120; i++) {
+            std::string s((size_t)(i * 197 % 20000), '\0');
+            b2o_corpus_fill(B2O_WORDS, 500 + i, reinterpret_cast<uint8_t*>(&s[0]), s.size());
+            BlockList bl;
+            for (size_t at = 0; at < s.size() || (at == 0 && bl.empty()); at += 8160) {
+                if (next_block == blocks.size()) blocks.push_back(pool.Allocate(8192));
+                char* blk = static_cast<char*>(blocks[next_block++]);
+                const size_t c = std::min<size_t>(8160, s.size() - at);
+                memcpy(blk + 32, s.data() + at, c);
+                bl.push_back({blk + 32, c});
+                if (s.empty()) break;
+            }
+            bodies.push_back(s);
+            in.push_back(bl);
+        }
+        // page-locked blocks: the device gathers them itself
+        CHECK(b2c_ctx_set_option(ctx, B2C_OPT_INPUT_PINNED, 1) == B2C_OK);
+        std::vector<std::string> z;
+        std::vector<uint32_t> crc;
+        b200::policy::SnappyCompressBatch(in, &z);
+        b200::policy::Crc32cBatch(in, nullptr, &crc);
+        CHECK(b2c_ctx_set_option(ctx, B2C_OPT_INPUT_PINNED, 0) == B2C_OK);
+        for (size_t i = 0; i < bodies.size(); i++) {
+            CHECK(z[i] == oracle_compress(bodies[i]));
+            CHECK(crc[i] == b2o_crc32c_value(reinterpret_cast<const uint8_t*>(bodies[i].data()), bodies[i].size()));
+        }
+        // recycling: everything back, then out again without new regions
+        const size_t regions = pool.stats().regions;
+        for (void* b : blocks) pool.Deallocate(b);
+        const size_t nblocks = blocks.size();
+        blocks.clear();
+        for (size_t i = 0; i < nblocks; i++) blocks.push_back(pool.Allocate(100));
+        CHECK(pool.stats().regions == regions);
+        for (void* b : blocks) pool.Deallocate(b);
+        // oversize requests get their own page-locked allocation
+        void* big = pool.Allocate(100000);
+        CHECK(big && pool.Owns(big) && pool.stats().big_out == 1);
+        pool.Deallocate(big);
+        CHECK(pool.stats().big_out == 0);
+        // many threads
+        std::vector<std::thread> th;
+        for (int t = 0; t < 4; t++)
+            th.emplace_back([&pool, t] {
+                std::vector<void*> mine;
+                unsigned x = 12345u + t;
+                for (int i = 0; i < 20000; i++) {
+                    x = x * 1664525u + 1013904223u;
+                    if ((x >> 16) % 3 != 0 || mine.empty()) {
+                        void* b = pool.Allocate(8192);
+                        *static_cast<unsigned*>(b) = x;
+                        mine.push_back(b);
+                    } else {
+                        pool.Deallocate(mine.back());
+                        mine.pop_back();
+                    }
+                    if (mine.size() > 200) {
+                        for (void* b : mine) pool.Deallocate(b);
+                        mine.clear();
+                    }
+                }
+                for (void* b : mine) pool.Deallocate(b);
+            });
+        for (auto& x : th) x.join();
+        const b200::PinnedBlockPool::Stats st = pool.stats();
+        CHECK(st.allocs == st.frees);
+        printf("block pool: %zu regions (%zu KiB page-locked), %llu allocations\n", st.regions, st.region_bytes >> 10,
+               (unsigned long long)st.allocs);
+    }
+    // the process-wide hook pair, with the signatures of butil::iobuf::blockmem_allocate / blockmem_deallocate
+    void* (*alloc_hook)(size_t) = b200::PinnedBlockPool::blockmem_allocate;
+    void (*free_hook)(void*) = b200::PinnedBlockPool::blockmem_deallocate;
+    void* b = alloc_hook(8192);
+    CHECK(b && b200::PinnedBlockPool::global().Owns(b));
+    free_hook(b);
+}
+
 int main() {
     crc_standard_results();
     crc_values_extend_mask();
@@ -367,6 +460,7 @@ int main() {
     batch_calls();
     framing_format();
     fused_and_iovec_calls();
+    block_pool();
     aggregator_many_threads();
     if (g_fail) {
         fprintf(stderr, "%d check(s) failed\n", g_fail);

@@ -25,7 +25,7 @@ def _build():
     cmd = [cxx, "-std=c++17", "-O1", "-Wall", "-I", os.path.join(ROOT, "include"), "-I", os.path.join(PKG, "host"),
            "-I", os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests", "cpp", "test_host_api.cpp"),
            os.path.join(PKG, "host", "b200_codec.cpp"), os.path.join(PKG, "host", "b200_aggregator.cpp"),
-           os.path.join(PKG, "host", "b200_framing.cpp"), "-L", PKG, "-lb2c", "-L", os.path.join(ROOT, "oracle"),
+           os.path.join(PKG, "host", "b200_framing.cpp"), os.path.join(PKG, "host", "b200_block_pool.cpp"), "-L", PKG, "-lb2c", "-L", os.path.join(ROOT, "oracle"),
            "-lb2oracle", f"-Wl,-rpath,{PKG}", f"-Wl,-rpath,{os.path.join(ROOT, 'oracle')}", "-lpthread", "-o", BIN]
     subprocess.run(cmd, check=True)
     return BIN
