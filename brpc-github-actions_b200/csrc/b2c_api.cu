@@ -519,6 +519,12 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     if (const char* s = getenv("B2C_SMALL_LPW_C")) ctx->small_lpw_compress = atoi(s);
     if (const char* s = getenv("B2C_WINDOW")) ctx->window_mask = atoi(s);
     if (const char* s = getenv("B2C_WINDOW_STAGE")) ctx->window_stage = atoi(s) != 0;
+    if (const char* s = getenv("B2C_WINDOW_SMEM64")) ctx->window_smem64 = atoi(s) != 0;
+    if (const char* s = getenv("B2C_LOCKSTEP")) ctx->small_lockstep = atoi(s) != 0;
+    if (const char* s = getenv("B2C_LOCKSTEP_LPW")) {
+        const int v = atoi(s);
+        if (v == 4 || v == 8 || v == 16 || v == 32) ctx->lockstep_lpw = v;
+    }
     if (const char* s = getenv("B2C_WINDOW_WPS")) ctx->window_warps_per_sm = atoi(s);
     if (const char* s = getenv("B2C_ASYNC_GATHER")) ctx->async_gather = atoi(s) != 0;
     if (const char* s = getenv("B2C_SMALL2")) ctx->small_two_phase = atoi(s) != 0;
@@ -536,6 +542,7 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
         if ((rc = crc_tables_init(ctx))) break;
         rc = small_kernels_configure(ctx);
         if (!rc) rc = window_kernels_configure(ctx);
+        if (!rc) rc = lockstep_kernels_configure(ctx);
     } while (0);
     if (rc != B2C_OK) {
         fprintf(stderr, "b2c_ctx_create failed: %s\n", ctx->err.c_str());

@@ -143,6 +143,9 @@ struct b2c_ctx {
     bool small_two_phase = true;  // B2C_SMALL2=0 restores the one-phase kernel; <=1 KiB bodies compress as find (lane per body) then encode (warp per body)
     int window_warps_per_sm = 40;  // B2C_WINDOW_WPS: resident warps per SM of the orbit kernel on 64 KiB fragments (tables in HBM/L2; B2C_GTAB_WPS=0 keeps them in shared memory)
     bool window_stage = true;  // B2C_WINDOW_STAGE=0: the window compressor reads <=4 KiB fragments from HBM instead of staging them
+    bool window_smem64 = false;  // B2C_WINDOW_SMEM64=1: 64 KiB fragments keep table + TMA-staged fragment in shared memory (one warp per CTA, 2 CTAs per SM); measured 7.6x slower than HBM/L2 tables with 40 warps per SM
+    bool small_lockstep = true;  // B2C_LOCKSTEP=0: bodies <= 1 KiB compress with the lane-per-body loops of snappy_small.cu instead of the lock-step state machines
+    int lockstep_lpw = 8;        // B2C_LOCKSTEP_LPW: bodies per warp of the lock-step compressor (4, 8, 16, 32)
     int window_mask = 6;    // B2C_WINDOW: bit c set = fragment class c (0: <=1 KiB, 1: <=4 KiB, 2: <=64 KiB) compresses with the orbit kernel (snappy_window.cu)
 };
 
@@ -194,6 +197,10 @@ int launch_decompress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& in, cons
 // host_gather.cpp: one message's blocks concatenated into staging (non-temporal whole-line stores when `stream`)
 void gather_message(uint8_t* dst, const b2c_iovec* segs, uint32_t nseg, uint64_t total, bool stream);
 void gather_fence();
+// lock-step state machines, 32 bodies <= 1 KiB per warp (snappy_lockstep.cu)
+int lockstep_kernels_configure(b2c_ctx* ctx);
+int launch_compress_lockstep(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint8_t* scratch,
+                             uint32_t* d_frag_clen);
 // window-parallel warp-per-fragment compressor (snappy_window.cu); c = fragment class 0..2
 int window_kernels_configure(b2c_ctx* ctx);
 int launch_compress_window(b2c_ctx* ctx, Lane& lane, const LayoutView& L, int c, const uint8_t* d_in, uint8_t* scratch,

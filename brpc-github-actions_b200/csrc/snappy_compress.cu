@@ -460,6 +460,10 @@ int launch_compress(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t
             if ((rc = launch_compress_window(ctx, lane, L, c, d_in, scratch, d_frag_clen))) return rc;
             continue;
         }
+        if (c == 0 && ctx->small_kernels && ctx->small_lockstep) {  // bodies <= 1 KiB: 32 per warp in lock-step
+            if ((rc = launch_compress_lockstep(ctx, lane, L, d_in, scratch, d_frag_clen))) return rc;
+            continue;
+        }
         if (c == 0 && ctx->small_kernels) {  // bodies <= 1 KiB: one lane per fragment
             if ((rc = launch_compress_small(ctx, lane, L, d_in, scratch, d_frag_clen))) return rc;
             continue;

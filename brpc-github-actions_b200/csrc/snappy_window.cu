@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(256) snappy_compress_orbit_kernel(WindowParams
 
 int window_kernels_configure(b2c_ctx* ctx) {
     B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_compress_orbit_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       64 * 1024));
+                                       100 * 1024));
     B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_compress_orbit_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        64 * 1024));
     return B2C_OK;
@@ -323,7 +323,11 @@ int launch_compress_window(b2c_ctx* ctx, Lane& lane, const LayoutView& L, int c,
     P.gtab = nullptr;
     uint32_t wpb = warps[c];
     uint32_t resident;  // CTAs per SM the launch is sized for
-    if (c == 2 && ctx->gtab_warps_per_sm > 0) {  // 64 KiB fragments: tables in HBM/L2, many resident warps
+    if (c == 2 && ctx->window_smem64) {  // 64 KiB fragments: table AND TMA-staged fragment in shared memory, 2 warps/SM
+        wpb = 1;
+        resident = 2;
+        P.in_stride = 65536 + 32;
+    } else if (c == 2 && ctx->gtab_warps_per_sm > 0) {  // 64 KiB fragments: tables in HBM/L2, many resident warps
         // A round is a chain of 2-3 L2 round trips, so throughput follows the number of resident warps: measured on
         // C5/words 68.9 / 38.9 / 31.6 / 26.9 / 23.7 ms per GiB at 8 / 16 / 24 / 32 / 40 warps per SM (40 = the
         // register limit; tables in shared memory allow 6: 80 ms).
