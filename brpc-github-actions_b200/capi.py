@@ -269,6 +269,7 @@ class Codec:
 
     # ---- plumbing ----------------------------------------------------------
     OPT_INPUT_PINNED = 1
+    OPT_HOST_THREADS = 2
 
     def set_option(self, option: int, value: int):
         self._check(self.lib.b2c_ctx_set_option(self.ctx, option, value))

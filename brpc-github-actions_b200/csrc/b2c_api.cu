@@ -116,7 +116,7 @@ public:
             fn(0, 1);
             return;
         }
-        std::lock_guard<std::mutex> serial(run_mu_);  // one parallel section at a time, process-wide
+        std::lock_guard<std::mutex> serial(run_mu_);  // one parallel section at a time on this pool
         {
             std::lock_guard<std::mutex> g(mu_);
             fn_ = &fn;
@@ -203,21 +203,21 @@ private:
     bool stop_ = false;
 };
 
-static std::mutex g_pool_mu;
-static HostPool* g_pool = nullptr;  // one per process, sized on first use
+// One pool per ctx (a ctx is used by one thread at a time), created on the first *_batch call.  Default size:
+// the host's cores divided among the ranks of this node (torchrun's LOCAL_WORLD_SIZE), between 2 and 16 --
+// eight ranks that each start 16 gather threads on a 32-core host only take turns on the cores.
+// B2C_OPT_HOST_THREADS / B2C_HOST_THREADS fix it.
+static unsigned default_host_threads() {
+    unsigned hw = std::thread::hardware_concurrency();
+    if (!hw) hw = 4;
+    unsigned ranks = 1;
+    if (const char* s = getenv("LOCAL_WORLD_SIZE")) ranks = (unsigned)std::max(1L, atol(s));
+    return std::min(16u, std::max(2u, hw / ranks));
+}
 
 static HostPool& pool(b2c_ctx* ctx) {
-    std::lock_guard<std::mutex> g(g_pool_mu);
-    if (!g_pool) {
-        unsigned n = ctx->host_threads;
-        if (!n) {
-            n = std::thread::hardware_concurrency();
-            if (!n) n = 4;
-            n = std::min(n, 16u);
-        }
-        g_pool = new HostPool(n);
-    }
-    return *g_pool;
+    if (!ctx->host_pool) ctx->host_pool = new HostPool(ctx->host_threads ? ctx->host_threads : default_host_threads());
+    return *static_cast<HostPool*>(ctx->host_pool);
 }
 
 static unsigned threads_for(uint64_t bytes) { return (unsigned)std::min<uint64_t>(64, bytes / (1u << 20) + 1); }
@@ -556,6 +556,8 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
 void b2c_ctx_destroy(b2c_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
+    delete static_cast<HostPool*>(ctx->host_pool);
+    ctx->host_pool = nullptr;
     lane_destroy(ctx->main);
     for (auto& l : ctx->pipe) lane_destroy(l);
     if (ctx->d_crc_tabA) cudaFree(ctx->d_crc_tabA);
@@ -574,6 +576,14 @@ int b2c_ctx_set_option(b2c_ctx* ctx, int option, int value) {
     if (!ctx) return B2C_E_ARG;
     switch (option) {
         case B2C_OPT_INPUT_PINNED: ctx->input_pinned = value != 0; return B2C_OK;
+        case B2C_OPT_HOST_THREADS:
+            if (value < 0 || value > 256) return B2C_E_ARG;
+            if (ctx->host_pool && (unsigned)value != ctx->host_threads) {  // takes effect from the next *_batch call
+                delete static_cast<HostPool*>(ctx->host_pool);
+                ctx->host_pool = nullptr;
+            }
+            ctx->host_threads = (unsigned)value;
+            return B2C_OK;
         default: return set_err(ctx, B2C_E_ARG, "unknown option", cudaSuccess);
     }
 }

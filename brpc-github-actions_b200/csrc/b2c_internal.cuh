@@ -129,7 +129,8 @@ struct b2c_ctx {
     // tunables (environment: B2C_SLAB_MB, B2C_HOST_THREADS, B2C_TRACE)
     size_t slab_bytes = 32u << 20;
     bool slab_fixed = false;  // B2C_SLAB_MB given: no adaptation to the batch's message sizes
-    unsigned host_threads = 0;
+    unsigned host_threads = 0;  // 0: cores / ranks on this node, 2..16 (B2C_OPT_HOST_THREADS, B2C_HOST_THREADS)
+    void* host_pool = nullptr;  // this ctx's gather / copy-out threads (HostPool, b2c_api.cu), created on first use
     bool trace = false;
     bool input_pinned = false;  // B2C_OPT_INPUT_PINNED: *_batch inputs are page-locked, gather them on the device
     bool ring_decode = false;        // B2C_RING_DECODE=1: unsplittable large slots decode through a 64 KiB smem ring
@@ -144,7 +145,7 @@ struct b2c_ctx {
     int window_warps_per_sm = 40;  // B2C_WINDOW_WPS: resident warps per SM of the orbit kernel on 64 KiB fragments (tables in HBM/L2; B2C_GTAB_WPS=0 keeps them in shared memory)
     bool window_stage = true;  // B2C_WINDOW_STAGE=0: the window compressor reads <=4 KiB fragments from HBM instead of staging them
     bool window_smem64 = false;  // B2C_WINDOW_SMEM64=1: 64 KiB fragments keep table + TMA-staged fragment in shared memory (one warp per CTA, 2 CTAs per SM); measured 7.6x slower than HBM/L2 tables with 40 warps per SM
-    bool small_lockstep = true;  // B2C_LOCKSTEP=0: bodies <= 1 KiB compress with the lane-per-body loops of snappy_small.cu instead of the lock-step state machines
+    bool small_lockstep = false;  // B2C_LOCKSTEP=1: bodies <= 1 KiB compress with the branch-free lock-step state machines of snappy_lockstep.cu (measured slower than the lane-per-body loops of snappy_small.cu: 15.5 vs 11.0 ms per GiB of 1 KiB `words` bodies)
     int lockstep_lpw = 8;        // B2C_LOCKSTEP_LPW: bodies per warp of the lock-step compressor (4, 8, 16, 32)
     int window_mask = 6;    // B2C_WINDOW: bit c set = fragment class c (0: <=1 KiB, 1: <=4 KiB, 2: <=64 KiB) compresses with the orbit kernel (snappy_window.cu)
 };

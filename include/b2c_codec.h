@@ -80,6 +80,12 @@ int b2c_ctx_sync(b2c_ctx* ctx);
  *     only the block list is copied and a kernel pulls the blocks over PCIe itself.  Passing a
  *     pageable block with this option set is a fatal device fault. */
 #define B2C_OPT_INPUT_PINNED 1
+/*   B2C_OPT_HOST_THREADS (default 0 = automatic): threads of this ctx's host pool, which gathers IOBuf
+ *     blocks into pinned staging and copies results out for the *_batch entry points.  Automatic is
+ *     the host's cores divided by the ranks on this node (LOCAL_WORLD_SIZE when set), at least 2 and
+ *     at most 16.  Every ctx owns its pool, so ctxs used from different threads (a sender and a
+ *     receiver, or one per device) never wait for each other; give each its share of the cores. */
+#define B2C_OPT_HOST_THREADS 2
 int b2c_ctx_set_option(b2c_ctx* ctx, int option, int value);
 /* Number of kernels this ctx has launched so far (bench.py's gpu_launches). */
 uint64_t b2c_ctx_launch_count(const b2c_ctx* ctx);

@@ -91,6 +91,10 @@ double b2o_batch_uncompress(const uint8_t* data, const uint64_t* off,
                             const uint32_t* len, uint32_t n, uint8_t* out,
                             const uint64_t* out_off, const uint32_t* out_cap,
                             uint32_t* ulen, int32_t* ok, int threads);
+/* message-by-message memcmp of two arenas; returns how many messages differ */
+uint32_t b2o_batch_equal(const uint8_t* a, const uint64_t* a_off, const uint8_t* b,
+                         const uint64_t* b_off, const uint32_t* len, uint32_t n,
+                         int32_t* scratch_ok, uint32_t* first_bad, int threads);
 
 #ifdef __cplusplus
 }

@@ -9,7 +9,9 @@
 #include <pthread.h>
 #include <time.h>
 
-enum { OP_CRC = 0, OP_COMP = 1, OP_UNCOMP = 2 };
+#include <string.h>
+
+enum { OP_CRC = 0, OP_COMP = 1, OP_UNCOMP = 2, OP_EQUAL = 3 };
 
 struct job {
     int op;
@@ -31,6 +33,8 @@ static void* worker(void* arg) {
         const uint8_t* src = j->data + j->off[i];
         if (j->op == OP_CRC) {
             j->u32_out[i] = b2o_crc32c_value(src, j->len[i]);
+        } else if (j->op == OP_EQUAL) { /* message i of `data` against the same message in `out` */
+            j->ok[i] = memcmp(src, j->out + j->out_off[i], j->len[i]) == 0;
         } else if (j->op == OP_COMP) {
             j->u32_out[i] = (uint32_t)b2o_snappy_compress(src, j->len[i], j->out + j->out_off[i]);
         } else {
@@ -86,4 +90,21 @@ double b2o_batch_uncompress(const uint8_t* data, const uint64_t* off, const uint
                             int threads) {
     struct job j = {OP_UNCOMP, 0, 0, data, off, len, out, out_off, out_cap, ulen, ok};
     return run(j, n, threads);
+}
+
+/* Compare message i of arena a (at a_off[i]) with message i of arena b (at b_off[i]), len[i] bytes each.
+ * Returns the number of messages that differ and stores the index of the first one (or n) in *first_bad.
+ * The parity gates of bench.py and the full-size tests use it to check EVERY message of a batch. */
+uint32_t b2o_batch_equal(const uint8_t* a, const uint64_t* a_off, const uint8_t* b, const uint64_t* b_off,
+                         const uint32_t* len, uint32_t n, int32_t* scratch_ok, uint32_t* first_bad, int threads) {
+    struct job j = {OP_EQUAL, 0, 0, a, a_off, len, (uint8_t*)b, b_off, 0, 0, scratch_ok};
+    uint32_t i, bad = 0;
+    run(j, n, threads);
+    *first_bad = n;
+    for (i = 0; i < n; i++)
+        if (!scratch_ok[i]) {
+            if (!bad) *first_bad = i;
+            bad++;
+        }
+    return bad;
 }

@@ -179,6 +179,8 @@ def port() -> Codec:
         L.b2o_corpus_fill_batch.argtypes = [C.c_int, C.c_uint64, C.c_uint32, _u64p, _u32p, _u8p, C.c_int]
         L.b2o_snappy_compress_fragment.restype = C.c_size_t
         L.b2o_snappy_compress_fragment.argtypes = [_u8p, C.c_size_t, _u8p]
+        L.b2o_batch_equal.restype = C.c_uint32
+        L.b2o_batch_equal.argtypes = [_u8p, _u64p, _u8p, _u64p, _u32p, C.c_uint32, _i32p, _u32p, C.c_int]
         L.b2o_crc32c_extend_tables.restype = C.c_uint32
         L.b2o_crc32c_extend_tables.argtypes = [C.c_uint32, _u8p, C.c_size_t]
     return _port
@@ -211,6 +213,25 @@ def best() -> Codec:
     """Reference library when present, else the port."""
     r = reference()
     return r if r is not None else port()
+
+
+def batch_equal(a: np.ndarray, a_off: np.ndarray, b: np.ndarray, b_off: np.ndarray, length: np.ndarray,
+                threads: int = 0):
+    """Compare message i of arena `a` (at a_off[i]) with message i of arena `b` (at b_off[i]), length[i] bytes
+    each, on `threads` host threads.  Returns (number of differing messages, index of the first or None)."""
+    n = len(length)
+    if n == 0:
+        return 0, None
+    a_off = np.ascontiguousarray(a_off, dtype=np.uint64)
+    b_off = np.ascontiguousarray(b_off, dtype=np.uint64)
+    length = np.ascontiguousarray(length, dtype=np.uint32)
+    ok = np.empty(n, dtype=np.int32)
+    first = C.c_uint32(0)
+    if threads <= 0:
+        threads = min(os.cpu_count() or 1, 64)
+    bad = port().lib.b2o_batch_equal(_ptr(a, _u8p), _ptr(a_off, _u64p), _ptr(b, _u8p), _ptr(b_off, _u64p),
+                                     _ptr(length, _u32p), n, _ptr(ok, _i32p), C.byref(first), threads)
+    return int(bad), (int(first.value) if bad else None)
 
 
 # ---- corpora -------------------------------------------------------------
