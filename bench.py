@@ -2,9 +2,13 @@
 """bench.py — payload GB/s of the snappy + CRC32C batch codec on B200.
 
 One step = one pass of the hot path over one batch of synthetic RPC bodies:
-CRC32C of every body, snappy compress, snappy decompress.  Workload at every N:
-BASELINE.json configs[1] — 2^20 x 1 KiB bodies per GPU, `words` corpus (weak
-scaling: every rank gets its own 1 GiB batch, no collective on the data path).
+CRC32C of every body, snappy compress, snappy decompress.  Headline workload at
+every N: BASELINE.json configs[1] — 2^20 x 1 KiB bodies per GPU, `words` corpus
+(weak scaling: every rank gets its own 1 GiB batch, no collective on the data
+path).  The same JSON line carries `workloads`: the other BASELINE configs
+(c1, c3, c4 at 8 GB, c5 = 64 GiB of 64 KiB fragments, decompress + CRC verify,
+split over the ranks), each gated on the parity of EVERY message against the
+reference's own CPU code before anything is timed.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
@@ -183,10 +187,374 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+# --------------------------------------------------------------------------- measurement helpers
+OPS = ("crc32c", "compress", "decompress", "pack")  # order of B2C_PROF_* in include/b2c_codec.h
+
+
+def kernel_names(max_len: int) -> dict:
+    small = max_len <= 1024
+    return {"crc32c": "crc32c_chunks_kernel" + ("" if max_len <= 4096 else " + crc32c_combine_kernel"),
+            "compress": ("snappy_compress_small2_kernel<4>" if small else
+                         "snappy_compress_orbit_kernel (fragments > 1 KiB) + snappy_compress_small2_kernel<4> (<= 1 KiB)"),
+            "decompress": ("snappy_decompress_small_kernel<8>" if small else
+                           "snappy_decompress_kernel / snappy_seg_* + snappy_decompress_blocks_kernel (+ small kernel for slots <= 1 KiB)"),
+            "pack": "snappy_message_sizes_kernel + scan + snappy_gather_kernel"}
+
+
+def mask_crc(crc: np.ndarray) -> np.ndarray:  # butil::crc32c::Mask, crc32c.h:44-48
+    return (((crc >> np.uint32(15)) | (crc << np.uint32(17))) + np.uint32(0xa282ead8)).astype(np.uint32)
+
+
+def load_traffic() -> dict:
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernels, taken from committed
+    `ncu --set full` captures by tools/ncu_traffic.py (profiles/ncu_traffic.json); absent entries are null."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
+def host_ram_available() -> int:
+    try:
+        import psutil
+        return int(psutil.virtual_memory().available)
+    except Exception:
+        return 64 << 30
+
+
+class DeviceBatch:
+    """One batch resident in HBM plus everything a step needs.  Construction runs the step once and checks
+    EVERY message against the CPU checker (the reference's own code when oracle/_ref is there): CRC values,
+    compressed bytes, decoded bytes (against the reference's decode of the same streams and the original)."""
+
+    def __init__(self, codec, arena, off, ln, label):
+        from oracle import oracle as O
+        self.codec, self.arena, self.off, self.ln, self.label = codec, arena, off, ln, label
+        n = self.n = len(ln)
+        self.payload = int(ln.astype(np.uint64).sum())
+        self.lay = codec.layout(off, ln)
+        self.d_in = codec.to_device(arena)
+        self.d_crc = codec.alloc(4 * n)
+        self.d_comp = codec.alloc(self.lay.max_compressed_bytes + 64)
+        self.d_coff = codec.alloc(8 * (n + 1))
+        self.d_back = codec.alloc(int(self.lay.arena_bytes) + 64)
+        self.d_st = codec.alloc(4 * n)
+        # the compressed layout is data-dependent: build it from a first (untimed) pass
+        codec.compress_dev(self.lay, self.d_in, self.d_comp, self.d_coff)
+        self.c_off = codec.d2h(self.d_coff, 8 * (n + 1), np.uint64)
+        self.comp_bytes = int(self.c_off[-1])
+        self.c_len = np.diff(self.c_off).astype(np.uint32)
+        self.clay = codec.layout(self.c_off[:-1], self.c_len)
+        self.step()
+        codec.sync()
+        # ---- parity gate: every message, before any timing ----
+        cpu = O.best()
+        threads = os.cpu_count() or 1
+        self.cpu_kind, self.cpu_threads = cpu.kind, threads
+        st = codec.d2h(self.d_st, 4 * n, np.int32)
+        assert (st == 0).all(), f"{label}: decompress reported errors"
+        self.crc = codec.d2h(self.d_crc, 4 * n, np.uint32)
+        want_crc, t_crc = cpu.batch_crc32c(arena, off, ln, threads=threads)
+        assert (self.crc == want_crc).all(), f"{label}: crc parity"
+        w_out, w_off, w_len, t_comp = cpu.batch_compress(arena, off, ln, threads=threads)
+        assert (self.c_len == w_len).all(), f"{label}: compressed lengths differ"
+        self.packed = codec.d2h(self.d_comp, self.comp_bytes)
+        bad, first = O.batch_equal(self.packed, self.c_off[:-1], w_out, w_off, w_len)
+        assert bad == 0, f"{label}: compressed bytes differ in {bad} messages, first {first}"
+        del w_out
+        ref_back, ref_ulen, ref_ok, t_dec = cpu.batch_uncompress(self.packed, self.c_off[:-1], self.c_len, off, ln,
+                                                                 threads=threads)
+        assert ref_ok.all() and (ref_ulen == ln).all(), f"{label}: the reference rejects our streams"
+        back = codec.d2h(self.d_back, int(self.lay.arena_bytes))
+        bad, first = O.batch_equal(back, off, ref_back, off, ln)
+        assert bad == 0, f"{label}: decoded bytes differ from the reference's in {bad} messages, first {first}"
+        del ref_back
+        bad, first = O.batch_equal(back, off, arena, off, ln)
+        assert bad == 0, f"{label}: round trip differs in {bad} messages, first {first}"
+        del back
+        self.cpu_seconds = {"crc32c": t_crc, "compress": t_comp, "decompress": t_dec}
+        self.d_masked = codec.to_device(mask_crc(self.crc))
+
+    def step(self):
+        c = self.codec
+        c.crc32c_dev(self.lay, self.d_in, self.d_crc)
+        c.compress_dev(self.lay, self.d_in, self.d_comp, self.d_coff)
+        c.decompress_dev(self.clay, self.d_comp, self.lay, self.d_back, self.d_st)
+
+    def verify_step(self):  # C5's op: decompress + CRC32C of the output against the stored masked CRC
+        self.codec.decompress_verify_dev(self.clay, self.d_comp, self.lay, self.d_back, self.d_masked, self.d_st)
+
+    def timed(self, fn, steps, warmup, dist, prof=False):
+        """(ms total for `steps` calls of fn, max over ranks; launches; per-op (ms, count) when prof)"""
+        import brpc_b200
+        c = self.codec
+        for _ in range(warmup):
+            fn()
+        c.sync()
+        if dist is not None:
+            dist.barrier()
+        if prof:
+            c.prof_enable(True)
+        l0 = c.launch_count
+        e0, e1 = c.event(), c.event()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        c.sync()
+        ms = e1.elapsed_ms_since(e0)
+        launches = c.launch_count - l0
+        per_op = None
+        if prof:
+            per_op = {name: c.prof_total_ms(k) for k, name in enumerate(OPS)}
+            c.prof_enable(False)
+        if dist is not None:
+            ms = brpc_b200.sharding.max_over_ranks(ms, device="cuda")
+            dist.barrier()
+        return ms, launches, per_op
+
+    def free(self):
+        for name in ("d_in", "d_crc", "d_comp", "d_coff", "d_back", "d_st", "d_masked"):
+            getattr(self, name).free()
+        self.lay.destroy()
+        self.clay.destroy()
+        self.packed = None
+
+
+def op_table(B: DeviceBatch, per_op: dict, hbm_peak: float, traffic: dict, key: str) -> dict:
+    """Per-op time, payload GB/s and roofline (algorithmic bytes of SURVEY 8(d) / mean launch duration)."""
+    N, Cb = B.payload, B.comp_bytes
+    alg = {"crc32c": N, "compress": N + Cb, "decompress": Cb + N, "pack": 2 * Cb}
+    names = kernel_names(int(B.ln.max()) if B.n else 0)
+    out = {}
+    for name in OPS:
+        t_ms, cnt = per_op[name]
+        ms = t_ms / max(cnt, 1)
+        gbs = alg[name] / (ms * 1e-3) / 1e9 if ms > 0 else None
+        out[name] = {"ms_per_step": ms, "payload_gbs": (N if name != "pack" else Cb) / (ms * 1e-3) / 1e9 if ms > 0 else None,
+                     "roofline": {"kernel": names[name], "bound": "hbm", "algorithmic_bytes_per_launch": alg[name],
+                                  "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
+                                  "frac": gbs / hbm_peak if gbs else None, "traffic": traffic.get(f"{key}/{name}")}}
+    return out
+
+
+class HostBatch:
+    """The same batch through the host-buffer C ABI, as a sender and a receiver call it: IOBuf-like block lists in
+    ordinary pageable memory in, page-locked flat buffers out, PCIe inside the timed region.
+      sender    b2c_snappy_compress_crc_batch    (checksum + compress, one pass over the staged bodies)
+      receiver  b2c_snappy_decompress_verify_batch (decode + check every body against the sender's checksum)
+    Serial: one thread calls sender then receiver.  Overlapped: two threads with a ctx each (what a loaded server
+    does: it compresses responses while it decompresses requests), so H2D and D2H use the link in both directions."""
+
+    def __init__(self, sender, receiver, B: DeviceBatch, workload: str, rank: int):
+        import brpc_b200
+        self.s, self.r, self.B = sender, receiver, B
+        rng = np.random.default_rng(2024 + rank)
+        if workload == "c2":  # 1-2 blocks per body at a seeded random cut (SURVEY.md 8(d))
+            self.segs, self.seg_begin = brpc_b200.make_iovecs(B.arena, B.off, B.ln, cuts=rng.integers(0, MSG_BYTES + 1, B.n))
+        else:  # IOBuf's default blocks: 8192 bytes minus the 32-byte header
+            self.segs, self.seg_begin = brpc_b200.make_iovecs(B.arena, B.off, B.ln, seg_bytes=8160)
+        # the receiver's input: the compressed streams in pageable memory, cut into IOBuf blocks
+        self.comp_host = np.array(B.packed, copy=True)
+        self.csegs, self.cbeg = brpc_b200.make_iovecs(self.comp_host, B.c_off[:-1], B.c_len, seg_bytes=8160)
+        self.masked = mask_crc(B.crc)
+        # results land in page-locked buffers (what the bRPC shim hands out from its pinned block pool)
+        self.h_comp = sender.pinned(B.comp_bytes + 4096)
+        self.h_back = receiver.pinned(B.payload + 64)
+        self.h2d = self.d2h = 0
+
+    def send(self):
+        o, crc = self.s.compress_crc_batch(self.segs, self.seg_begin, self.h_comp, masked=True)
+        self.last_o, self.last_crc = o, crc
+        return self.s.last_transfer_bytes()
+
+    def recv(self):
+        o, status = self.r.decompress_verify_batch(self.csegs, self.cbeg, self.masked, self.h_back)
+        self.last_ro, self.last_status = o, status
+        return self.r.last_transfer_bytes()
+
+    def check(self):
+        """every message of the last send/recv against the parity-gated device results"""
+        from oracle import oracle as O
+        B = self.B
+        assert np.array_equal(self.last_o, B.c_off), f"{B.label}: e2e compressed offsets differ"
+        assert np.array_equal(self.last_crc, self.masked), f"{B.label}: e2e checksums differ"
+        assert np.array_equal(self.h_comp[:B.comp_bytes], B.packed), f"{B.label}: e2e compressed bytes differ"
+        assert not self.last_status.any(), f"{B.label}: e2e receiver reported errors"
+        bad, first = O.batch_equal(self.h_back, self.last_ro[:-1], B.arena, B.off, B.ln)
+        assert bad == 0, f"{B.label}: e2e decoded bytes differ in {bad} messages, first {first}"
+
+    def _sync_ranks(self, dist):
+        if dist is not None:
+            dist.barrier()
+
+    def time_serial(self, steps, dist):
+        import brpc_b200
+        self.send(), self.recv()  # warm-up: sizes the pinned staging and device arenas
+        self.check()
+        self._sync_ranks(dist)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            a = self.send()
+            b = self.recv()
+        dt = time.perf_counter() - t0
+        self.h2d, self.d2h = a[0] + b[0], a[1] + b[1]
+        if dist is not None:
+            dt = brpc_b200.sharding.max_over_ranks(dt, device="cuda")
+        self.check()
+        return dt
+
+    def time_overlapped(self, steps, dist, threads_each):
+        import threading
+        import brpc_b200
+        for c in (self.s, self.r):
+            c.set_option(c.OPT_HOST_THREADS, threads_each)
+        self.send(), self.recv()  # re-creates each ctx's pool at its new size
+        start = threading.Barrier(3)
+        err = []
+
+        def loop(fn):
+            try:
+                start.wait()
+                for _ in range(steps):
+                    fn()
+            except Exception as e:  # noqa: BLE001
+                err.append(e)
+
+        ts = [threading.Thread(target=loop, args=(f,)) for f in (self.send, self.recv)]
+        for t in ts:
+            t.start()
+        self._sync_ranks(dist)
+        start.wait()
+        t0 = time.perf_counter()
+        for t in ts:
+            t.join()
+        dt = time.perf_counter() - t0
+        if err:
+            raise err[0]
+        if dist is not None:
+            dt = brpc_b200.sharding.max_over_ranks(dt, device="cuda")
+        self.check()
+        for c in (self.s, self.r):
+            c.set_option(c.OPT_HOST_THREADS, 0)
+        return dt
+
+
+def pcie_probe(codec, d_buf, h_buf):
+    """this box's pinned-memory copy rate, one direction at a time (measured, not assumed)"""
+    nb = min(256 << 20, len(h_buf))
+    out = {}
+    for name, fn, a in (("h2d_gbs", codec.lib.b2c_memcpy_h2d, (d_buf.ptr, h_buf.ctypes.data, nb)),
+                        ("d2h_gbs", codec.lib.b2c_memcpy_d2h, (h_buf.ctypes.data, d_buf.ptr, nb))):
+        fn(codec.ctx, *a)
+        codec.sync()
+        e0, e1 = codec.event(), codec.event()
+        e0.record()
+        for _ in range(4):
+            fn(codec.ctx, *a)
+        e1.record()
+        codec.sync()
+        out[name] = 4 * nb / (e1.elapsed_ms_since(e0) * 1e-3) / 1e9
+    return out
+
+
+PARITY_NOTE = ("every message of the timed batch, before timing: CRC32C values, compressed bytes and decoded bytes equal "
+               "the CPU checker's (kind below); e2e outputs are compared with the same bytes after the timed calls")
+
+
+def measure_workload(codecs, wl, corpus, nbytes, messages, rank, world, dist, steps, warmup, e2e_steps, hbm_peak, traffic,
+                     want_e2e=True, c5_total=0, sampler_factory=None, extras=False):
+    """One workload shape on this rank's GPU: parity gate, device-resident step, per-op rooflines, end to end."""
+    from oracle import oracle as O
+    a = argparse.Namespace(workload=wl, corpus=corpus, bytes=nbytes, messages=messages)
+    lengths = workload_lengths(a)
+    arena, off, ln = O.corpus_batch(corpus, lengths, first_index=rank * len(lengths))
+    label = f"{wl}/{corpus}"
+    codec = codecs[0]
+    B = DeviceBatch(codec, arena, off, ln, label)
+    sampler = sampler_factory() if sampler_factory else None  # samples over warm-up + timed steps (all under load)
+    ms, launches, per_op = B.timed(B.step, steps, warmup, dist, prof=True)
+    clocks = sampler.stop() if sampler else None
+    payload = B.payload
+    cpu_total = sum(B.cpu_seconds.values())
+    res = {
+        "config": config_dict(world, a, ln),
+        "value": payload * world * steps / (ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": ms / steps, "steps": steps,
+        "gpu_launches": int(launches), "compression_ratio": B.comp_bytes / max(payload, 1),
+        "ops": op_table(B, per_op, hbm_peak, traffic, label),
+        "parity": PARITY_NOTE,
+        "cpu_baseline": {"value": payload / cpu_total / 1e9, "unit": "GB/s", "cores": B.cpu_threads, "kind": B.cpu_kind,
+                         "per_op_gbs": {k: payload / v / 1e9 for k, v in B.cpu_seconds.items()},
+                         "sample": f"full batch ({B.n} bodies, {payload} B), one pass of crc32c + RawCompress + RawUncompress, "
+                                   f"static split over {B.cpu_threads} threads (rank 0's batch)"},
+    }
+    if clocks is not None:
+        res["clocks"] = clocks
+    if wl == "c5" and c5_total:
+        # C5's own op on the config that names it: 64 GiB of 64 KiB fragments, decompress + CRC32C check of the output
+        # against the stored masked CRC, split over the ranks; every rank walks its share as `tiles` passes over its
+        # own unique slab (SURVEY 8(d) allows a >= 1 GiB unique slab tiled, with the factor reported)
+        tiles = max(1, c5_total // (payload * world))
+        vms, vl, _ = B.timed(B.verify_step, tiles, 2, dist)
+        st = codec.d2h(B.d_st, 4 * B.n, np.int32)
+        assert (st == 0).all(), "decompress+verify reported errors"
+        alg = B.comp_bytes + payload
+        gbs = alg * tiles / (vms * 1e-3) / 1e9
+        res["decompress_verify"] = {
+            "total_payload_bytes": payload * tiles * world, "unique_slab_bytes_per_gpu": payload, "tile_factor": tiles,
+            "scaling": "strong (the 64 GiB total is fixed; each rank owns total / n_gpus)",
+            "dev": {"value": payload * tiles * world / (vms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_slab": vms / tiles,
+                    "roofline": {"kernel": "snappy_decompress_kernel + crc32c_chunks_kernel + snappy_verify_crc_kernel",
+                                 "bound": "hbm", "algorithmic_bytes_per_launch": alg, "achieved": gbs, "peak": hbm_peak,
+                                 "unit": "GB/s", "frac": gbs / hbm_peak, "traffic": traffic.get(f"{label}/verify")}}}
+    H = None
+    if want_e2e:
+        import brpc_b200
+        H = HostBatch(codecs[0], codecs[1], B, wl, rank)
+        hw = os.cpu_count() or 1
+        lw = int(os.environ.get("LOCAL_WORLD_SIZE", world))
+        serial_s = H.time_serial(e2e_steps, dist)
+        over_s = H.time_overlapped(e2e_steps, dist, max(2, hw // max(lw, 1) // 2))
+        res["e2e"] = {
+            "value": payload * world * e2e_steps / over_s / 1e9, "unit": "GB/s",
+            "h2d_bytes_per_step": int(H.h2d), "d2h_bytes_per_step": int(H.d2h), "steps": e2e_steps,
+            "serial_value": payload * world * e2e_steps / serial_s / 1e9,
+            "path": "sender b2c_snappy_compress_crc_batch (crc32c + compress) and receiver b2c_snappy_decompress_verify_batch "
+                    "(decompress + crc32c check) on every body; inputs = pageable host block lists (1-2 blocks per 1 KiB "
+                    "body, 8160-byte IOBuf blocks otherwise) gathered into pinned staging by each ctx's host threads; "
+                    "outputs = page-locked host buffers.  value: sender and receiver run on two threads with a ctx each, "
+                    "as a loaded server does (H2D and D2H overlap); serial_value: one thread calls them back to back"}
+        if wl == "c5" and c5_total:
+            tiles = res["decompress_verify"]["tile_factor"]
+            H._sync_ranks(dist)
+            t0 = time.perf_counter()
+            for _ in range(tiles):
+                H.recv()
+            dt = time.perf_counter() - t0
+            if dist is not None:
+                dt = brpc_b200.sharding.max_over_ranks(dt, device="cuda")
+            H.check()
+            a2, b2 = codecs[1].last_transfer_bytes()
+            res["decompress_verify"]["batch"] = {"value": payload * tiles * world / dt / 1e9, "unit": "GB/s",
+                                                 "h2d_bytes_per_slab": int(a2), "d2h_bytes_per_slab": int(b2),
+                                                 "entry_point": "b2c_snappy_decompress_verify_batch"}
+        if extras and rank == 0:
+            res["e2e"]["pcie_probe"] = pcie_probe(codec, B.d_back, H.h_back)
+    return res, B, H
+
+
+def release(B, H):
+    if H is not None:
+        for c, arr in ((H.s, H.h_comp), (H.r, H.h_back)):
+            c.lib.b2c_host_free_pinned(c.ctx, arr.ctypes.data)
+        H.h_comp = H.h_back = None
+    B.free()
+
+
 # --------------------------------------------------------------------------- our arm
 def run_ours(args, rank, local_rank, world):
     import brpc_b200
-    from oracle import oracle as O
     dist = None
     if world > 1:
         import torch
@@ -194,239 +562,60 @@ def run_ours(args, rank, local_rank, world):
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    codec = brpc_b200.Codec(local_rank)
-    arena, off, ln = make_batch(rank, args)
-    n_msgs = len(ln)
-    payload = int(ln.astype(np.uint64).sum())
-    lay = codec.layout(off, ln)
-    d_in = codec.to_device(arena)
-    d_crc = codec.alloc(4 * n_msgs)
-    d_comp = codec.alloc(lay.max_compressed_bytes + 64)
-    d_coff = codec.alloc(8 * (n_msgs + 1))
-    d_back = codec.alloc(int(lay.arena_bytes) + 64)
-    d_st = codec.alloc(4 * n_msgs)
-
-    # the compressed layout is data-dependent: build it once from a first (untimed) pass
-    codec.compress_dev(lay, d_in, d_comp, d_coff)
-    c_off = codec.d2h(d_coff, 8 * (n_msgs + 1), np.uint64)
-    comp_bytes = int(c_off[-1])
-    clay = codec.layout(c_off[:-1], np.diff(c_off).astype(np.uint32))
-
-    def step():
-        codec.crc32c_dev(lay, d_in, d_crc)
-        codec.compress_dev(lay, d_in, d_comp, d_coff)
-        codec.decompress_dev(clay, d_comp, lay, d_back, d_st)
-
-    # ---- parity gate before any timing (sampled against the CPU checker) ----
-    step()
-    codec.sync()
-    st = codec.d2h(d_st, 4 * n_msgs, np.int32)
-    assert (st == 0).all(), "decompress reported errors"
-    cpu = O.best()
-    idx = np.arange(0, n_msgs, max(1, n_msgs // 2048))
-    crc = codec.d2h(d_crc, 4 * n_msgs, np.uint32)
-    want_crc, _ = cpu.batch_crc32c(arena, off[idx], ln[idx], threads=4)
-    assert (crc[idx] == want_crc).all(), "crc parity"
-    packed = codec.d2h(d_comp, comp_bytes)
-    w_out, w_off, w_len, _ = cpu.batch_compress(arena, off[idx], ln[idx], threads=4)
-    for j, i in enumerate(idx):
-        assert packed[int(c_off[i]):int(c_off[i + 1])].tobytes() == \
-            w_out[int(w_off[j]):int(w_off[j]) + int(w_len[j])].tobytes(), f"compress parity at message {i}"
-    back = codec.d2h(d_back, int(lay.arena_bytes))
-    assert all(back[int(off[i]):int(off[i]) + int(ln[i])].tobytes() ==
-               arena[int(off[i]):int(off[i]) + int(ln[i])].tobytes() for i in idx), "round-trip parity"
-    del packed, back
-
-    sampler = ClockSampler(local_rank) if rank == 0 else None  # samples over warm-up + timed steps (all under load)
-    for _ in range(args.warmup):
-        step()
-    codec.sync()
-    if dist is not None:
-        dist.barrier()
-    codec.prof_enable(True)
-    launches0 = codec.launch_count
-    e0, e1 = codec.event(), codec.event()
-    e0.record()
-    for _ in range(args.steps):
-        step()
-    e1.record()
-    codec.sync()
-    ms = e1.elapsed_ms_since(e0)
-    launches = codec.launch_count - launches0
-    prof = {name: codec.prof_total_ms(k) for k, name in enumerate(("crc32c", "compress", "decompress", "pack"))}
-    codec.prof_enable(False)
-    clocks = sampler.stop() if sampler else None
-    if dist is not None:
-        ms = brpc_b200.sharding.max_over_ranks(ms, device="cuda")  # device time, max over ranks
-        dist.barrier()
-
-    # ---- the fused receiver op on device-resident data (decompress + CRC32C of the output compared
-    #      with the stored masked CRC, snappy-framing semantics), timed on its own ----
-    verify_ms = None
-    if args.workload == "c5":
-        crc_host = codec.d2h(d_crc, 4 * n_msgs, np.uint32)
-        masked = ((crc_host >> np.uint32(15)) | (crc_host << np.uint32(17))) + np.uint32(0xa282ead8)  # crc32c.h:44-48
-        d_masked = codec.to_device(masked.astype(np.uint32))
-        codec.decompress_verify_dev(clay, d_comp, lay, d_back, d_masked, d_st)
-        codec.sync()
-        assert (codec.d2h(d_st, 4 * n_msgs, np.int32) == 0).all(), "decompress+verify reported errors"
-        v0, v1 = codec.event(), codec.event()
-        v0.record()
-        for _ in range(args.steps):
-            codec.decompress_verify_dev(clay, d_comp, lay, d_back, d_masked, d_st)
-        v1.record()
-        codec.sync()
-        verify_ms = v1.elapsed_ms_since(v0) / args.steps
-        if dist is not None:
-            verify_ms = brpc_b200.sharding.max_over_ranks(verify_ms, device="cuda")
-
-    # ---- end to end through the host-buffer ABI (iovec block lists, PCIe inside) ----
-    rng = np.random.default_rng(2024 + rank)
-    if args.workload == "c2":  # 1-2 blocks per body at a seeded random cut
-        segs, seg_begin = brpc_b200.make_iovecs(arena, off, ln, cuts=rng.integers(0, MSG_BYTES + 1, n_msgs))
-    else:  # IOBuf's default blocks: 8192 bytes minus the 32-byte header
-        segs, seg_begin = brpc_b200.make_iovecs(arena, off, ln, seg_bytes=8160)
-    # result buffers are page-locked (b2c_host_alloc_pinned), as the bRPC shim's output blocks would be, so the
-    # library DMAs results straight into them; the INPUT blocks stay ordinary pageable memory like IOBuf blocks
-    h_comp = codec.pinned(int(lay.max_compressed_bytes))
-    h_back = codec.pinned(payload + 64)
+    codecs = (brpc_b200.Codec(local_rank), brpc_b200.Codec(local_rank))  # [1]: the receiver's ctx of the e2e legs
+    hbm_peak, peak_src = read_peaks()
+    traffic = load_traffic()
     e2e_steps = max(1, min(args.steps, 3))
-    bytes_h2d = bytes_d2h = 0
+    head, B, H = measure_workload(codecs, args.workload, args.corpus, args.bytes, args.messages, rank, world, dist, args.steps,
+                                  args.warmup, e2e_steps, hbm_peak, traffic, c5_total=args.c5_total if args.workload == "c5" else 0,
+                                  sampler_factory=(lambda: ClockSampler(local_rank)) if rank == 0 else None, extras=True)
+    n_msgs = B.n
+    release(B, H)
 
-    cache = {}
-
-    def e2e_step(fused=True):
-        nonlocal bytes_h2d, bytes_d2h
-        h2d = d2h = 0
-        if fused:  # sender: checksum + compress in one pass over the staged bodies
-            o, crc = codec.compress_crc_batch(segs, seg_begin, h_comp, masked=True)
-            a, b = codec.last_transfer_bytes(); h2d += a; d2h += b
-        else:
-            codec.crc32c_batch(segs, seg_begin)
-            a, b = codec.last_transfer_bytes(); h2d += a; d2h += b
-            o = codec.compress_batch(segs, seg_begin, h_comp)
-            a, b = codec.last_transfer_bytes(); h2d += a; d2h += b
-        if "o" not in cache or o[-1] != cache["o"][-1]:
-            # iovecs of the compressed bodies (what an IOBuf holding them would report); built once —
-            # the streams are a pure function of the inputs, so they land at the same offsets every step
-            csegs = np.empty((n_msgs, 2), dtype=np.uint64)
-            csegs[:, 0] = h_comp.ctypes.data + o[:-1]
-            csegs[:, 1] = np.diff(o)
-            cache["o"], cache["csegs"] = o, csegs
-            cache["cbeg"] = np.arange(n_msgs + 1, dtype=np.uint32)
-        if fused:  # receiver: decompress + verify each body against the sender's checksum
-            _, status = codec.decompress_verify_batch(cache["csegs"], cache["cbeg"], crc, h_back)
-        else:
-            _, status = codec.decompress_batch(cache["csegs"], cache["cbeg"], h_back)
-        a, b = codec.last_transfer_bytes(); h2d += a; d2h += b
-        assert not status.any()
-        bytes_h2d, bytes_d2h = h2d, d2h
-
-    def time_e2e(fused=True):
-        nonlocal bytes_h2d, bytes_d2h
-        e2e_step(fused)  # warm-up: sizes the pinned staging and device arenas
-        if dist is not None:
-            dist.barrier()
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            e2e_step(fused)
-        dt = time.perf_counter() - t0
-        if dist is not None:
-            dt = brpc_b200.sharding.max_over_ranks(dt, device="cuda")
-        return dt, bytes_h2d, bytes_d2h
-
-    # what bounds the end-to-end path: this box's pinned-memory copy rate, one direction at a time (SURVEY 8(d):
-    # measured in the same run, not assumed; tools/pcie_bw.py also times both directions at once)
-    def pcie_probe():
-        nb = min(256 << 20, len(h_back))
-        out = {}
-        for name, fn, args in (("h2d_gbs", codec.lib.b2c_memcpy_h2d, (d_back.ptr, h_back.ctypes.data, nb)),
-                               ("d2h_gbs", codec.lib.b2c_memcpy_d2h, (h_back.ctypes.data, d_back.ptr, nb))):
-            fn(codec.ctx, *args)
-            codec.sync()
-            a, b = codec.event(), codec.event()
-            a.record()
-            for _ in range(4):
-                fn(codec.ctx, *args)
-            b.record()
-            codec.sync()
-            out[name] = 4 * nb / (b.elapsed_ms_since(a) * 1e-3) / 1e9
-        return out
-
-    pcie = pcie_probe() if rank == 0 else None
-    # (a) the headline: input blocks in ordinary pageable memory (what IOBuf blocks are today); host threads gather
-    #     them into pinned staging and the copy engines move the slabs
-    e2e_s, bytes_h2d, bytes_d2h = time_e2e()
-    # (a') the same work as three separate calls (crc32c_batch, compress_batch, decompress_batch): the bodies cross
-    #      PCIe twice on the sender side and nothing is verified on the receiver side
-    e2e_separate_s, _, _ = time_e2e(fused=False)
-    # (b) for the record: blocks in page-locked memory + B2C_OPT_INPUT_PINNED (the device gathers them over PCIe
-    #     itself).  On this box kernel reads of host memory reach ~35 GB/s against ~55 GB/s for the copy engines,
-    #     so (a) stays the default path.
-    p_arena = codec.pinned(len(arena))
-    p_arena[:] = arena
-    segs_pageable = segs.copy()
-    segs[:, 0] = segs[:, 0] - np.uint64(arena.ctypes.data) + np.uint64(p_arena.ctypes.data)
-    cache.clear()
-    codec.set_option(codec.OPT_INPUT_PINNED, 1)
-    e2e_zero_copy_s, _, _ = time_e2e()
-    codec.set_option(codec.OPT_INPUT_PINNED, 0)
-    segs[:] = segs_pageable
-    first = b"".join(arena[int(off[i]):int(off[i]) + int(ln[i])].tobytes() for i in range(min(4, n_msgs)))
-    assert h_back[:len(first)].tobytes() == first
+    # ---- the other BASELINE configs, same gates, one entry each ----
+    workloads = {}
+    if args.workload == "c2" and not args.only_headline:
+        ram = host_ram_available()
+        c4_bytes = int(min(args.c4_bytes, max(1 << 30, ram // 7)))  # ~6 host copies of the batch are alive at the peak
+        plan = [("c5", "c5", "words", 1 << 30, True, args.c5_total)]
+        if world == 1:  # the single-GPU configs are measured at N = 1 only (C4 alone holds ~45 GB of host memory per rank)
+            plan = [("c1", "c1", "words", 0, True, 0), ("c3", "c3", "words", 0, True, 0),
+                    ("c4", "c4", "words", c4_bytes, True, 0)] + plan + \
+                   [("c5_rand62", "c5", "rand62", 1 << 30, False, 0), ("c5_az09", "c5", "az09", 1 << 30, False, 0),
+                    ("c2_rand62", "c2", "rand62", 0, False, 0), ("c2_az09", "c2", "az09", 0, False, 0)]
+        for key, wl, corpus, nbytes, e2e, c5_total in plan:
+            t0 = time.perf_counter()
+            big = nbytes > (2 << 30)
+            r, B, H = measure_workload(codecs, wl, corpus, nbytes, N_MSGS, rank, world, dist, 2 if big else 3, 3,
+                                       1 if big else 2, hbm_peak, traffic, want_e2e=e2e, c5_total=c5_total)
+            release(B, H)
+            r["bench_seconds"] = time.perf_counter() - t0
+            if key == "c4" and c4_bytes < args.c4_bytes:
+                r["config"]["scaled_down"] = f"{c4_bytes} B instead of {args.c4_bytes} B: host RAM available {ram} B"
+            workloads[key] = r
 
     if rank == 0:
-        hbm_peak, peak_src = read_peaks()
-        k_ms, k_n = prof["compress"]
-        alg_bytes = payload + comp_bytes  # N read + C written, per launch
-        achieved = alg_bytes / (k_ms / max(k_n, 1) * 1e-3) / 1e9 if k_ms > 0 else 0.0
-        per_op = {}
-        for name, nbytes in (("crc32c", payload), ("compress", payload), ("decompress", payload), ("pack", comp_bytes)):
-            t_ms, cnt = prof[name]
-            per_op[name] = {"ms_per_step": t_ms / max(cnt, 1),
-                            "payload_gbs": nbytes / (t_ms / max(cnt, 1) * 1e-3) / 1e9 if t_ms > 0 else None}
-        # CPU baseline on this box's host cores, same buffers, rank 0 only
-        cores = os.cpu_count() or 1
-        t_cpu = 0.0
-        reps = 2
-        for _ in range(reps):
-            _, dt = cpu.batch_crc32c(arena, off, ln, threads=cores); t_cpu += dt
-            o, oo, ol, dt = cpu.batch_compress(arena, off, ln, threads=cores); t_cpu += dt
-            _, _, _, dt = cpu.batch_uncompress(o, oo, ol, off, ln, threads=cores); t_cpu += dt
-        cpu_gbs = payload * reps / t_cpu / 1e9
+        comp = head["ops"]["compress"]["roofline"]
         line = {
-            "metric": METRIC, "value": payload * world * args.steps / (ms * 1e-3) / 1e9, "unit": "GB/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": config_dict(world, args, ln), "clocks": clocks,
-            "e2e": {"value": payload * world * e2e_steps / e2e_s / 1e9, "unit": "GB/s",
-                    "h2d_bytes_per_step": int(bytes_h2d), "d2h_bytes_per_step": int(bytes_d2h), "steps": e2e_steps,
-                    "path": "b2c_snappy_compress_crc_batch (sender: crc32c + compress, one pass) + "
-                            "b2c_snappy_decompress_verify_batch (receiver: decompress + crc32c check); inputs = pageable host "
-                            "iovecs (1-2 blocks per body) gathered into pinned staging by host threads; outputs = "
-                            "page-locked host buffers",
-                    "separate_calls_value": payload * world * e2e_steps / e2e_separate_s / 1e9,
-                    "pcie_probe": pcie,
-                    "pinned_inputs_device_gather_value": payload * world * e2e_steps / e2e_zero_copy_s / 1e9},
-            "gpu_launches": int(launches),
-            "roofline": {"kernel": "snappy_compress_small2_kernel" if int(ln.max()) <= 1024 else "snappy_compress_*_kernel (all size classes of the batch)", "bound": "hbm", "achieved": achieved,
-                         "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                         # dram__bytes_read+write of this kernel from the committed ncu --set full capture of this
-                         # very workload (profiles/r1_ncu_full_key_metrics.txt); unknown for other workloads
-                         "traffic": 1623731000 if (args.workload, args.corpus, n_msgs) == ("c2", "words", N_MSGS) else None,
-                         "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
-                         "note": "byte-exact greedy LZ77 is a serial dependency chain per fragment: latency/issue bound, "
-                                 "not HBM bound (see DESIGN.md)"},
-            "ops": per_op, "compression_ratio": comp_bytes / payload,
-            "messages_per_s": n_msgs * world * args.steps / (ms * 1e-3),
-            **({"decompress_verify": {"ms_per_step": verify_ms, "payload_gbs": payload * world / (verify_ms * 1e-3) / 1e9}}
-               if verify_ms else {}),
-            "cpu_baseline": {"value": cpu_gbs, "unit": "GB/s", "cores": cores, "kind": cpu.kind,
-                             "sample": f"full batch ({n_msgs} bodies, {payload} B) x {reps} passes of crc32c + RawCompress + "
-                                       f"RawUncompress, static split over {cores} threads"},
+            "metric": METRIC, "value": head["value"], "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": head["config"], "clocks": head.get("clocks"),
+            "e2e": head["e2e"], "gpu_launches": head["gpu_launches"],
+            "roofline": {"kernel": comp["kernel"], "bound": "hbm", "achieved": comp["achieved"], "peak": hbm_peak,
+                         "unit": "GB/s", "frac": comp["frac"], "traffic": comp["traffic"],
+                         "algorithmic_bytes_per_launch": comp["algorithmic_bytes_per_launch"], "peak_source": peak_src,
+                         "note": "dominant kernel of the step (compress); crc32c / decompress / pack rooflines are in `ops`. "
+                                 "Byte-exact greedy LZ77 is a serial dependency chain per fragment: latency/issue bound, not "
+                                 "HBM bound (see DESIGN.md)"},
+            "ops": head["ops"], "compression_ratio": head["compression_ratio"],
+            "messages_per_s": n_msgs * world * args.steps / (head["ms_per_step"] * args.steps * 1e-3),
+            "parity": head["parity"], "cpu_baseline": head["cpu_baseline"],
+            **({"decompress_verify": head["decompress_verify"]} if "decompress_verify" in head else {}),
+            "workloads": workloads,
         }
         print(json.dumps(line), flush=True)
-    codec.close()
+    for c in codecs:
+        c.close()
     if dist is not None:
         dist.destroy_process_group()
 
@@ -438,9 +627,12 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--messages", type=int, default=N_MSGS, help="bodies per GPU for --workload c2")
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS), help="default c2 = BASELINE configs[1]")
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS), help="headline workload; default c2 = BASELINE configs[1]")
     ap.add_argument("--corpus", default=CORPUS, choices=["words", "az09", "rand62"])
     ap.add_argument("--bytes", type=int, default=1 << 30, help="payload per GPU for --workload c4 / c5")
+    ap.add_argument("--c4-bytes", type=int, default=8_000_000_000, help="payload of the `workloads.c4` entry (BASELINE: 8 GB)")
+    ap.add_argument("--c5-total", type=int, default=64 << 30, help="total payload of C5's decompress + verify op (BASELINE: 64 GiB)")
+    ap.add_argument("--only-headline", action="store_true", help="skip the `workloads` entries (kernel tuning runs)")
     args = ap.parse_args()
     if args.impl == "ours":
         args.warmup = max(args.warmup, 3)  # timing rule: at least 3 warm-up steps

@@ -22,6 +22,7 @@ def _batch(seed):
     lengths = np.concatenate([rng.integers(4097, 300000, 40), rng.integers(0, 4097, 200),
                               np.array([0, 1, 4096, 4097, 8192, 1 << 20, (3 << 20) + 5])]).astype(np.uint32)
     rng.shuffle(lengths)
+    assert (lengths > 4096).sum() >= 40  # messages of more than one 4 KiB chunk are the ones that use the scratch array
     return O.corpus_batch(("words", "rand62")[seed % 2], lengths, first_index=seed * 1000)
 
 
@@ -42,10 +43,13 @@ def test_noalloc_crc_matches_allocating_entry_point_twice():
             ref = codec.d2h(d_ref, 4 * len(ln), np.uint32)
             new = codec.d2h(d_new, 4 * len(ln), np.uint32)
             assert (ref == new).all(), (call, np.nonzero(ref != new)[0][:10])
-            # and both agree with the CPU checker on a few messages
-            for i in (0, len(ln) // 2, len(ln) - 1):
-                m = arena[int(off[i]):int(off[i]) + int(ln[i])]
-                assert int(new[i]) == O.best().crc32c_extend(int(init[i]), m)
+            # and EVERY message, the multi-chunk ones included, agrees with the CPU checker
+            cpu = O.best()
+            want = np.array([cpu.crc32c_extend(int(init[i]), arena[int(off[i]):int(off[i]) + int(ln[i])])
+                             for i in range(len(ln))], dtype=np.uint32)
+            assert (new == want).all(), (call, np.nonzero(new != want)[0][:10])
+            multi = ln > 4096
+            assert multi.any() and (new[multi] == want[multi]).all()
     finally:
         codec.close()
 
