@@ -347,16 +347,27 @@ class HostBatch:
     Serial: one thread calls sender then receiver.  Overlapped: two threads with a ctx each (what a loaded server
     does: it compresses responses while it decompresses requests), so H2D and D2H use the link in both directions."""
 
-    def __init__(self, sender, receiver, B: DeviceBatch, workload: str, rank: int):
+    def __init__(self, sender, receiver, B: DeviceBatch, workload: str, rank: int, pinned_inputs: bool = False):
         import brpc_b200
         self.s, self.r, self.B = sender, receiver, B
+        self.pinned_inputs = pinned_inputs
         rng = np.random.default_rng(2024 + rank)
+        arena = B.arena
+        if pinned_inputs:  # the blocks come from a page-locked IOBuf block pool (host/b200_block_pool): no host gather
+            self.p_arena = sender.pinned(len(B.arena))
+            self.p_arena[:] = B.arena
+            arena = self.p_arena
+            self.comp_host = receiver.pinned(B.comp_bytes + 64)
+            self.comp_host[:B.comp_bytes] = B.packed
+        else:  # ordinary pageable memory, as IOBuf blocks are without the pool
+            self.comp_host = np.array(B.packed, copy=True)
+        for c in (sender, receiver):
+            c.set_option(c.OPT_INPUT_PINNED, 1 if pinned_inputs else 0)
         if workload == "c2":  # 1-2 blocks per body at a seeded random cut (SURVEY.md 8(d))
-            self.segs, self.seg_begin = brpc_b200.make_iovecs(B.arena, B.off, B.ln, cuts=rng.integers(0, MSG_BYTES + 1, B.n))
+            self.segs, self.seg_begin = brpc_b200.make_iovecs(arena, B.off, B.ln, cuts=rng.integers(0, MSG_BYTES + 1, B.n))
         else:  # IOBuf's default blocks: 8192 bytes minus the 32-byte header
-            self.segs, self.seg_begin = brpc_b200.make_iovecs(B.arena, B.off, B.ln, seg_bytes=8160)
-        # the receiver's input: the compressed streams in pageable memory, cut into IOBuf blocks
-        self.comp_host = np.array(B.packed, copy=True)
+            self.segs, self.seg_begin = brpc_b200.make_iovecs(arena, B.off, B.ln, seg_bytes=8160)
+        # the receiver's input: the compressed streams cut into IOBuf blocks
         self.csegs, self.cbeg = brpc_b200.make_iovecs(self.comp_host, B.c_off[:-1], B.c_len, seg_bytes=8160)
         self.masked = mask_crc(B.crc)
         # results land in page-locked buffers (what the bRPC shim hands out from its pinned block pool)
@@ -546,9 +557,14 @@ def measure_workload(codecs, wl, corpus, nbytes, messages, rank, world, dist, st
 
 def release(B, H):
     if H is not None:
-        for c, arr in ((H.s, H.h_comp), (H.r, H.h_back)):
+        bufs = [(H.s, H.h_comp), (H.r, H.h_back)]
+        if H.pinned_inputs:
+            bufs += [(H.s, H.p_arena), (H.r, H.comp_host)]
+        for c, arr in bufs:
             c.lib.b2c_host_free_pinned(c.ctx, arr.ctypes.data)
-        H.h_comp = H.h_back = None
+        H.h_comp = H.h_back = H.comp_host = H.p_arena = None
+        for c in (H.s, H.r):
+            c.set_option(c.OPT_INPUT_PINNED, 0)
     B.free()
 
 

@@ -403,54 +403,73 @@ void LayoutPlan::bind(const uint8_t* d, LayoutView* out) const {
     out->d_multi_list = has_chunk_arrays ? reinterpret_cast<const uint32_t*>(d + o_multi) : nullptr;
 }
 
-// Zero-copy input: one warp per message walks the message's blocks in page-locked HOST memory
-// (device-visible under UVA) and writes them, concatenated, into the device arena.
-__global__ void __launch_bounds__(256) gather_host_segments_kernel(const b2c_iovec* __restrict__ segs,
-                                                                   const uint32_t* __restrict__ seg_begin,
-                                                                   const uint64_t* __restrict__ off, uint32_t cnt,
-                                                                   uint8_t* __restrict__ d_in) {
+// Zero-copy input: one warp per message walks the message's blocks in page-locked HOST memory (device-visible
+// under UVA) and writes them, concatenated, into the device arena.
+//
+// What crosses PCIe is decided by the LOADS: a kernel pulls pinned host memory at the copy engines' rate (51 of
+// 55 GB/s on this box, tools/sysmem_read_probe.cu) as long as every request is a run of whole aligned 16-byte
+// vectors -- 4-byte or byte loads of the same bytes reach 35.  So each block is fetched as the aligned 16-byte
+// vectors that cover it (never a vector that holds none of its bytes), parked in the warp's shared-memory
+// buffer, and written out from there with aligned 16-byte stores whatever the phase between source and
+// destination is (the funnel shifts happen on shared-memory words, not on PCIe reads).
+// Small on purpose (16.6 KiB of shared memory per CTA, one CTA per SM): the gather of slab k+1 has to run beside the
+// codec kernels of slab k, which fill the SMs' shared memory (2 x 97 KiB for the small-body compressor); with 8 KiB
+// buffers the two took turns on the GPU and the sender's call went from 29 to 37 ms.
+constexpr uint32_t kGatherSlack = 32;  // per-warp buffer = chunk + the lead-in of an unaligned source + the copy-out's read-ahead
+
+// n bytes from shared memory `s` (any phase) to global `dst` (any phase): bytes up to dst's next 16-byte
+// boundary, aligned vectors assembled from 5 shared-memory words each, bytes again for the tail
+__device__ __forceinline__ void smem_to_global(uint8_t* __restrict__ dst, const uint8_t* s, uint32_t n, uint32_t lane) {
+    uint32_t head = (16u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15)) & 15u;
+    if (head > n) head = n;
+    if (lane < head) dst[lane] = s[lane];
+    const uint32_t vecs = (n - head) >> 4;
+    uint4* d4 = reinterpret_cast<uint4*>(dst + head);
+    const uint32_t sa = (uint32_t)__cvta_generic_to_shared(s + head);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(s + head - (sa & 3));  // aligned word holding the first byte
+    const uint32_t sh = (sa & 3) * 8;
+    for (uint32_t i = lane; i < vecs; i += 32) {
+        const uint32_t* q = w + 4 * i;
+        const uint32_t a = q[0], b = q[1], c = q[2], d = q[3], e = q[4];
+        d4[i] = make_uint4(__funnelshift_r(a, b, sh), __funnelshift_r(b, c, sh), __funnelshift_r(c, d, sh),
+                           __funnelshift_r(d, e, sh));
+    }
+    const uint32_t done = head + (vecs << 4);
+    if (lane < n - done) dst[done + lane] = s[done + lane];
+}
+
+__global__ void __launch_bounds__(1024) gather_host_segments_kernel(const b2c_iovec* __restrict__ segs,
+                                                                     const uint32_t* __restrict__ seg_begin,
+                                                                     const uint64_t* __restrict__ off, uint32_t cnt,
+                                                                     uint8_t* __restrict__ d_in, const uint32_t kGatherChunk) {
+    extern __shared__ __align__(16) uint8_t gather_smem[];
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t warps = gridDim.x * (blockDim.x >> 5);
-    for (uint32_t m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); m < cnt; m += warps) {
+    const uint32_t kGatherWarps = blockDim.x >> 5;
+    uint8_t* buf = gather_smem + (size_t)(threadIdx.x >> 5) * (kGatherChunk + kGatherSlack);
+    uint4* buf4 = reinterpret_cast<uint4*>(buf);
+    const uint32_t warps = gridDim.x * kGatherWarps;
+    for (uint32_t m = blockIdx.x * kGatherWarps + (threadIdx.x >> 5); m < cnt; m += warps) {
         uint8_t* dst = d_in + off[m];
         for (uint32_t q = seg_begin[m]; q < seg_begin[m + 1]; q++) {
             const uint8_t* src = static_cast<const uint8_t*>(segs[q].iov_base);
-            const uint32_t len = (uint32_t)segs[q].iov_len;
-            const uint32_t rel = (uint32_t)((reinterpret_cast<uintptr_t>(src) ^ reinterpret_cast<uintptr_t>(dst)) & 15);
-            if (rel == 0) {
-                // same phase modulo 16 (the arena is laid out so that a message's first block always is):
-                // every host byte crosses PCIe exactly once, in 16-byte pieces
-                uint32_t head = (16u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15)) & 15u;
-                if (head > len) head = len;
-                if (lane < head) dst[lane] = src[lane];
-                const uint32_t vecs = (len - head) >> 4;
-                const uint4* s4 = reinterpret_cast<const uint4*>(src + head);
-                uint4* d4 = reinterpret_cast<uint4*>(dst + head);
-                for (uint32_t i = lane; i < vecs; i += 32) d4[i] = s4[i];
-                const uint32_t done = head + (vecs << 4);
-                if (lane < len - done) dst[done + lane] = src[done + lane];
-            } else if ((rel & 3) == 0) {
-                uint32_t head = (4u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 3)) & 3u;
-                if (head > len) head = len;
-                if (lane < head) dst[lane] = src[lane];
-                const uint32_t words = (len - head) >> 2;
-                const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src + head);
-                uint32_t* d32 = reinterpret_cast<uint32_t*>(dst + head);
-                for (uint32_t i = lane; i < words; i += 32) d32[i] = s32[i];
-                const uint32_t done = head + (words << 2);
-                if (lane < len - done) dst[done + lane] = src[done + lane];
-            } else {
-                // word stores aligned to the destination, words assembled from the unaligned source
-                uint32_t head = (4u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 3)) & 3u;
-                if (head > len) head = len;
-                if (lane < head) dst[lane] = src[lane];
-                const uint32_t words = (len - head) >> 2;
-                uint32_t* d32 = reinterpret_cast<uint32_t*>(dst + head);
-                for (uint32_t i = lane; i < words; i += 32) d32[i] = ld32u(src + head + 4 * (size_t)i);
-                const uint32_t done = head + (words << 2);
-                if (lane < len - done) dst[done + lane] = src[done + lane];
+            const uint64_t len = segs[q].iov_len;
+            for (uint64_t c0 = 0; c0 < len; c0 += kGatherChunk) {
+                const uint8_t* cs = src + c0;
+                const uint32_t cl = (uint32_t)(len - c0 < kGatherChunk ? len - c0 : kGatherChunk);
+                const uint32_t lead = (uint32_t)(reinterpret_cast<uintptr_t>(cs) & 15);
+                const uint4* s4 = reinterpret_cast<const uint4*>(cs - lead);
+                const uint32_t nv = (lead + cl + 15) >> 4;  // every vector holds at least one byte of the block
+                uint32_t i = lane;
+                for (; i + 96 < nv; i += 128) {  // four independent requests per lane in flight
+                    const uint4 v0 = __ldg(s4 + i), v1 = __ldg(s4 + i + 32), v2 = __ldg(s4 + i + 64), v3 = __ldg(s4 + i + 96);
+                    buf4[i] = v0, buf4[i + 32] = v1, buf4[i + 64] = v2, buf4[i + 96] = v3;
+                }
+                for (; i < nv; i += 32) buf4[i] = __ldg(s4 + i);
+                __syncwarp();
+                smem_to_global(dst, buf + lead, cl, lane);
+                __syncwarp();
+                dst += cl;
             }
-            dst += len;
         }
     }
 }
@@ -458,8 +477,18 @@ __global__ void __launch_bounds__(256) gather_host_segments_kernel(const b2c_iov
 int launch_gather_host(b2c_ctx* ctx, Lane& lane, const b2c_iovec* d_segs, const uint32_t* d_seg_begin,
                        const uint64_t* d_off, uint32_t cnt, uint8_t* d_in) {
     if (!cnt) return B2C_OK;
-    const uint32_t blocks = std::min<uint32_t>((cnt + 7) / 8, (uint32_t)ctx->num_sms * 4);
-    gather_host_segments_kernel<<<blocks, 256, 0, lane.stream>>>(d_segs, d_seg_begin, d_off, cnt, d_in);
+    const uint32_t kGatherWarps = (uint32_t)ctx->gather_warps, chunk = (uint32_t)ctx->gather_chunk;
+    const size_t smem = (size_t)kGatherWarps * (chunk + kGatherSlack);
+    if (!ctx->gather_attr_done) {
+        B2C_CUDA(ctx, cudaFuncSetAttribute(gather_host_segments_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        // same L1 / shared-memory split as the codec kernels it has to run beside: an SM does not change its
+        // carve-out while CTAs are resident, so a kernel that prefers another split waits for the SM to drain
+        B2C_CUDA(ctx, cudaFuncSetAttribute(gather_host_segments_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                           cudaSharedmemCarveoutMaxShared));
+        ctx->gather_attr_done = true;
+    }
+    const uint32_t blocks = std::min<uint32_t>((cnt + kGatherWarps - 1) / kGatherWarps, (uint32_t)ctx->num_sms * (uint32_t)ctx->gather_ctas_per_sm);
+    gather_host_segments_kernel<<<blocks, 32 * kGatherWarps, smem, lane.stream>>>(d_segs, d_seg_begin, d_off, cnt, d_in, chunk);
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
     return B2C_OK;
@@ -520,6 +549,9 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     if (const char* s = getenv("B2C_WINDOW")) ctx->window_mask = atoi(s);
     if (const char* s = getenv("B2C_WINDOW_STAGE")) ctx->window_stage = atoi(s) != 0;
     if (const char* s = getenv("B2C_WINDOW_SMEM64")) ctx->window_smem64 = atoi(s) != 0;
+    if (const char* s = getenv("B2C_GATHER_CTAS")) ctx->gather_ctas_per_sm = std::max(1, atoi(s));
+    if (const char* s = getenv("B2C_GATHER_WARPS")) ctx->gather_warps = std::min(32, std::max(1, atoi(s)));
+    if (const char* s = getenv("B2C_GATHER_CHUNK")) ctx->gather_chunk = std::min(8192, std::max(512, atoi(s) / 16 * 16));
     if (const char* s = getenv("B2C_LOCKSTEP")) ctx->small_lockstep = atoi(s) != 0;
     if (const char* s = getenv("B2C_LOCKSTEP_LPW")) {
         const int v = atoi(s);
@@ -858,26 +890,56 @@ int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, u
     if (p.len.size() < n) p.len.resize(n);
     std::atomic<bool> too_long(false);
     const bool zc = ctx->input_pinned;
-    auto staged_size = [](uint32_t l) -> uint64_t { return l >= 256 ? align_up(l, 64) : align_up(l, 16); };
+    // zero-copy: a message gets the same phase modulo 16 as its first block has in host memory (so that block moves
+    // in whole aligned 16-byte pieces), i.e. `skew` bytes of slack in front of it
+    auto skew_of = [&](uint32_t i) -> uint32_t {
+        return zc && seg_begin[i] < seg_begin[i + 1] ? (uint32_t)(reinterpret_cast<uintptr_t>(segs[seg_begin[i]].iov_base) & 15) : 0u;
+    };
+    auto staged_size = [&](uint32_t i, uint32_t l) -> uint64_t {
+        if (zc) return align_up((uint64_t)skew_of(i) + l, 16);
+        return l >= 256 ? align_up(l, 64) : align_up(l, 16);
+    };
     uint64_t part[64] = {0};
     unsigned used = 1;
+    std::atomic<bool> pageable(false);
     pool(ctx).run(threads_for((uint64_t)n * 64), [&](unsigned t, unsigned T) {
         if (t == 0) used = T;
         uint32_t lo = (uint32_t)((uint64_t)n * t / T), hi = (uint32_t)((uint64_t)n * (t + 1) / T);
         uint64_t sum = 0;
+        // zero-copy: the kernel will dereference every block, and a pageable one is a fatal device fault, so each
+        // 2 MiB region a block touches is looked up once per thread (cudaPointerGetAttributes) and remembered
+        uint64_t seen[64];
+        for (auto& x : seen) x = ~0ull;
+        auto pinned_region = [&](uintptr_t a) {
+            const uint64_t r = (uint64_t)a >> 21;
+            uint64_t& slot = seen[(r * 0x9e3779b97f4a7c15ull) >> 58];
+            if (slot == r) return;
+            if (!is_pinned_host(reinterpret_cast<const void*>(a))) pageable = true;
+            slot = r;
+        };
         for (uint32_t i = lo; i < hi; i++) {
             uint64_t l = 0;
             for (uint32_t s = seg_begin[i]; s < seg_begin[i + 1]; s++) l += segs[s].iov_len;
+            if (zc)
+                for (uint32_t s = seg_begin[i]; s < seg_begin[i + 1]; s++)
+                    if (segs[s].iov_len) {
+                        const uintptr_t a = reinterpret_cast<uintptr_t>(segs[s].iov_base);
+                        pinned_region(a);
+                        pinned_region(a + segs[s].iov_len - 1);
+                    }
             if (l > 0xffffffffull) {
                 too_long = true;
                 l = 0;
             }
             p.len[i] = (uint32_t)l;
-            sum += staged_size((uint32_t)l);
+            sum += staged_size(i, (uint32_t)l);
         }
         part[t] = sum;
     });
     if (too_long) return set_err(ctx, B2C_E_ARG, "message longer than 4 GiB - 1", cudaSuccess);
+    if (pageable)
+        return set_err(ctx, B2C_E_ARG, "B2C_OPT_INPUT_PINNED is set but an input block is not in page-locked host memory",
+                       cudaSuccess);
     // Slab size: ~32 MiB keeps gather, copies and kernels of different slabs overlapped; batches of large messages get
     // up to 128 MiB, because a 64 KiB fragment occupies a warp for milliseconds and a 32 MiB slab holds only 512 of them
     // (measured end to end, 32 -> 128 MiB: C5 10.4 -> 15.2, C4 8.3 -> 13.1 GB/s).  B2C_SLAB_MB fixes the size.
@@ -888,7 +950,7 @@ int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, u
         target = std::min<uint64_t>(128ull << 20, std::max<uint64_t>(target, total / n * 8192));
     }
     const uint32_t max_msgs = 1u << 18;
-    if (!zc) {
+    {
         uint64_t base[65];
         base[0] = 0;
         for (unsigned t = 0; t < used; t++) base[t + 1] = base[t] + part[t];
@@ -898,7 +960,7 @@ int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, u
             uint64_t pos = base[t];
             for (uint32_t i = lo; i < hi; i++) {
                 g[i] = pos;
-                pos += staged_size(p.len[i]);
+                pos += staged_size(i, p.len[i]);
             }
         });
         g[n] = base[used];
@@ -918,7 +980,7 @@ int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, u
                 const uint64_t start = g[slabs[k].m0];
                 uint64_t payload = 0;
                 for (uint32_t i = slabs[k].m0; i < slabs[k].m1; i++) {
-                    g[i] -= start;
+                    g[i] = g[i] - start + skew_of(i);
                     payload += p.len[i];
                 }
                 slabs[k].payload = payload;
@@ -927,26 +989,6 @@ int plan_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, u
         for (const Slab& sl : slabs) p.payload += sl.payload;
         return B2C_OK;
     }
-    Slab cur = {0, 0, 0, 0};
-    for (uint32_t i = 0; i < n; i++) {
-        // zero-copy: give the message the same phase modulo 16 as its first block has in host memory, so the
-        // device-side gather moves whole aligned 16-byte pieces over PCIe
-        const uint32_t skew = seg_begin[i] < seg_begin[i + 1]
-                                  ? (uint32_t)(reinterpret_cast<uintptr_t>(segs[seg_begin[i]].iov_base) & 15)
-                                  : 0u;
-        const uint64_t a = align_up((uint64_t)skew + p.len[i], 16);
-        if (cur.m1 > cur.m0 && (cur.bytes + a > target || cur.m1 - cur.m0 >= max_msgs)) {
-            p.slabs.push_back(cur);
-            cur = {i, i, 0, 0};
-        }
-        p.off[i] = cur.bytes + skew;
-        cur.bytes += a;
-        cur.payload += p.len[i];
-        cur.m1 = i + 1;
-        p.payload += p.len[i];
-    }
-    if (cur.m1 > cur.m0) p.slabs.push_back(cur);
-    return B2C_OK;
 }
 
 // memcpy every segment of the slab's messages into pinned staging.  When `caps` is given the
@@ -1165,7 +1207,7 @@ int b2c_crc32c_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_be
         const uint32_t cnt = s.m1 - s.m0;
         Prep& P = prep[k & 1];
         if (ctx->input_pinned) {
-            P.lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, nullptr);
+            P.lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx);
         } else {
             PlanStats a, b;
             stats[k & 1].merged(a, b);
@@ -1294,6 +1336,15 @@ static int compress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint32
         size_t meta_bytes = 0, out_meta_bytes = 0, off_at = 0;
         uint64_t cap = 0;
     } prep[2];
+    const bool timeline = getenv("B2C_TIMELINE") != nullptr;
+    std::vector<cudaEvent_t> tl;
+    auto tl_mark = [&](cudaStream_t st) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) == cudaSuccess) {
+            cudaEventRecord(e, st);
+            tl.push_back(e);
+        }
+    };
     std::unique_ptr<SlabStats[]> stats(new SlabStats[2]);
     PoolGuard guard{ctx};
     auto layout = [&](size_t k) {  // size the layout: from the workers' statistics once the gather is through
@@ -1301,7 +1352,7 @@ static int compress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint32
         const uint32_t cnt = s.m1 - s.m0;
         Prep& P = prep[k & 1];
         if (ctx->input_pinned) {
-            P.lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, nullptr);
+            P.lp.plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx);
         } else {
             PlanStats a, b;
             stats[k & 1].merged(a, b);
@@ -1328,12 +1379,30 @@ static int compress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint32
             gather_slab_start(ctx, segs, seg_begin, bp, s, static_cast<uint8_t*>(lane.h_in.p), nullptr, &stats[k & 1]);
         return B2C_OK;
     };
+    // Can slab k's gather start before the slab that used its lane last (k - 4) has been retired?  Its staging is free
+    // (that slab's sizes were read two iterations ago, so its H2D copy is long done); what must not happen is a
+    // buffer of the lane being re-allocated under the retiring slab, so every capacity has to suffice already.
+    auto fits = [&](size_t k) -> bool {
+        const Lane& lane = ctx->pipe[k % kPipeLanes];
+        const Slab& s = bp.slabs[k];
+        const uint32_t cnt = s.m1 - s.m0;
+        const size_t meta_at = align_up(s.bytes, 256);
+        const size_t meta_total = align_up(LayoutPlan::max_blob_bytes(cnt, s.payload), 256);
+        const uint64_t cap = s.payload + s.payload / 6 + 37ull * cnt;
+        const size_t out_meta = ((size_t)cnt + 1) * 8 + (crc ? (size_t)cnt * 4 : 0);
+        return meta_at + meta_total + 64 <= lane.d_in.cap && meta_at + meta_total + 64 <= lane.h_in.cap &&
+               align_up(cap, 256) + out_meta + 64 <= lane.d_out.cap && align_up(out_meta, 256) + 64 <= lane.h_out.cap;
+    };
     if ((rc = prepare(0))) return rc;
     for (size_t k = 0; k < K + 3; k++) {
         if (k < K) TIMED(tr.gather, pool(ctx).wait());
-        if (k >= 3 && k - 3 < K && (rc = finish(k - 3))) return rc;  // frees slab k+1's lane; the pool is idle here
+        // keep the gathering threads busy: slab k+1's gather starts before this thread retires slab k-3, when nothing
+        // has to grow (outputs DMA'd straight into the caller's page-locked buffer, so retiring needs no pool either)
+        const bool early = k + 1 < K && direct && !ctx->input_pinned && fits(k + 1);
+        if (early && (rc = prepare(k + 1))) return rc;
+        if (k >= 3 && k - 3 < K && (rc = finish(k - 3))) return rc;  // frees slab k+1's lane
         if (k < K) {
-            if (k + 1 < K && (rc = prepare(k + 1))) return rc;
+            if (k + 1 < K && !early && (rc = prepare(k + 1))) return rc;
             Lane& lane = ctx->pipe[k % kPipeLanes];
             const Slab& s = bp.slabs[k];
             const uint32_t cnt = s.m1 - s.m0;
@@ -1344,12 +1413,15 @@ static int compress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint32
             uint8_t* d_in = P.io.d_in;
             LayoutView lv;
             P.lp.bind(d_in + P.io.meta_at, &lv);
+            if (timeline) tl_mark(lane.stream);
             if ((rc = slab_submit(ctx, lane, segs, seg_begin, s, P.io, P.meta_bytes, lv.d_off, h2d))) return rc;
+            if (timeline) tl_mark(lane.stream);
             uint8_t* d_out = static_cast<uint8_t*>(lane.d_out.p);
             uint64_t* d_out_off = reinterpret_cast<uint64_t*>(d_out + P.off_at);
             if (crc && (rc = launch_crc32c(ctx, lane, lv, d_in, nullptr, reinterpret_cast<uint32_t*>(d_out_off + cnt + 1))))
                 return rc;
             if ((rc = launch_compress(ctx, lane, lv, d_in, d_out, P.cap, d_out_off))) return rc;
+            if (timeline) tl_mark(lane.stream);
             B2C_CUDA(ctx, cudaMemcpyAsync(lane.h_out.p, d_out_off, P.out_meta_bytes, cudaMemcpyDeviceToHost, lane.stream));
             d2h += P.out_meta_bytes;
             B2C_CUDA(ctx, cudaEventRecord(lane.ev_meta, lane.stream));
@@ -1360,6 +1432,17 @@ static int compress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint32
     ctx->last_h2d = h2d;
     ctx->last_d2h = d2h;
     tr.report(K, bp.payload);
+    if (timeline) {  // B2C_TIMELINE=1: when each slab's input transfer and kernels ran on the GPU, relative to the first mark
+        for (size_t i = 0; i + 2 < tl.size(); i += 3) {
+            float a = 0, b = 0, c = 0;
+            cudaEventSynchronize(tl[i + 2]);
+            cudaEventElapsedTime(&a, tl[0], tl[i]);
+            cudaEventElapsedTime(&b, tl[0], tl[i + 1]);
+            cudaEventElapsedTime(&c, tl[0], tl[i + 2]);
+            fprintf(stderr, "[b2c timeline] slab %2zu  input %7.3f .. %7.3f  kernels .. %7.3f ms\n", i / 3, a, b, c);
+        }
+        for (cudaEvent_t e : tl) cudaEventDestroy(e);
+    }
     return B2C_OK;
 }
 
@@ -1461,7 +1544,7 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
         if (caps.size() < cnt) caps.resize(cnt);
         // output slot sizes come from the (lenient) preambles
         if (ctx->input_pinned) {
-            TIMED(tr.layout, lin_ring[k & 1].plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, nullptr));
+            TIMED(tr.layout, lin_ring[k & 1].plan(cnt, bp.off.data() + s.m0, bp.len.data() + s.m0, ctx));
             TIMED(tr.gather, slab_caps(ctx, segs, seg_begin, bp, s, caps.data()));
         } else {  // read by the gathering threads while the bytes are in their cache
             int r;
@@ -1472,11 +1555,24 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
         }
         return B2C_OK;
     };
+    // as in the compress pipeline: slab k+1's gather may start before slab k-3 is retired when its staging need not grow
+    auto fits = [&](size_t k) -> bool {
+        const Slab& s = bp.slabs[k];
+        const uint32_t cnt = s.m1 - s.m0;
+        return align_up(s.bytes, 256) + 2 * LayoutPlan::max_blob_bytes(cnt, s.payload) + (size_t)cnt * 16 + 4096 <=
+               ctx->pipe[k % kPipeLanes].h_in.cap;
+    };
     if ((rc = prepare(0))) return rc;
     for (size_t k = 0; k < K; k++) {
         TIMED(tr.gather, pool(ctx).wait());
+        const bool early = k + 1 < K && direct && !ctx->input_pinned && fits(k + 1);
+        if (early) {
+            // the lane's staging is free once the H2D copy of the slab that used it last has completed (ev_meta)
+            if (k + 1 >= (size_t)kPipeLanes) B2C_CUDA(ctx, cudaEventSynchronize(ctx->pipe[(k + 1) % kPipeLanes].ev_meta));
+            if ((rc = prepare(k + 1))) return rc;
+        }
         if (k + 1 >= (size_t)kPipeLanes && (rc = finish(k + 1 - kPipeLanes))) return rc;  // frees slab k+1's lane
-        if (k + 1 < K && (rc = prepare(k + 1))) return rc;
+        if (k + 1 < K && !early && (rc = prepare(k + 1))) return rc;
         Lane& lane = ctx->pipe[k % kPipeLanes];
         const Slab& s = bp.slabs[k];
         const uint32_t cnt = s.m1 - s.m0;
@@ -1519,7 +1615,7 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
         }
         LayoutPlan lout;
         if (ctx->input_pinned || clamped) {
-            lout.plan(cnt, o_off.data(), o_cap.data(), nullptr);
+            lout.plan(cnt, o_off.data(), o_cap.data(), ctx);
         } else {  // the workers summed everything but the end of the arena, which is the running total
             st_out.arena_end = pos;
             lout.plan_with(cnt, o_off.data(), o_cap.data(), st_out);
@@ -1542,6 +1638,7 @@ static int decompress_batch_impl(b2c_ctx* ctx, const b2c_iovec* segs, const uint
         lin.bind(d_in + io.meta_at, &vin);
         lout.bind(d_in + io.meta_at + blob_out_rel, &vout);
         if ((rc = slab_submit(ctx, lane, segs, seg_begin, s, io, meta_bytes, vin.d_off, h2d))) return rc;
+        B2C_CUDA(ctx, cudaEventRecord(lane.ev_meta, lane.stream));  // the staging has been read
         uint8_t* d_out = static_cast<uint8_t*>(lane.d_out.p);
         int32_t* d_status = reinterpret_cast<int32_t*>(d_out + st_at);
         if (masked_crc) {

@@ -137,6 +137,9 @@ struct b2c_ctx {
     bool lift_scan = true;           // B2C_LIFT_SCAN=0: find the 64 KiB block boundaries with the tag-by-tag scan
     bool block_decode = true;        // B2C_BLOCK_DECODE=0: never split large streams into 64 KiB blocks
     bool ring_attr_done = false;
+    bool gather_attr_done = false;
+    int gather_warps = 8, gather_chunk = 2048;  // B2C_GATHER_WARPS / B2C_GATHER_CHUNK: warps per CTA and bytes per round and warp
+    int gather_ctas_per_sm = 1;  // B2C_GATHER_CTAS: CTAs per SM of the device-side gather of pinned input blocks
     bool batch_decode = true;        // B2C_BATCH_DECODE=0: one tag per step in the warp decoder
     bool batch_decode_small = false; // B2C_BATCH_DECODE_SMALL=1: <=1 KiB slots use the warp batch decoder, not one lane per stream
     bool nt_gather = true;  // B2C_NT_GATHER=0: plain memcpy into staging

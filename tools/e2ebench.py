@@ -1,0 +1,57 @@
+#!/usr/bin/env python
+"""End-to-end (host buffers in, host buffers out) timing of the sender / receiver calls alone, back to back and
+overlapped on two threads, for one workload shape -- a tuning aid for the slab pipeline (bench.py is the contract).
+
+  [B2C_TRACE=1] [B2C_SLAB_MB=..] python tools/e2ebench.py [--workload c2] [--threads N] [--steps K] [--tag NAME]"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+import brpc_b200  # noqa: E402
+from oracle import oracle as O  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--corpus", default="words")
+    ap.add_argument("--bytes", type=int, default=1 << 30)
+    ap.add_argument("--messages", type=int, default=1 << 20)
+    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--threads", type=int, default=0, help="host threads per ctx (0 = library default)")
+    ap.add_argument("--over-threads", type=int, default=0, help="host threads per ctx in the overlapped run (0 = cores / 2)")
+    ap.add_argument("--pinned", action="store_true", help="input blocks in page-locked memory + B2C_OPT_INPUT_PINNED")
+    ap.add_argument("--tag", default="")
+    a = ap.parse_args()
+    arena, off, ln = O.corpus_batch(a.corpus, bench.workload_lengths(a))
+    s, r = brpc_b200.Codec(0), brpc_b200.Codec(0)
+    B = bench.DeviceBatch(s, arena, off, ln, f"{a.workload}/{a.corpus}")
+    H = bench.HostBatch(s, r, B, a.workload, 0, pinned_inputs=a.pinned)
+    for c in (s, r):
+        c.set_option(c.OPT_HOST_THREADS, a.threads)
+    H.send(), H.recv()
+    H.check()
+
+    def timed(fn):
+        t0 = time.perf_counter()
+        for _ in range(a.steps):
+            fn()
+        return (time.perf_counter() - t0) / a.steps * 1e3
+
+    send_ms, recv_ms = timed(H.send), timed(H.recv)
+    over = H.time_overlapped(a.steps, None, a.over_threads or max(2, (os.cpu_count() or 2) // 2)) / a.steps * 1e3
+    gb = B.payload / 1e9
+    print(json.dumps({"tag": a.tag, "workload": a.workload, "corpus": a.corpus, "threads": a.threads, "pinned_inputs": a.pinned,
+                      "send_ms": round(send_ms, 2), "recv_ms": round(recv_ms, 2), "serial_gbs": round(gb / (send_ms + recv_ms) * 1e3, 2),
+                      "overlapped_ms": round(over, 2), "overlapped_gbs": round(gb / over * 1e3, 2)}), flush=True)
+
+
+if __name__ == "__main__":
+    main()
