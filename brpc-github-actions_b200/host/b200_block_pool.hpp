@@ -19,6 +19,7 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <mutex>
 #include <unordered_map>
 #include <vector>
@@ -47,10 +48,30 @@ public:
     void Deallocate(void* p);   // p from Allocate of this pool
     bool Owns(const void* p) const;
     Stats stats() const;
+
+    // ---- result slabs ------------------------------------------------------------------------------------------
+    // One page-locked buffer that the results of a whole BATCH are DMA'd into; every result is then handed to its
+    // owner as a slice of it, which an IOBuf adopts without a copy:
+    //     out->append_user_data_with_meta(slice.data, slice.size, slice.deleter, slice.meta);   // iobuf.cpp:1216-1240
+    // (meta = the slab's base address, as the RDMA transport stores its registration key there,
+    // src/brpc/rdma/rdma_helper.cpp:528-531).  The slab goes back to the pool's slab cache when the batch's creator
+    // and every slice have let go of it, in whatever order and on whatever thread.  Slabs are cached and re-used:
+    // page-locking memory costs about a millisecond.
+    struct Slice {
+        char* data = nullptr;
+        size_t size = 0;
+        void (*deleter)(void*) = nullptr;  // call with `data` when done (IOBuf's user-data deleter signature)
+        uint64_t meta = 0;
+    };
+    char* SlabAcquire(size_t bytes);              // page-locked, >= bytes; nullptr when it cannot be had
+    Slice SlabSlice(char* slab, size_t at, size_t n);  // adds a reference
+    void SlabRelease(char* slab);                 // the creator's reference
+    static void ReleaseSlice(void* data);         // Slice::deleter: finds the slab that holds `data`
+    size_t slabs_live() const;                    // acquired and not yet fully released
     void flush_cache(std::vector<void*>& cache, size_t keep);  // thread caches -> shared list (used at thread exit)
 
-    // The process-wide pool behind the two hook functions (created on first use on the calling thread's
-    // Context::local() device, 8192-byte blocks).
+    // The process-wide pool behind the two hook functions (created on first use with a context of its own on
+    // Context::default_device(), 8192-byte blocks).
     static PinnedBlockPool& global();
     static void* blockmem_allocate(size_t n);
     static void blockmem_deallocate(void* p);
@@ -69,6 +90,14 @@ private:
     std::vector<void*> free_;                     // shared free list
     std::unordered_map<void*, size_t> big_;       // oversize allocations
     Stats st_;
+    std::atomic<uint64_t> allocs_{0}, frees_{0};  // counted without the pool mutex: the thread caches exist to avoid it
+    struct SlabRec {
+        char* base;
+        size_t cap;
+    };
+    std::vector<SlabRec> slab_free_;              // cached slabs, any sizes
+    size_t slabs_live_ = 0;
+    void slab_retire(char* base, size_t cap);
     const uint64_t id_;                           // distinguishes pools in the per-thread cache
 };
 

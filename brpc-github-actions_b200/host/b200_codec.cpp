@@ -5,6 +5,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
+#include <memory>
 #include <stdexcept>
 
 namespace b200 {
@@ -55,12 +57,19 @@ Context::Context(int device) : ctx_(nullptr) {
 }
 Context::~Context() { b2c_ctx_destroy(ctx_); }
 
+static std::atomic<int> g_default_device{-1};
+void Context::set_default_device(int device) { g_default_device.store(device); }
+
+int Context::default_device() {
+    const int dev = g_default_device.load();
+    if (dev >= 0) return dev;
+    const char* d = getenv("B200_DEVICE");
+    return d ? atoi(d) : 0;
+}
+
 Context& Context::local() {
-    static thread_local Context* c = nullptr;
-    if (!c) {
-        const char* d = getenv("B200_DEVICE");
-        c = new Context(d ? atoi(d) : 0);
-    }
+    static thread_local std::unique_ptr<Context> c;  // streams, staging and workspaces go when the thread ends
+    if (!c) c.reset(new Context(default_device()));
     return *c;
 }
 
@@ -252,6 +261,95 @@ bool IsValidCompressedBuffer(const char* compressed, size_t n) {
     if (ulen > (uint64_t)n * 64 / 3 + 64) return false;
     std::vector<char> tmp(ulen ? ulen : 1);
     return RawUncompress(compressed, n, tmp.data());
+}
+
+// ---- Source / Sink ------------------------------------------------------------------------------------------
+Sink::~Sink() {}
+Source::~Source() {}
+char* Sink::GetAppendBuffer(size_t, char* scratch) { return scratch; }
+char* Sink::GetAppendBufferVariable(size_t, size_t, char* scratch, size_t scratch_size, size_t* allocated_size) {
+    *allocated_size = scratch_size;
+    return scratch;
+}
+void Sink::AppendAndTakeOwnership(char* bytes, size_t n, void (*deleter)(void*, const char*, size_t), void* deleter_arg) {
+    Append(bytes, n);
+    (*deleter)(deleter_arg, bytes, n);
+}
+void UncheckedByteArraySink::Append(const char* data, size_t n) {
+    if (data != dest_) memcpy(dest_, data, n);  // GetAppendBuffer handed out dest_ itself
+    dest_ += n;
+}
+void UncheckedByteArraySink::AppendAndTakeOwnership(char* bytes, size_t n, void (*deleter)(void*, const char*, size_t),
+                                                    void* deleter_arg) {
+    if (bytes != dest_) {
+        memcpy(dest_, bytes, n);
+        (*deleter)(deleter_arg, bytes, n);
+    }
+    dest_ += n;
+}
+
+namespace {
+std::string drain(Source* s) {
+    std::string all;
+    all.reserve(s->Available());
+    for (;;) {
+        size_t len = 0;
+        const char* p = s->Peek(&len);
+        if (len == 0) break;
+        all.append(p, len);
+        s->Skip(len);
+    }
+    return all;
+}
+}  // namespace
+
+size_t Compress(Source* source, Sink* sink) {
+    const std::string in = drain(source);
+    std::string out;
+    Compress(in.data(), in.size(), &out);
+    sink->Append(out.data(), out.size());
+    return out.size();
+}
+
+bool GetUncompressedLength(Source* source, uint32_t* result) {
+    // SnappyDecompressor::ReadUncompressedLength (snappy.cc:692-711): one byte at a time, lenient about the last byte
+    *result = 0;
+    uint32_t shift = 0;
+    for (;;) {
+        if (shift >= 32) return false;
+        size_t n = 0;
+        const char* ip = source->Peek(&n);
+        if (n == 0) return false;
+        const unsigned char c = *reinterpret_cast<const unsigned char*>(ip);
+        source->Skip(1);
+        *result |= static_cast<uint32_t>(c & 0x7f) << shift;
+        if (c < 128) return true;
+        shift += 7;
+    }
+}
+
+bool Uncompress(Source* compressed, Sink* uncompressed) {
+    const std::string in = drain(compressed);
+    uint32_t ulen = 0;
+    if (!b2c_snappy_read_preamble(in.data(), in.size(), &ulen)) return false;
+    if (ulen > (uint64_t)in.size() * 64 / 3 + 64) return false;  // no valid stream expands more than 64/3 times
+    // like the reference, decode into the sink's own buffer when it offers one large enough (snappy.cc:1536-1545)
+    char c;
+    size_t allocated = 0;
+    char* buf = uncompressed->GetAppendBufferVariable(1, ulen, &c, 1, &allocated);
+    std::string own;
+    if (allocated < ulen) {
+        own.resize(ulen ? ulen : 1);
+        buf = &own[0];
+    }
+    if (!RawUncompress(in.data(), in.size(), buf)) return false;
+    uncompressed->Append(buf, ulen);
+    return true;
+}
+
+bool IsValidCompressed(Source* compressed) {
+    const std::string in = drain(compressed);
+    return IsValidCompressedBuffer(in.data(), in.size());
 }
 
 }  // namespace snappy

@@ -26,8 +26,11 @@ public:
     Context(const Context&) = delete;
     Context& operator=(const Context&) = delete;
     b2c_ctx* get() const { return ctx_; }
-    // per-thread default context on device $B200_DEVICE (default 0)
+    // this thread's default context (created on first use, destroyed when the thread ends), on the device chosen
+    // with set_default_device (else $B200_DEVICE, else 0)
     static Context& local();
+    static void set_default_device(int device);
+    static int default_device();
 
 private:
     b2c_ctx* ctx_;
@@ -47,6 +50,79 @@ bool Uncompress(const char* compressed, size_t n, std::string* uncompressed);   
 bool IsValidCompressedBuffer(const char* compressed, size_t n);                      // snappy.h:190
 // snappy.h:168-171: the decoded bytes fill iov[0], iov[1], ... in order; false when they do not fit
 bool RawUncompressToIOVec(const char* compressed, size_t n, const struct ::b2c_iovec* iov, size_t iov_cnt);
+
+// The streaming abstraction of the reference (src/butil/third_party/snappy/snappy-sinksource.h:38-181), same
+// virtual interfaces and default behaviours (snappy-sinksource.cc:36-104), so that a caller that holds a Source* or
+// implements a Sink (butil::IOBufAsSnappySource / IOBufAsSnappySink, src/butil/iobuf.h:596-634) ports by renaming
+// the namespace.
+class Sink {
+public:
+    Sink() {}
+    virtual ~Sink();
+    virtual void Append(const char* bytes, size_t n) = 0;
+    virtual char* GetAppendBuffer(size_t length, char* scratch);  // default: scratch
+    virtual void AppendAndTakeOwnership(char* bytes, size_t n, void (*deleter)(void*, const char*, size_t),
+                                        void* deleter_arg);  // default: Append, then the deleter
+    virtual char* GetAppendBufferVariable(size_t min_size, size_t desired_size_hint, char* scratch, size_t scratch_size,
+                                          size_t* allocated_size);  // default: scratch
+
+private:
+    Sink(const Sink&);
+    void operator=(const Sink&);
+};
+class Source {
+public:
+    Source() {}
+    virtual ~Source();
+    virtual size_t Available() const = 0;
+    virtual const char* Peek(size_t* len) = 0;
+    virtual void Skip(size_t n) = 0;
+
+private:
+    Source(const Source&);
+    void operator=(const Source&);
+};
+class ByteArraySource : public Source {
+public:
+    ByteArraySource(const char* p, size_t n) : ptr_(p), left_(n) {}
+    size_t Available() const override { return left_; }
+    const char* Peek(size_t* len) override {
+        *len = left_;
+        return ptr_;
+    }
+    void Skip(size_t n) override {
+        left_ -= n;
+        ptr_ += n;
+    }
+
+private:
+    const char* ptr_;
+    size_t left_;
+};
+class UncheckedByteArraySink : public Sink {
+public:
+    explicit UncheckedByteArraySink(char* dest) : dest_(dest) {}
+    void Append(const char* data, size_t n) override;
+    char* GetAppendBuffer(size_t len, char* scratch) override { return dest_; }
+    char* GetAppendBufferVariable(size_t min_size, size_t desired_size_hint, char* scratch, size_t scratch_size,
+                                  size_t* allocated_size) override {
+        *allocated_size = desired_size_hint;
+        return dest_;
+    }
+    void AppendAndTakeOwnership(char* bytes, size_t n, void (*deleter)(void*, const char*, size_t), void* deleter_arg) override;
+    char* CurrentDestination() const { return dest_; }
+
+private:
+    char* dest_;
+};
+// snappy.h:63-104 on the streaming types.  The Source is consumed to its end, as the reference does; what it
+// yields is handed to the GPU as a block list (a piece returned by Peek is copied only when the Source gives no
+// promise that it stays valid after Skip, i.e. always here: one host pass, the reference's scratch copies
+// included).  Compress returns the bytes written; Uncompress reads the preamble leniently (snappy.cc:692-711).
+size_t Compress(Source* source, Sink* sink);
+bool Uncompress(Source* compressed, Sink* uncompressed);
+bool GetUncompressedLength(Source* source, uint32_t* result);  // consumes the preamble, snappy.cc:870-873
+bool IsValidCompressed(Source* compressed);
 }  // namespace snappy
 
 namespace crc32c {

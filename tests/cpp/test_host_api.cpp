@@ -358,6 +358,112 @@ static void fused_and_iovec_calls() {
     for (size_t i = 0; i < bodies.size(); i++) CHECK(ok[i] && sinks[i] == bodies[i]);
 }
 
+// ---- Source / Sink (snappy-sinksource.h): the streaming forms, with a Source that yields small pieces and a Sink that
+// relies on the base class's defaults, as the reference's own chunked tests do ----
+namespace {
+class ChunkedSource : public b200::snappy::Source {
+public:
+    ChunkedSource(const std::string& s, size_t chunk) : s_(s), at_(0), chunk_(chunk) {}
+    size_t Available() const override { return s_.size() - at_; }
+    const char* Peek(size_t* len) override {
+        *len = std::min(chunk_, s_.size() - at_);
+        return s_.data() + at_;
+    }
+    void Skip(size_t n) override { at_ += n; }
+
+private:
+    const std::string& s_;
+    size_t at_, chunk_;
+};
+class StringSink : public b200::snappy::Sink {
+public:
+    std::string got;
+    void Append(const char* bytes, size_t n) override { got.append(bytes, n); }
+};
+}  // namespace
+
+static void source_sink() {
+    for (size_t n : {(size_t)0, (size_t)1, (size_t)14, (size_t)1000, (size_t)65536, (size_t)65537, (size_t)300000}) {
+        std::string body(n, '\0');
+        b2o_corpus_fill(B2O_WORDS, 900 + n, reinterpret_cast<uint8_t*>(&body[0]), n);
+        const std::string want = oracle_compress(body);
+        for (size_t chunk : {(size_t)7, (size_t)8160, (size_t)70000}) {
+            ChunkedSource src(body, chunk);
+            StringSink z;
+            CHECK(b200::snappy::Compress(&src, &z) == want.size());
+            CHECK(z.got == want && src.Available() == 0);
+            ChunkedSource zsrc(z.got, chunk);
+            StringSink back;
+            CHECK(b200::snappy::Uncompress(&zsrc, &back) && back.got == body);
+            ChunkedSource vsrc(z.got, chunk);
+            CHECK(b200::snappy::IsValidCompressed(&vsrc));
+            ChunkedSource lsrc(z.got, chunk);
+            uint32_t ulen = 0;
+            CHECK(b200::snappy::GetUncompressedLength(&lsrc, &ulen) && ulen == n);
+        }
+        // flat forms: ByteArraySource -> UncheckedByteArraySink (what RawCompress / RawUncompress are made of)
+        std::vector<char> flat(b200::snappy::MaxCompressedLength(n) + 8), out(n + 8);
+        b200::snappy::ByteArraySource bsrc(body.data(), n);
+        b200::snappy::UncheckedByteArraySink bsink(flat.data());
+        CHECK(b200::snappy::Compress(&bsrc, &bsink) == want.size());
+        CHECK(bsink.CurrentDestination() == flat.data() + want.size() && memcmp(flat.data(), want.data(), want.size()) == 0);
+        b200::snappy::ByteArraySource zsrc(flat.data(), want.size());
+        b200::snappy::UncheckedByteArraySink osink(out.data());
+        CHECK(b200::snappy::Uncompress(&zsrc, &osink) && memcmp(out.data(), body.data(), n) == 0);
+        if (want.size() > 6) {  // a truncated stream is refused
+            std::string cut = want.substr(0, want.size() - 2);
+            ChunkedSource csrc(cut, 100);
+            StringSink junk;
+            CHECK(!b200::snappy::Uncompress(&csrc, &junk));
+        }
+    }
+}
+
+// A GPU path that cannot run (here: a device that does not exist) must neither take the process down nor leave
+// callers waiting: every call completes, reports an infrastructure error, and the caller falls back.
+static void aggregator_survives_gpu_failure() {
+    b200::BatchAggregator::Options opt;
+    opt.device = 99;
+    b200::BatchAggregator agg(opt);
+    std::string body(5000, 'x'), z, back;
+    std::vector<std::thread> th;
+    std::atomic<int> bad(0);
+    for (int t = 0; t < 8; t++)
+        th.emplace_back([&] {
+            std::string out;
+            bool infra = false;
+            if (agg.Compress(blocks_of(body, 1000), &out, &infra) || !infra) bad++;
+            infra = false;
+            if (agg.Decompress(blocks_of(body, 1000), &out, &infra) || !infra) bad++;
+            infra = false;
+            if (agg.Crc32c(blocks_of(body, 1000), 0, &infra) != 0 || !infra) bad++;
+        });
+    for (auto& x : th) x.join();
+    CHECK(bad.load() == 0);
+    CHECK(agg.stats().failed_batches >= 3);
+}
+
+// Results of the aggregator are slices of page-locked result slabs; they are released exactly once, on any thread.
+static void aggregator_pooled_results() {
+    b200::BatchAggregator agg;
+    std::string body(30000, '\0');
+    b2o_corpus_fill(B2O_WORDS, 77, reinterpret_cast<uint8_t*>(&body[0]), body.size());
+    std::vector<b200::PinnedBlockPool::Slice> kept;
+    for (int i = 0; i < 20; i++) {
+        b200::OutSlice s;
+        CHECK(agg.Compress(blocks_of(body, 8160), &s));
+        CHECK(std::string(s.data(), s.size()) == oracle_compress(body));
+        CHECK(s.meta() != 0 && s.deleter() != nullptr);
+        if (i % 2) kept.push_back(s.adopt());  // as an IOBuf would: released later, elsewhere
+    }
+    std::thread([&] {
+        for (auto& k : kept) {
+            CHECK(std::string(k.data, k.size) == oracle_compress(body));
+            k.deleter(k.data);
+        }
+    }).join();
+}
+
 // ---- page-locked IOBuf block pool (the blockmem_allocate / blockmem_deallocate hook) ----
 static void block_pool() {
     b2c_ctx* ctx = b200::Context::local().get();
@@ -461,7 +567,10 @@ int main() {
     framing_format();
     fused_and_iovec_calls();
     block_pool();
+    source_sink();
     aggregator_many_threads();
+    aggregator_survives_gpu_failure();
+    aggregator_pooled_results();
     if (g_fail) {
         fprintf(stderr, "%d check(s) failed\n", g_fail);
         return 1;
