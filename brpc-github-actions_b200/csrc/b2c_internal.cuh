@@ -229,5 +229,48 @@ __device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {
     return __funnelshift_r(lo, hi, sh);
 }
 
+// n bytes from src to dst by one warp, any alignment on either side; nothing outside [dst, dst + n) is written and
+// only aligned words that hold at least one byte of [src, src + n) are read:
+// bytes up to dst's next 16-byte boundary, then aligned 16-byte stores whose four words are assembled from aligned
+// source words (one 16-byte load when source and destination have the same phase), then the tail bytes.  This is
+// what moves long literals (incompressible bodies are ONE literal per 64 KiB fragment): 512 bytes per warp
+// instruction instead of 32.  The ranges must not overlap.
+__device__ __forceinline__ void warp_copy_bytes(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, uint32_t n,
+                                                uint32_t lane) {
+    if (n < 64) {
+        for (uint32_t i = lane; i < n; i += 32) dst[i] = src[i];
+        return;
+    }
+    const uint32_t head = (16u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15)) & 15u;
+    if (lane < head) dst[lane] = src[lane];
+    const uint32_t vecs = (n - head) >> 4;
+    uint4* d4 = reinterpret_cast<uint4*>(dst + head);
+    const uint8_t* s = src + head;
+    const uintptr_t sa = reinterpret_cast<uintptr_t>(s);
+    if ((sa & 15) == 0) {
+        const uint4* s4 = reinterpret_cast<const uint4*>(s);
+        for (uint32_t i = lane; i < vecs; i += 32) d4[i] = s4[i];
+    } else {
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(sa & ~uintptr_t(3));
+        const uint32_t sh = (uint32_t)(sa & 3) * 8;
+        if (sh == 0) {
+            for (uint32_t i = lane; i < vecs; i += 32) {
+                const uint32_t* q = w + 4 * i;
+                d4[i] = make_uint4(q[0], q[1], q[2], q[3]);
+            }
+        } else {
+            // the fifth word of a vector holds that vector's last bytes in its low part
+            for (uint32_t i = lane; i < vecs; i += 32) {
+                const uint32_t* q = w + 4 * i;
+                const uint32_t a = q[0], b = q[1], c = q[2], d = q[3], e = q[4];
+                d4[i] = make_uint4(__funnelshift_r(a, b, sh), __funnelshift_r(b, c, sh), __funnelshift_r(c, d, sh),
+                                   __funnelshift_r(d, e, sh));
+            }
+        }
+    }
+    const uint32_t done = head + (vecs << 4);
+    if (lane < n - done) dst[done + lane] = src[done + lane];
+}
+
 }  // namespace b2c
 #endif

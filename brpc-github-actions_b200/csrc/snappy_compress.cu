@@ -38,25 +38,6 @@ __device__ __forceinline__ uint32_t varint_len(uint32_t v) {
     return v < (1u << 7) ? 1 : v < (1u << 14) ? 2 : v < (1u << 21) ? 3 : v < (1u << 28) ? 4 : 5;
 }
 
-// Warp-cooperative copy of len bytes (global -> global), arbitrary alignment.
-__device__ __forceinline__ void warp_copy_bytes(uint8_t* dst, const uint8_t* src, uint32_t len, uint32_t lane) {
-    if (len >= 128) {
-        // align dst to 4, then move words built from (possibly unaligned) source
-        uint32_t head = (4u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 3)) & 3u;
-        if (lane < head) dst[lane] = src[lane];
-        dst += head;
-        src += head;
-        len -= head;
-        uint32_t words = len >> 2;
-        uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
-        for (uint32_t i = lane; i < words; i += 32) d32[i] = ld32u(src + 4 * (size_t)i);
-        uint32_t done = words << 2;
-        if (lane < len - done) dst[done + lane] = src[done + lane];
-    } else {
-        for (uint32_t i = lane; i < len; i += 32) dst[i] = src[i];
-    }
-}
-
 // EmitLiteral, snappy.cc:156-196.  Returns bytes written.
 __device__ __forceinline__ uint32_t emit_literal(uint8_t* out, const uint8_t* src, uint32_t len, uint32_t lane) {
     uint32_t n = len - 1, hdr;

@@ -90,9 +90,7 @@ __device__ int decode_message_warp(const uint8_t* __restrict__ in, const uint32_
             if (len >= 61) len = (trailer & tmask) + 1u;  // may wrap to 0 like the reference
             if (n - ip < len) return B2C_CORRUPT;          // premature end of input
             if (expected - produced < len) return B2C_CORRUPT;
-            const uint8_t* src = in + ip;
-            uint8_t* dst = obuf + produced;
-            for (uint32_t i = lane; i < len; i += 32) dst[i] = src[i];
+            warp_copy_bytes(obuf + produced, in + ip, len, lane);
             produced += len;
             ip += len;
         } else {
@@ -169,6 +167,10 @@ struct LinearOut {
     __device__ __forceinline__ void on_tag(bool, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {}
     __device__ __forceinline__ uint8_t ld(uint32_t p) const { return base[p]; }
     __device__ __forceinline__ void st(uint32_t p, uint8_t v) { base[p] = v; }
+    // a long literal, by the whole warp: 16-byte stores (incompressible bodies are one literal per 64 KiB fragment)
+    __device__ __forceinline__ void copy_in(uint32_t p, const uint8_t* src, uint32_t len, uint32_t lane) {
+        warp_copy_bytes(base + p, src, len, lane);
+    }
     __device__ __forceinline__ void begin_batch(uint32_t, uint32_t, uint32_t) {}
     __device__ __forceinline__ bool takes_direct(uint32_t) const { return false; }
     __device__ __forceinline__ void direct_literal(const uint8_t*, uint32_t, uint32_t, uint32_t) {}
@@ -189,6 +191,9 @@ struct RingOut {
     uint32_t bound;     // during a batch: bytes >= bound are read from the ring
     __device__ __forceinline__ uint8_t ld(uint32_t p) const { return p >= bound ? ring[p & 0xffffu] : gout[p]; }
     __device__ __forceinline__ void st(uint32_t p, uint8_t v) { ring[p & 0xffffu] = v; }
+    __device__ __forceinline__ void copy_in(uint32_t p, const uint8_t* src, uint32_t len, uint32_t lane) {
+        for (uint32_t i = lane; i < len; i += 32) ring[(p + i) & 0xffffu] = src[i];
+    }
     __device__ void flush_to(uint32_t upto, uint32_t lane) {  // warp-cooperative
         uint32_t a = flushed;
         if (upto <= a) return;
@@ -217,8 +222,7 @@ struct RingOut {
     __device__ __forceinline__ bool takes_direct(uint32_t len) const { return len > 8192u; }
     __device__ void direct_literal(const uint8_t* src, uint32_t produced, uint32_t len, uint32_t lane) {
         flush_to(produced, lane);
-        uint8_t* dst = gout + produced;
-        for (uint32_t i = lane; i < len; i += 32) dst[i] = src[i];
+        warp_copy_bytes(gout + produced, src, len, lane);
         __syncwarp();
         flushed = produced + len;
         ring_lo = produced + len;
@@ -247,6 +251,7 @@ struct ScanOut {
     }
     __device__ __forceinline__ uint8_t ld(uint32_t) const { return 0; }
     __device__ __forceinline__ void st(uint32_t, uint8_t) {}
+    __device__ __forceinline__ void copy_in(uint32_t, const uint8_t*, uint32_t, uint32_t) {}
     __device__ __forceinline__ void begin_batch(uint32_t, uint32_t, uint32_t) {}
     __device__ __forceinline__ bool takes_direct(uint32_t) const { return false; }
     __device__ __forceinline__ void direct_literal(const uint8_t*, uint32_t, uint32_t, uint32_t) {}
@@ -393,8 +398,7 @@ __device__ int decode_message_batched(const uint8_t* __restrict__ in, const uint
             longs &= longs - 1;
             const uint32_t s0 = __shfl_sync(kFull, lit_src, l), d0 = __shfl_sync(kFull, out_pos, l),
                            ln = __shfl_sync(kFull, len, l);
-            const uint8_t* src = in + s0;
-            for (uint32_t i = lane; i < ln; i += 32) out.st(d0 + i, src[i]);
+            out.copy_in(d0, in + s0, ln, lane);
         }
         __syncwarp();
         // ---- 4b. copies
@@ -859,7 +863,7 @@ __global__ void __launch_bounds__(256) snappy_seg_boundary_kernel(SegScanParams 
 }
 
 // Pass 2 for large slots: every 64 KiB block of a splittable stream is decoded by its own warp.
-__global__ void __launch_bounds__(256) snappy_decompress_blocks_kernel(DecompressParams P) {
+__global__ void __launch_bounds__(256, 5) snappy_decompress_blocks_kernel(DecompressParams P) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t wib = threadIdx.x >> 5;
@@ -883,7 +887,7 @@ __global__ void __launch_bounds__(256) snappy_decompress_blocks_kernel(Decompres
 }
 
 
-__global__ void __launch_bounds__(256) snappy_decompress_kernel(DecompressParams P) {
+__global__ void __launch_bounds__(256, 5) snappy_decompress_kernel(DecompressParams P) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t wib = threadIdx.x >> 5;

@@ -30,6 +30,8 @@ struct InShared {  // fragment staged in shared memory, 4-byte aligned base
         return __funnelshift_r(w[0], w[1], (p & 3) * 8);
     }
     __device__ __forceinline__ uint8_t ld8(uint32_t p) const { return base[p]; }
+    static constexpr bool kContiguous = true;
+    __device__ __forceinline__ const uint8_t* addr(uint32_t p) const { return base + p; }
 };
 struct InGlobal {  // fragment read from HBM through L1
     const uint8_t* base;
@@ -42,7 +44,20 @@ struct InGlobal {  // fragment read from HBM through L1
     }
     __device__ __forceinline__ uint32_t ld32(uint32_t p) const { return ld32u(base + p); }
     __device__ __forceinline__ uint8_t ld8(uint32_t p) const { return base[p]; }
+    static constexpr bool kContiguous = true;
+    __device__ __forceinline__ const uint8_t* addr(uint32_t p) const { return base + p; }
 };
+
+// literal bytes [from, from + n) of the input to d, by the whole warp
+template <class In>
+__device__ __forceinline__ void copy_literal_warp(const In& in, uint32_t from, uint8_t* __restrict__ d, uint32_t n,
+                                                  uint32_t lane) {
+    if constexpr (In::kContiguous) {
+        warp_copy_bytes(d, in.addr(from), n, lane);  // 16-byte stores: an incompressible fragment is one 64 KiB literal
+    } else {
+        for (uint32_t i = lane; i < n; i += 32) d[i] = in.ld8(from + i);
+    }
+}
 
 __device__ __forceinline__ uint32_t literal_header_bytes(uint32_t len) {  // EmitLiteral, snappy.cc:156-196
     const uint32_t n1 = len - 1;
@@ -123,7 +138,7 @@ __device__ __forceinline__ uint32_t emit_elements_warp(const In& in, const bool 
         const uint64_t oa = reinterpret_cast<uint64_t>(o + lit_sz - ll);
         uint8_t* d = reinterpret_cast<uint8_t*>(((uint64_t)__shfl_sync(kFullMask, (uint32_t)(oa >> 32), l) << 32) |
                                                 __shfl_sync(kFullMask, (uint32_t)oa, l));
-        for (uint32_t i = lane; i < ln; i += 32) d[i] = in.ld8(s0 + i);
+        for (uint32_t i = lane; i < ln; i += 32) d[i] = in.ld8(s0 + i);  // (the vector copy here costs the orbit kernel registers it has not got)
     }
     if (has && mm < 68) write_copy_tail(o + lit_sz, off, mm);
     uint32_t lcopies = __ballot_sync(kFullMask, has && mm >= 68);
@@ -153,8 +168,7 @@ __device__ __forceinline__ uint32_t emit_remainder_warp(const In& in, const uint
         const uint32_t ll = n - from;
         uint8_t* o = out + op;
         if (lane == 0) write_literal_header(o, ll);
-        uint8_t* d = o + literal_header_bytes(ll);
-        for (uint32_t i = lane; i < ll; i += 32) d[i] = in.ld8(from + i);
+        copy_literal_warp(in, from, o + literal_header_bytes(ll), ll, lane);
         op += literal_header_bytes(ll) + ll;
     }
     return op;

@@ -30,6 +30,7 @@ struct LockstepParams {
 };
 
 struct InInterleaved {  // a body in the interleaved layout: word w at col[w * 32]
+    static constexpr bool kContiguous = false;
     const uint32_t* col;
     __device__ __forceinline__ uint8_t ld8(uint32_t p) const {
         return (uint8_t)(col[(p >> 2) * ls::kSlots] >> ((p & 3) * 8));

@@ -213,7 +213,9 @@ __device__ __forceinline__ uint32_t smem_addr32(const void* p) { return (uint32_
 // Persistent warps, one fragment at a time.  Shared memory per warp: element queue, then the u16 table
 // (unless it lives in HBM/L2), then the staged fragment (if staged).
 template <bool kStage>
-__global__ void __launch_bounds__(256) snappy_compress_orbit_kernel(WindowParams P) {
+// (256, 5): the HBM-table variant lives on resident warps (40 per SM = 48 registers per thread); the vector copies of
+// long literals must not cost it a fifth of them
+__global__ void __launch_bounds__(256, kStage ? 1 : 5) snappy_compress_orbit_kernel(WindowParams P) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     __shared__ uint64_t bars[8];
     const uint32_t lane = threadIdx.x & 31;
