@@ -215,7 +215,7 @@ __device__ __forceinline__ uint32_t smem_addr32(const void* p) { return (uint32_
 template <bool kStage>
 // (256, 5): the HBM-table variant lives on resident warps (40 per SM = 48 registers per thread); the vector copies of
 // long literals must not cost it a fifth of them
-__global__ void __launch_bounds__(256, kStage ? 1 : 5) snappy_compress_orbit_kernel(WindowParams P) {
+__global__ void __launch_bounds__(256) snappy_compress_orbit_kernel(WindowParams P) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     __shared__ uint64_t bars[8];
     const uint32_t lane = threadIdx.x & 31;
