@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "snappy_lockstep.cuh"
+#include "snappy_lockstep_dec.cuh"
 
 using namespace b2c::ls;
 
@@ -96,6 +97,42 @@ int ls_model_compress(const uint8_t* arena, const uint64_t* off, const uint32_t*
         }
         if (next_emit < len[l]) op = emit_literal(op, src + next_emit, len[l] - next_emit);
         clen[l] = (uint32_t)(op - o0);
+    }
+    if (trips) *trips = t;
+    return 0;
+}
+
+// Decode up to 32 snappy streams (stream i = arena[off[i], off[i]+len[i]), output capacity cap[i] <= 1024) as one
+// warp of the lock-step decoder would.  out: slot i at out + i * out_stride; ulen[i] = the preamble's length;
+// status[i] = 0 ok / 1 corrupt / 2 too small; *trips = trips of the slowest lane.
+int ls_model_decompress(const uint8_t* arena, const uint64_t* off, const uint32_t* len, uint32_t nb, const uint32_t* cap,
+                        uint8_t* out, uint32_t out_stride, uint32_t* ulen, int32_t* status, uint64_t* trips) {
+    using namespace b2c::lsd;
+    if (nb > 32) return -1;
+    std::vector<uint32_t> sm((size_t)kSlotWords * 32, 0xdeadbeefu);  // stale shared memory must not matter
+    DecodeLane L[32];
+    for (uint32_t l = 0; l < nb; l++) {
+        if (cap[l] > kOutMax) return -2;
+        L[l].init(arena + off[l], len[l], sm.data() + l, cap[l]);
+    }
+    uint64_t t = 0;
+    for (;;) {
+        bool any = false;
+        for (uint32_t l = 0; l < nb; l++)
+            if (L[l].live) {
+                L[l].trip();
+                any = true;
+            }
+        if (!any) break;
+        t++;
+    }
+    for (uint32_t l = 0; l < nb; l++) {
+        L[l].finish();
+        ulen[l] = L[l].expected;
+        status[l] = L[l].status;
+        if (L[l].status == kOk)
+            for (uint32_t b = 0; b < L[l].expected; b++)
+                out[(size_t)l * out_stride + b] = (uint8_t)(sm[(size_t)(b >> 2) * 32 + l] >> (8 * (b & 3)));
     }
     if (trips) *trips = t;
     return 0;

@@ -26,6 +26,8 @@ def model():
     subprocess.run([cxx, "-O2", "-std=c++17", "-shared", "-fPIC", "-I", CSRC, "-o", LIB, SRC], check=True)
     lib = C.CDLL(LIB)
     u8p, u32p, u64p = C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)
+    lib.ls_model_decompress.restype = C.c_int
+    lib.ls_model_decompress.argtypes = [u8p, u64p, u32p, C.c_uint32, u32p, u8p, C.c_uint32, u32p, C.POINTER(C.c_int32), u64p]
     lib.ls_model_compress.restype = C.c_int
     lib.ls_model_compress.argtypes = [u8p, u64p, u32p, C.c_uint32, u8p, C.c_uint32, u32p, u64p, u64p]
 
@@ -43,6 +45,23 @@ def model():
         assert rc == 0
         return [out[i * stride:i * stride + int(clen[i])].tobytes() for i in range(len(bodies))], trips.value, modes
 
+    def decompress(streams, caps):
+        """list of <= 32 streams -> (list of (status, bytes), trips)"""
+        arena, off, ln = pack_tight(streams)
+        caps = np.ascontiguousarray(caps, dtype=np.uint32)
+        stride = 1040
+        out = np.zeros(32 * stride, dtype=np.uint8)
+        ulen = np.zeros(32, dtype=np.uint32)
+        status = np.zeros(32, dtype=np.int32)
+        trips = C.c_uint64(0)
+        rc = lib.ls_model_decompress(arena.ctypes.data_as(u8p), off.ctypes.data_as(u64p), ln.ctypes.data_as(u32p),
+                                     len(streams), caps.ctypes.data_as(u32p), out.ctypes.data_as(u8p), stride,
+                                     ulen.ctypes.data_as(u32p), status.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(trips))
+        assert rc == 0
+        return [(int(status[i]), out[i * stride:i * stride + int(ulen[i])].tobytes() if status[i] == 0 else b"")
+                for i in range(len(streams))], trips.value
+
+    compress.decompress = decompress
     return compress
 
 
@@ -108,3 +127,86 @@ def test_random_mixtures(model):
                     b[d:d + l] = b[a:a + l].copy()
             bodies.append(b.tobytes())
         check(model, bodies)
+
+
+# ---------------------------------------------------------------- the lock-step decoder
+def check_decode(model, streams, caps=None):
+    cpu = O.port()
+    if caps is None:
+        caps = [min(1024, cpu.ulen_lenient(s) or 0) for s in streams]
+    got, trips = model.decompress(streams, caps)
+    for i, s in enumerate(streams):
+        ulen = cpu.ulen_lenient(s)
+        if ulen is None:
+            want = (1, b"")
+        elif ulen > caps[i]:
+            want = (2, b"")
+        else:
+            ok, body = cpu.uncompress(s, cap=ulen)
+            want = (0, body) if ok else (1, b"")
+        assert got[i] == want, f"stream {i} ({len(s)} B): got status {got[i][0]} want {want[0]}"
+    return trips
+
+
+def test_decoder_round_trips_all_corpora(model):
+    cpu = O.port()
+    for kind in ("words", "az09", "rand62"):
+        sizes = list(range(0, 40)) + [63, 64, 65, 127, 128, 255, 256, 257, 511, 512, 513, 777, 1000, 1023, 1024]
+        for base in range(0, len(sizes), 32):
+            bodies = [O.corpus(kind, n, index=300 + base + j).tobytes() for j, n in enumerate(sizes[base:base + 32])]
+            check_decode(model, [cpu.compress(b) for b in bodies])
+    trips = check_decode(model, [cpu.compress(O.corpus("words", 1024, index=i).tobytes()) for i in range(32)])
+    print("decode trips for 32 x 1 KiB words:", trips)
+    assert trips < 300
+
+
+def test_decoder_runs_and_foreign_streams(model):
+    cpu = O.port()
+    rng = np.random.default_rng(8)
+    bodies = [bytes(1024), b"a" * 1000, b"ab" * 500, b"abc" * 300, b"abcde" * 200, b"abcdef" * 170, b"abcdefg" * 140,
+              bytes(range(256)) * 4, bytes(rng.integers(0, 256, 1024, dtype=np.uint8))]
+    streams = [cpu.compress(b) for b in bodies]
+
+    def lit(b):
+        n1 = len(b) - 1
+        if n1 < 60:
+            return bytes([n1 << 2]) + b
+        return bytes([62 << 2]) + n1.to_bytes(3, "little") + b  # a 3-byte length, as a foreign encoder may write
+
+    def copy4(offset, length):
+        return bytes([3 | ((length - 1) << 2)]) + offset.to_bytes(4, "little")
+
+    def copy2(offset, length):
+        return bytes([2 | ((length - 1) << 2)]) + offset.to_bytes(2, "little")
+
+    for o in range(1, 12):  # overlapping copies of every small offset, lengths straddling the 8-byte chunk
+        for ln in (4, 7, 8, 9, 15, 16, 17, 33, 64):
+            body_len = o + ln
+            streams.append(bytes([body_len]) + lit(bytes(range(65, 65 + o))) + copy2(o, ln))
+    streams.append(bytes([100]) + lit(b"x" * 50) + copy4(50, 50))
+    streams.append(bytes([0x80, 0x02]) + lit(bytes(rng.integers(0, 256, 200, dtype=np.uint8))) + copy4(200, 56))
+    for base in range(0, len(streams), 32):
+        check_decode(model, streams[base:base + 32])
+
+
+def test_decoder_rejects_what_the_reference_rejects(model):
+    cpu = O.port()
+    rng = np.random.default_rng(21)
+    streams = []
+    for t in range(640):
+        body = O.corpus(("words", "az09", "rand62")[t % 3], int(rng.integers(1, 1025)), index=t).tobytes()
+        z = bytearray(cpu.compress(body))
+        how = t % 5
+        if how == 0 and len(z) > 3:
+            z = z[: int(rng.integers(1, len(z)))]  # truncated
+        elif how == 1:
+            z[int(rng.integers(0, len(z)))] ^= 1 << int(rng.integers(0, 8))  # a flipped bit
+        elif how == 2:
+            z += bytes(rng.integers(0, 256, int(rng.integers(1, 6)), dtype=np.uint8))  # trailing bytes
+        elif how == 3:
+            z[0] = (z[0] + int(rng.integers(1, 5))) & 0x7f  # the preamble lies
+        streams.append(bytes(z))
+    for base in range(0, len(streams), 32):
+        chunk = streams[base:base + 32]
+        caps = [1024] * len(chunk)
+        check_decode(model, chunk, caps)
