@@ -553,6 +553,8 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     if (const char* s = getenv("B2C_GATHER_WARPS")) ctx->gather_warps = std::min(32, std::max(1, atoi(s)));
     if (const char* s = getenv("B2C_GATHER_CHUNK")) ctx->gather_chunk = std::min(8192, std::max(512, atoi(s) / 16 * 16));
     if (const char* s = getenv("B2C_LOCKSTEP")) ctx->small_lockstep = atoi(s) != 0;
+    if (const char* s = getenv("B2C_LOCKSTEP_D")) ctx->lockstep_decode = atoi(s) != 0;
+    if (const char* s = getenv("B2C_LOCKSTEP_D_CTAS")) ctx->lockstep_decode_ctas = std::min(8, std::max(1, atoi(s)));
     if (const char* s = getenv("B2C_LOCKSTEP_LPW")) {
         const int v = atoi(s);
         if (v == 4 || v == 8 || v == 16 || v == 32) ctx->lockstep_lpw = v;

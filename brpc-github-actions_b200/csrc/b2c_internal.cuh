@@ -138,6 +138,9 @@ struct b2c_ctx {
     bool block_decode = true;        // B2C_BLOCK_DECODE=0: never split large streams into 64 KiB blocks
     bool ring_attr_done = false;
     bool gather_attr_done = false;
+    bool lsd_attr_done = false;
+    bool lockstep_decode = false;  // B2C_LOCKSTEP_D=1: slots <= 1 KiB decode with the lock-step state machine of snappy_lockstep_dec.cuh (measured slower than the lane-per-stream loops of snappy_small.cu: 6.8 vs 5.2 ms per GiB of 1 KiB `words` bodies)
+    int lockstep_decode_ctas = 6;  // B2C_LOCKSTEP_D_CTAS: resident one-warp CTAs per SM of the lock-step decoder
     int gather_warps = 8, gather_chunk = 2048;  // B2C_GATHER_WARPS / B2C_GATHER_CHUNK: warps per CTA and bytes per round and warp
     int gather_ctas_per_sm = 1;  // B2C_GATHER_CTAS: CTAs per SM of the device-side gather of pinned input blocks
     bool batch_decode = true;        // B2C_BATCH_DECODE=0: one tag per step in the warp decoder
@@ -205,6 +208,8 @@ void gather_fence();
 int lockstep_kernels_configure(b2c_ctx* ctx);
 int launch_compress_lockstep(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint8_t* scratch,
                              uint32_t* d_frag_clen);
+int launch_decompress_lockstep(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint8_t* d_in,
+                               const LayoutView& out, uint8_t* d_out, uint32_t* d_ulen, int32_t* d_status);
 // window-parallel warp-per-fragment compressor (snappy_window.cu); c = fragment class 0..2
 int window_kernels_configure(b2c_ctx* ctx);
 int launch_compress_window(b2c_ctx* ctx, Lane& lane, const LayoutView& L, int c, const uint8_t* d_in, uint8_t* scratch,

@@ -1054,7 +1054,8 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
     for (int c = 0; c < 3; c++) {
         if (!out.n_dclass[c]) continue;
         if (c == 0 && ctx->small_kernels && !ctx->batch_decode_small) {  // slots <= 1 KiB: one lane per stream
-            int rc = launch_decompress_small(ctx, lane, in, d_in, out, d_out, d_ulen, d_status);
+            int rc = ctx->lockstep_decode ? launch_decompress_lockstep(ctx, lane, in, d_in, out, d_out, d_ulen, d_status)
+                                          : launch_decompress_small(ctx, lane, in, d_in, out, d_out, d_ulen, d_status);
             if (rc) return rc;
             continue;
         }

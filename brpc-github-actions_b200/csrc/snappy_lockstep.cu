@@ -11,6 +11,7 @@
 
 #include "snappy_emit.cuh"
 #include "snappy_lockstep.cuh"
+#include "snappy_lockstep_dec.cuh"
 
 namespace b2c {
 
@@ -197,6 +198,107 @@ int launch_compress_lockstep(b2c_ctx* ctx, Lane& lane, const LayoutView& L, cons
         case 32: snappy_compress_lockstep_kernel<32><<<grid, threads, kLockstepSmem, lane.stream>>>(P); break;
         default: snappy_compress_lockstep_kernel<8><<<grid, threads, kLockstepSmem, lane.stream>>>(P); break;
     }
+    ctx->launches++;
+    B2C_CUDA(ctx, cudaGetLastError());
+    return B2C_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// decompress: 32 streams per warp in lock-step (snappy_lockstep_dec.cuh), output slots <= 1 KiB
+// ---------------------------------------------------------------------------------------------------------------
+struct LockstepDecodeParams {
+    const uint8_t* in;
+    const uint64_t* in_off;
+    const uint32_t* in_len;
+    const uint64_t* out_off;
+    const uint32_t* out_cap;
+    const uint32_t* list;
+    uint8_t* out;
+    uint32_t* ulen;
+    int32_t* status;
+    uint32_t n_list;
+};
+
+// One lane writes its own decoded body (n bytes, word w at col[w * 32]) to dst: its shared-memory reads stay in the
+// lane's bank, and the 16-byte stores of the 32 lanes go to 32 different bodies -- two consecutive stores of a lane
+// fill a 32-byte sector, which L2 merges.
+__device__ __forceinline__ void flush_slot_lane(const uint32_t* __restrict__ col, uint8_t* __restrict__ dst, uint32_t n) {
+    auto byte_at = [&](uint32_t i) -> uint8_t { return (uint8_t)(col[(i >> 2) * lsd::kSlots] >> ((i & 3) * 8)); };
+    uint32_t head = (16u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15)) & 15u;
+    if (head > n) head = n;
+    for (uint32_t i = 0; i < head; i++) dst[i] = byte_at(i);
+    const uint32_t vecs = (n - head) >> 4;
+    const uint32_t* w = col + (head >> 2) * lsd::kSlots;
+    const uint32_t sh = (head & 3) * 8;
+    uint4* d4 = reinterpret_cast<uint4*>(dst + head);
+    if (sh == 0) {
+        for (uint32_t v = 0; v < vecs; v++) {
+            const uint32_t* q = w + (size_t)v * 4 * lsd::kSlots;
+            d4[v] = make_uint4(q[0], q[lsd::kSlots], q[2 * lsd::kSlots], q[3 * lsd::kSlots]);
+        }
+    } else {
+        for (uint32_t v = 0; v < vecs; v++) {
+            const uint32_t* q = w + (size_t)v * 4 * lsd::kSlots;
+            const uint32_t a = q[0], b = q[lsd::kSlots], c = q[2 * lsd::kSlots], d = q[3 * lsd::kSlots], e = q[4 * lsd::kSlots];
+            d4[v] = make_uint4(__funnelshift_r(a, b, sh), __funnelshift_r(b, c, sh), __funnelshift_r(c, d, sh),
+                               __funnelshift_r(d, e, sh));
+        }
+    }
+    for (uint32_t i = head + (vecs << 4); i < n; i++) dst[i] = byte_at(i);
+}
+
+__global__ void __launch_bounds__(32, 6) snappy_decompress_lockstep_kernel(LockstepDecodeParams P) {
+    extern __shared__ __align__(16) uint32_t lsd_smem[];
+    const uint32_t lane = threadIdx.x;
+    const uint32_t groups = (P.n_list + 31) / 32;
+    for (uint32_t g = blockIdx.x; g < groups; g += gridDim.x) {
+        const uint32_t idx = g * 32 + lane;
+        const bool have = idx < P.n_list;
+        uint32_t m = 0;
+        lsd::DecodeLane L;
+        L.live = 0;
+        L.status = B2C_OK;
+        L.expected = L.op = L.cur = L.rem = 0;
+        L.slot = lsd_smem + lane;
+        if (have) {
+            m = P.list ? P.list[idx] : idx;
+            L.init(P.in + P.in_off[m], P.in_len[m], lsd_smem + lane, min(P.out_cap[m], lsd::kOutMax));
+        }
+        while (__any_sync(kFullMask, L.live != 0)) {
+            if (L.live) L.trip();
+        }
+        if (have) {
+            L.finish();
+            P.status[m] = L.status;
+            if (P.ulen) P.ulen[m] = L.expected;
+            if (L.status == B2C_OK) flush_slot_lane(lsd_smem + lane, P.out + P.out_off[m], L.expected);
+        }
+    }
+}
+
+constexpr size_t kLockstepDecodeSmem = (size_t)lsd::kSlotWords * lsd::kSlots * 4;
+
+int launch_decompress_lockstep(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint8_t* d_in, const LayoutView& out,
+                               uint8_t* d_out, uint32_t* d_ulen, int32_t* d_status) {
+    LockstepDecodeParams P;
+    P.in = d_in;
+    P.in_off = in.d_off;
+    P.in_len = in.d_len;
+    P.out_off = out.d_off;
+    P.out_cap = out.d_len;
+    P.list = out.d_dclass_list[0];
+    P.out = d_out;
+    P.ulen = d_ulen;
+    P.status = d_status;
+    P.n_list = out.n_dclass[0];
+    if (!ctx->lsd_attr_done) {
+        B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_decompress_lockstep_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                           cudaSharedmemCarveoutMaxShared));
+        ctx->lsd_attr_done = true;
+    }
+    const uint32_t groups = (P.n_list + 31) / 32;
+    const uint32_t grid = std::min<uint32_t>(groups, (uint32_t)ctx->num_sms * (uint32_t)ctx->lockstep_decode_ctas);
+    snappy_decompress_lockstep_kernel<<<grid, 32, kLockstepDecodeSmem, lane.stream>>>(P);
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
     return B2C_OK;

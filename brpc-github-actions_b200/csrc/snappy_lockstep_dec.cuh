@@ -32,15 +32,20 @@ constexpr uint32_t kSlotWords = kOutMax / 4 + 4;  // an append writes up to thre
 
 enum : int32_t { kOk = 0, kCorrupt = 1, kTooSmall = 2 };  // B2C_OK / B2C_CORRUPT / B2C_TOO_SMALL
 
-// byte_perm selectors that expand the first o bytes of an 8-byte window into the pattern s[i] = b[i % o], o = 1..7
-LS_HD uint32_t pattern_sel(uint32_t o, uint32_t hi_half) {
-    // nibble i of the selector = (i + 4 * hi_half) % o
-    uint32_t sel = 0;
+// For a copy whose offset o is below 8: byte_perm selectors that expand the first o bytes of an 8-byte window into the
+// pattern s[i] = b[i % o] (low half in bits 0-15, high half in bits 16-31), and the smallest multiple of o that is
+// >= 8 (bits 0-3 of the second table).  Tables, not arithmetic: i % o by a run-time o costs a division each.
+LS_HD uint32_t pattern_sel(uint32_t o) {
+    const uint32_t t[8] = {0, 0x00000000u, 0x10101010u, 0x10210210u, 0x32103210u, 0x21043210u, 0x10543210u, 0x06543210u};
+    return t[o & 7];
+}
+LS_HD uint32_t pattern_step(uint32_t o) { return (uint32_t)((0xECA89880ull >> (4 * (o & 7))) & 15); }  // 8 8 9 8 10 12 14
+LS_HD uint32_t fsl(uint32_t lo, uint32_t hi, uint32_t sh) {  // (hi << sh) | (lo >> (32 - sh)), sh = 0, 8, 16, 24
 #if defined(__CUDA_ARCH__)
-#pragma unroll
+    return __funnelshift_l(lo, hi, sh);
+#else
+    return sh ? (hi << sh) | (lo >> (32 - sh)) : hi;
 #endif
-    for (uint32_t i = 0; i < 4; i++) sel |= ((i + 4 * hi_half) % o) << (4 * i);
-    return sel;
 }
 LS_HD uint32_t byte_perm(uint32_t lo, uint32_t hi, uint32_t sel) {
 #if defined(__CUDA_ARCH__)
@@ -57,35 +62,54 @@ struct DecodeLane {
     const uint8_t* in;  // the stream (global memory); reads touch only aligned words that hold one of its bytes
     uint32_t* slot;     // word w of this lane's output at slot[w * 32]
     uint32_t n, ip, expected, op;
+    // The stream is consumed strictly in order (tag, then a literal's bytes), so the lane keeps a 32-byte window of
+    // it in registers and asks for the following 16 bytes one refill ahead: the global-memory latency of a lane's
+    // private, uncoalesced stream is off the tag-to-tag chain.
+    const uint32_t* win;  // aligned word that holds the stream's first byte
+    uint32_t lead;        // in - win, in bytes (0..3)
+    uint32_t wb;          // word index (from win) of w[0]; lead + ip - 4 * wb is in [0, 16) between trips
+    uint32_t w[8], nx[4];
     uint32_t rem;       // bytes of the element in progress still to move
-    uint32_t src;       // where they come from: a stream position (literal) or an output position (copy)
-    uint32_t is_lit, first;  // first: the next chunk is the first of a copy whose offset is below 8
+    uint32_t src;       // a copy's source: an output position
+    uint32_t is_lit;
     uint32_t offset;
     uint32_t cur;       // the bytes of the word that holds `op` which lie below op
     uint32_t live;
     int32_t status;
 
-    // 12 stream bytes from position p (bytes past the end of the stream read as 0)
-    LS_HD void load12(uint32_t p, uint32_t& g0, uint32_t& g1, uint32_t& g2) const {
-        const uintptr_t a = reinterpret_cast<uintptr_t>(in + p);
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~uintptr_t(3));
-        const uint32_t lead = (uint32_t)(a & 3), sh = lead * 8;
-        const uint32_t left = n > p ? n - p : 0u;  // stream bytes from p on
-        // word k holds stream bytes iff 4k < lead + left
-        const uint32_t have = lead + left;
-        const uint32_t w0 = have > 0 ? w[0] : 0u, w1 = have > 4 ? w[1] : 0u, w2 = have > 8 ? w[2] : 0u, w3 = have > 12 ? w[3] : 0u;
-        g0 = ls::fsr(w0, w1, sh);
-        g1 = ls::fsr(w1, w2, sh);
-        g2 = ls::fsr(w2, w3, sh);
+    LS_HD uint32_t ldw(uint32_t k) const { return 4 * k < lead + n ? win[k] : 0u; }  // words past the stream read as 0
+    // 12 stream bytes from ip, out of the register window
+    LS_HD void peek12(uint32_t& g0, uint32_t& g1, uint32_t& g2) const {
+        const uint32_t r = lead + ip - 4 * wb, s = r >> 2, sh = (r & 3) * 8;
+        const uint32_t x0 = s == 0 ? w[0] : s == 1 ? w[1] : s == 2 ? w[2] : w[3];
+        const uint32_t x1 = s == 0 ? w[1] : s == 1 ? w[2] : s == 2 ? w[3] : w[4];
+        const uint32_t x2 = s == 0 ? w[2] : s == 1 ? w[3] : s == 2 ? w[4] : w[5];
+        const uint32_t x3 = s == 0 ? w[3] : s == 1 ? w[4] : s == 2 ? w[5] : w[6];
+        g0 = ls::fsr(x0, x1, sh);
+        g1 = ls::fsr(x1, x2, sh);
+        g2 = ls::fsr(x2, x3, sh);
+    }
+    // after ip moved: slide the window by 16 bytes when ip has left its first 16, and ask for the 16 after next
+    LS_HD void slide() {
+        if (lead + ip - 4 * wb >= 16) {
+            w[0] = w[4], w[1] = w[5], w[2] = w[6], w[3] = w[7];
+            w[4] = nx[0], w[5] = nx[1], w[6] = nx[2], w[7] = nx[3];
+            wb += 4;
+            nx[0] = ldw(wb + 8), nx[1] = ldw(wb + 9), nx[2] = ldw(wb + 10), nx[3] = ldw(wb + 11);
+        }
     }
 
     LS_HD void init(const uint8_t* in_, uint32_t n_, uint32_t* slot_, uint32_t cap) {
         in = in_;
         n = n_;
         slot = slot_;
-        ip = op = rem = src = is_lit = first = offset = cur = expected = 0;
+        ip = op = rem = src = is_lit = offset = cur = expected = 0;
         live = 1;
         status = kOk;
+        const uintptr_t a0 = reinterpret_cast<uintptr_t>(in);
+        win = reinterpret_cast<const uint32_t*>(a0 & ~uintptr_t(3));
+        lead = (uint32_t)(a0 & 3);
+        wb = 0;
         // lenient preamble, snappy.cc:692-711
         uint32_t shift = 0;
         for (;;) {
@@ -102,113 +126,100 @@ struct DecodeLane {
         if (expected > cap) {
             status = kTooSmall;
             live = 0;
-        }
-    }
-
-    LS_HD void trip() {
-        // ---- the stream bytes this trip needs: the tag at ip, or the next chunk of a literal in progress ----
-        const bool need_tag = rem == 0;
-        if (need_tag && ip == n) {  // clean end of input: snappy.cc:867
-            if (op != expected) status = kCorrupt;
-            live = 0;
             return;
         }
-        const uint32_t gp = need_tag ? ip : src;
+        wb = (lead + ip) >> 2;
+        for (uint32_t i = 0; i < 8; i++) w[i] = ldw(wb + i);
+        for (uint32_t i = 0; i < 4; i++) nx[i] = ldw(wb + 8 + i);
+    }
+
+    // One step.  Straight-line selects on the common path (a short literal, a copy with a 1- or 2-byte offset of at
+    // least 8); the rare kinds — a literal with length bytes, a 4-byte offset, a copy that overlaps itself within 8
+    // bytes — take a branch of their own.
+    LS_HD void trip() {
+        const bool need_tag = rem == 0;
+        const bool eof = need_tag && ip == n;  // clean end of input: snappy.cc:867
         uint32_t g0, g1, g2;
-        load12(gp, g0, g1, g2);
-        uint32_t lo = g0, hi = g1, avail = 8;  // a literal's next bytes
-        if (need_tag) {
-            const uint32_t c = g0 & 0xff, kind = c & 3;
-            uint32_t len = (c >> 2) + 1;             // literal < 61, copy-2, copy-4
-            uint32_t used = kind + 1;                // 1, 2, 3 (copy-4 and long literals: below)
-            uint32_t off = (g0 >> 8) & 0xffffu;      // copy-2
-            if (kind == 1) {
-                len = ((c >> 2) & 7) + 4;
-                off = ((c >> 5) << 8) | ((g0 >> 8) & 0xff);
-            }
-            const bool long_lit = kind == 0 && c >= 0xf0u;
-            if (long_lit) {  // literal with 1..4 length bytes
+        peek12(g0, g1, g2);
+        // ---- the tag at ip (computed by every lane, applied by those that need one) ----
+        const uint32_t c = g0 & 0xff, kind = c & 3;
+        uint32_t len = kind == 1 ? ((c >> 2) & 7) + 4 : (c >> 2) + 1;
+        uint32_t used = kind + 1;
+        uint32_t off = kind == 1 ? ((c >> 5) << 8) | ((g0 >> 8) & 0xff) : (g0 >> 8) & 0xffffu;
+        uint32_t lit_lo = need_tag ? ls::fsr(g0, g1, 8) : g0, lit_hi = need_tag ? ls::fsr(g1, g2, 8) : g1, avail = 8;
+        if (need_tag && (kind == 3 || (kind == 0 && c >= 0xf0u))) {  // rare: length bytes / 4-byte offset
+            if (kind == 0) {
                 const uint32_t extra = len - 60;
                 uint32_t v = (g0 >> 8) | (g1 << 24);
                 if (extra < 4) v &= (1u << (8 * extra)) - 1u;
                 len = v + 1u;  // may wrap to 0 like the reference
                 used = 1 + extra;
-            }
-            if (kind == 3) {
+                const uint32_t sh = (used & 3) * 8;
+                const uint32_t a = used < 4 ? g0 : g1, b = used < 4 ? g1 : g2, d = used < 4 ? g2 : 0u;
+                lit_lo = ls::fsr(a, b, sh);
+                lit_hi = ls::fsr(b, d, sh);
+                avail = 12 - used;  // 7 when the tag had 4 length bytes
+            } else {
                 off = (g0 >> 8) | (g1 << 24);
                 used = 5;
             }
-            const uint32_t left = n - ip;
-            bool bad = left < used;                              // tag cut short
-            if (!bad) {
-                if (kind == 0) bad = left - used < len;          // premature end of input
-                else bad = off - 1u >= op;                       // offset 0 or beyond what was produced
-            }
-            if (bad || expected - op < len) {                    // or more output than announced
-                status = kCorrupt;
-                live = 0;
-                return;
-            }
-            rem = len;
-            is_lit = kind == 0 ? 1u : 0u;
-            offset = off;
-            if (is_lit) {
-                src = ip + used;
-                ip += used + len;
-                // the literal's first bytes came with the tag: bytes used.. of (g0, g1, g2)
-                const uint32_t sh = (used & 3) * 8;
-                const uint32_t a = used < 4 ? g0 : g1, b = used < 4 ? g1 : g2, d = used < 4 ? g2 : 0u;
-                lo = ls::fsr(a, b, sh);
-                hi = ls::fsr(b, d, sh);
-                avail = 12 - used;  // 7 when the tag had 4 length bytes
-            } else {
-                ip += used;
-                src = op - off;
-                first = off < 8 ? 1u : 0u;
-            }
         }
-        // ---- a copy's next bytes come from the lane's own output ----
-        if (!is_lit) {
-            const uint32_t* w = slot + (src >> 2) * kSlots;
-            const uint32_t sh = (src & 3) * 8;
-            const uint32_t w0 = w[0], w1 = w[kSlots], w2 = w[2 * kSlots];
-            // the word that holds op is in `cur`, not in the slot yet
-            const uint32_t wc = op >> 2, ws = src >> 2;
-            const uint32_t x0 = ws == wc ? cur : w0, x1 = ws + 1 == wc ? cur : w1, x2 = ws + 2 == wc ? cur : w2;
-            lo = ls::fsr(x0, x1, sh);
-            hi = ls::fsr(x1, x2, sh);
-            avail = 8;
-            if (first) {  // offset o < 8: the 8 bytes are the pattern of the o bytes at src (IncrementalCopy)
-                const uint32_t o = offset;
-                const uint32_t plo = byte_perm(lo, hi, pattern_sel(o, 0)), phi = byte_perm(lo, hi, pattern_sel(o, 1));
-                lo = plo;
-                hi = phi;
-                // from here on the run continues `o2` bytes back, the smallest multiple of o that is >= 8: those
-                // bytes are written by now and no longer overlap the 8 bytes a trip moves
-                const uint32_t o2 = o * ((7 + o) / o);
-                offset = o2;
-                first = 0;
-                src = op - o2;  // + k below: the next chunk starts at (op + k) - o2
-            }
+        const uint32_t left = n - ip;
+        const bool lit = kind == 0;
+        // tag cut short | premature end of input | offset 0 or beyond what was produced | more output than announced
+        const bool bad = need_tag && !eof &&
+                         (left < used || (lit ? left - used < len : off - 1u >= op) || expected - op < len);
+        const bool stop = eof || bad;
+        status = bad || (eof && op != expected) ? kCorrupt : status;
+        live = stop ? 0u : 1u;
+        const bool take = need_tag && !stop;  // a stopped lane changes nothing below: k == 0, no store, no slide
+        rem = take ? len : rem;
+        is_lit = take ? (lit ? 1u : 0u) : is_lit;
+        offset = take ? off : offset;
+        src = take ? (lit ? 0u : op - off) : src;  // always a valid output position
+        ip += take ? used : 0u;
+        // ---- a copy's next bytes come from the lane's own output (a literal reads, and ignores, a valid word too) ----
+        const uint32_t rs = ls::umin(src, kOutMax - 1);  // a finished pattern copy may leave src out of range: read something valid
+        const uint32_t* w = slot + (rs >> 2) * kSlots;
+        const uint32_t sh2 = (rs & 3) * 8;
+        const uint32_t w0 = w[0], w1 = w[kSlots], w2 = w[2 * kSlots];
+        const uint32_t dw = (op >> 2) - (rs >> 2);  // the word that holds op is in `cur`, not in the slot yet
+        const uint32_t x0 = dw == 0 ? cur : w0, x1 = dw == 1 ? cur : w1, x2 = dw == 2 ? cur : w2;
+        uint32_t lo = ls::fsr(x0, x1, sh2), hi = ls::fsr(x1, x2, sh2);
+        if (!stop && !is_lit && offset < 8) {  // rare: the 8 bytes are the pattern of the `offset` bytes at src (IncrementalCopy)
+            const uint32_t o = offset;
+            const uint32_t sel = pattern_sel(o);
+            const uint32_t plo = byte_perm(lo, hi, sel & 0xffffu), phi = byte_perm(lo, hi, sel >> 16);
+            lo = plo;
+            hi = phi;
+            // from here on the run continues `o2` bytes back, the smallest multiple of o that is >= 8: those bytes
+            // are written by now and no longer overlap the 8 bytes a trip moves
+            const uint32_t o2 = pattern_step(o);
+            offset = o2;
+            src = op - o2;  // + k below: the next chunk starts at (op + k) - o2
         }
+        lo = is_lit ? lit_lo : lo;
+        hi = is_lit ? lit_hi : hi;
         // ---- append k bytes at op ----
-        const uint32_t k = ls::umin(ls::umin(rem, 8u), avail);
+        const uint32_t k = stop ? 0u : ls::umin(ls::umin(rem, 8u), avail);
         const uint32_t sh = (op & 3) * 8;
         uint32_t* d = slot + (op >> 2) * kSlots;
         // bytes 0..11 of the three words from the word of op: cur below op, then lo, hi
         const uint32_t d0 = cur | (lo << sh);
-        const uint32_t d1 = sh ? (lo >> (32 - sh)) | (hi << sh) : hi;
-        const uint32_t d2 = sh ? hi >> (32 - sh) : 0u;
-        const uint32_t end = (op & 3) + k;  // bytes of (d0, d1, d2) that are final: 1..11
+        const uint32_t d1s = fsl(lo, hi, sh);
+        const uint32_t d2 = fsl(hi, 0u, sh);
+        const uint32_t end = (op & 3) + k;  // bytes of (d0, d1, d2) that are final: 0..11
         if (end >= 4) d[0] = d0;
-        if (end >= 8) d[kSlots] = d1;
+        if (end >= 8) d[kSlots] = d1s;
         // the new partial word: the bytes of the word that holds op + k which lie below op + k
         const uint32_t part = end & 3, wsel = end >> 2;
-        const uint32_t dw = wsel == 0 ? d0 : wsel == 1 ? d1 : d2;
-        cur = part ? dw & ((1u << (8 * part)) - 1u) : 0u;
+        const uint32_t nw = wsel == 0 ? d0 : wsel == 1 ? d1s : d2;
+        cur = nw & ~(0xffffffffu << (8 * part));  // part == 0: nothing
         op += k;
-        src += k;
+        src += is_lit ? 0u : k;  // (a literal leaves src alone: it must stay a valid output position)
         rem -= k;
+        ip += is_lit ? k : 0u;   // a literal's bytes are consumed from the stream as they are moved
+        slide();
     }
 
     // the last partial word goes to the slot; returns the status
