@@ -70,6 +70,15 @@ SYMBOLS = {
     "b2c_snappy_decompress_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b2c_snappy_validate_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     "b2c_snappy_decompress_verify_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b2c_multi_create": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(_vp)]),
+    "b2c_multi_destroy": (None, [_vp]),
+    "b2c_multi_device_count": (C.c_int, [_vp]),
+    "b2c_multi_last_error": (C.c_char_p, [_vp]),
+    "b2c_multi_crc32c_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _u32p, _u32p]),
+    "b2c_multi_snappy_compress_crc_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _vp, C.c_uint64, _u64p, _u32p,
+                                                      _u32p, C.c_int]),
+    "b2c_multi_snappy_decompress_verify_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _u32p, _vp, C.c_uint64,
+                                                           _u64p, _i32p]),
     "b2c_snappy_compress_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _vp, C.c_uint64, _u64p]),
     "b2c_snappy_decompress_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _vp, C.c_uint64, _u64p, _i32p]),
     "b2c_snappy_compress_crc_batch": (C.c_int, [_vp, C.POINTER(IoVec), _u32p, C.c_uint32, _vp, C.c_uint64, _u64p, _u32p,
@@ -478,3 +487,65 @@ class Codec:
         a, b = C.c_uint64(0), C.c_uint64(0)
         self.lib.b2c_last_transfer_bytes(self.ctx, C.byref(a), C.byref(b))
         return a.value, b.value
+
+
+class MultiCodec:
+    """One b2c_multi: a batch split over several GPUs by bytes (b2c_multi_*), results in message order."""
+
+    def __init__(self, devices):
+        self.lib = load()
+        devs = (C.c_int * len(devices))(*devices)
+        h = _vp()
+        rc = self.lib.b2c_multi_create(devs, len(devices), C.byref(h))
+        if rc != OK:
+            raise B2CError(f"b2c_multi_create({list(devices)}) failed with {rc}")
+        self.h = h.value
+        self.devices = list(devices)
+
+    def close(self):
+        if self.h:
+            self.lib.b2c_multi_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != OK:
+            raise B2CError(f"libb2c multi error {rc}: {self.lib.b2c_multi_last_error(self.h).decode(errors='replace')}")
+
+    def _segs(self, raw):
+        return raw.ctypes.data_as(C.POINTER(IoVec))
+
+    def crc32c_batch(self, raw_segs, seg_begin, init=None):
+        n = len(seg_begin) - 1
+        crc = np.empty(n, dtype=np.uint32)
+        ini = np.ascontiguousarray(init, dtype=np.uint32) if init is not None else None
+        self._check(self.lib.b2c_multi_crc32c_batch(self.h, self._segs(raw_segs), _ptr(seg_begin, _u32p), n,
+                                                    _ptr(ini, _u32p) if ini is not None else None, _ptr(crc, _u32p)))
+        return crc
+
+    def compress_crc_batch(self, raw_segs, seg_begin, out, masked=True, want_crc=True):
+        """(out_off[n], out_len[n], crc[n] or None): stream i = out[out_off[i] : out_off[i] + out_len[i]]"""
+        n = len(seg_begin) - 1
+        out_off = np.empty(n, dtype=np.uint64)
+        out_len = np.empty(n, dtype=np.uint32)
+        crc = np.empty(n, dtype=np.uint32) if want_crc else None
+        self._check(self.lib.b2c_multi_snappy_compress_crc_batch(
+            self.h, self._segs(raw_segs), _ptr(seg_begin, _u32p), n, out.ctypes.data, out.nbytes, _ptr(out_off, _u64p),
+            _ptr(out_len, _u32p), _ptr(crc, _u32p) if want_crc else None, 1 if masked else 0))
+        return out_off, out_len, crc
+
+    def decompress_verify_batch(self, raw_segs, seg_begin, masked_crc, out):
+        """(out_off[n+1], status[n]); masked_crc None = plain decompress"""
+        n = len(seg_begin) - 1
+        out_off = np.empty(n + 1, dtype=np.uint64)
+        status = np.empty(n, dtype=np.int32)
+        mc = np.ascontiguousarray(masked_crc, dtype=np.uint32) if masked_crc is not None else None
+        self._check(self.lib.b2c_multi_snappy_decompress_verify_batch(
+            self.h, self._segs(raw_segs), _ptr(seg_begin, _u32p), n, _ptr(mc, _u32p) if mc is not None else None,
+            out.ctypes.data, out.nbytes, _ptr(out_off, _u64p), _ptr(status, _i32p)))
+        return out_off, status

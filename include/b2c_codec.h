@@ -283,6 +283,35 @@ int b2c_snappy_decompress_verify_batch(b2c_ctx* ctx, const b2c_iovec* segs, cons
 int b2c_crc32c_batch(b2c_ctx* ctx, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n,
                      const uint32_t* init, uint32_t* crc);
 
+/* ---- one batch over several GPUs ----------------------------------------------- */
+/* Message bodies are independent (snappy.cc:887-948; CRC per message), so a batch shards over the GPUs of a box
+ * by a host-side split and nothing else: the message list is cut into one contiguous range per device, balanced
+ * by bytes; every range runs through its device's own ctx on that device's own worker thread; results land in
+ * the caller's buffers in message order.  No collective, no peer traffic.  The reference has no counterpart (it
+ * has no device at all); this is the proposed `ctx_create(const int* devices, int n, ...)` of SURVEY.md 8(b).
+ * A b2c_multi is used by one thread at a time.  The host's cores are divided among the devices' gather pools. */
+typedef struct b2c_multi b2c_multi;
+int b2c_multi_create(const int* devices, int n_devices, b2c_multi** multi);
+void b2c_multi_destroy(b2c_multi* multi);
+int b2c_multi_device_count(const b2c_multi* multi);
+const char* b2c_multi_last_error(const b2c_multi* multi);
+/* b2c_crc32c_batch over all devices */
+int b2c_multi_crc32c_batch(b2c_multi* multi, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n,
+                           const uint32_t* init, uint32_t* crc);
+/* b2c_snappy_compress_crc_batch (crc == NULL: b2c_snappy_compress_batch) over all devices.  Compressed sizes are not
+ * known before the devices have run, so every device packs its streams into its own part of `out`: stream i =
+ * out[out_off[i], out_off[i] + out_len[i]) (both arrays have n entries); out_cap must be at least the sum of
+ * MaxCompressedLength(len) + 5 over the batch plus 256 bytes per device. */
+int b2c_multi_snappy_compress_crc_batch(b2c_multi* multi, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n,
+                                        void* out, uint64_t out_cap, uint64_t* out_off, uint32_t* out_len, uint32_t* crc,
+                                        int masked);
+/* b2c_snappy_decompress_verify_batch (masked_crc == NULL: b2c_snappy_decompress_batch) over all devices; the decoded
+ * sizes come from the preambles, so the result is packed exactly as by the single-device call: message i =
+ * out[out_off[i], out_off[i+1]). */
+int b2c_multi_snappy_decompress_verify_batch(b2c_multi* multi, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n,
+                                             const uint32_t* masked_crc, void* out, uint64_t out_cap, uint64_t* out_off,
+                                             int32_t* status);
+
 /* Bytes the last *_batch call moved over PCIe (bench.py's e2e accounting). */
 void b2c_last_transfer_bytes(const b2c_ctx* ctx, uint64_t* h2d, uint64_t* d2h);
 
