@@ -78,17 +78,48 @@ struct b2c_multi {
 
 namespace {
 
+// fn(lo, hi, t) over [0, n) on up to 8 short-lived threads (the per-message host passes of a million-message batch
+// would otherwise cost more than the GPUs need for it)
+template <class F>
+void pfor(uint32_t n, F fn) {
+    unsigned hw = std::thread::hardware_concurrency();
+    const unsigned T = n < (1u << 15) ? 1u : std::min(8u, std::max(1u, hw));
+    if (T == 1) {
+        fn(0u, n, 0u);
+        return;
+    }
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < T; t++)
+        th.emplace_back([=, &fn] { fn((uint32_t)((uint64_t)n * t / T), (uint32_t)((uint64_t)n * (t + 1) / T), t); });
+    for (auto& x : th) x.join();
+}
+
 // Cut [0, n) into `parts` contiguous ranges of about equal payload bytes.  cuts[parts + 1].
 void split_by_bytes(b2c_multi* m, const b2c_iovec* segs, const uint32_t* seg_begin, uint32_t n, std::vector<uint32_t>& cuts) {
     const size_t parts = m->workers.size();
     m->prefix.resize((size_t)n + 1);
     uint64_t* p = m->prefix.data();
     p[0] = 0;
-    for (uint32_t i = 0; i < n; i++) {
-        uint64_t l = 0;
-        for (uint32_t s = seg_begin[i]; s < seg_begin[i + 1]; s++) l += segs[s].iov_len;
-        p[i + 1] = p[i] + l + 64;  // + a per-message constant: a million empty bodies still split evenly
-    }
+    uint64_t part[8] = {0};
+    pfor(n, [&](uint32_t lo, uint32_t hi, unsigned t) {  // lengths, and each thread's total
+        uint64_t sum = 0;
+        for (uint32_t i = lo; i < hi; i++) {
+            uint64_t l = 0;
+            for (uint32_t s = seg_begin[i]; s < seg_begin[i + 1]; s++) l += segs[s].iov_len;
+            p[i + 1] = l + 64;  // + a per-message constant: a million empty bodies still split evenly
+            sum += l + 64;
+        }
+        part[t] = sum;
+    });
+    uint64_t base[9] = {0};
+    for (int t = 0; t < 8; t++) base[t + 1] = base[t] + part[t];
+    pfor(n, [&](uint32_t lo, uint32_t hi, unsigned t) {  // prefix sums
+        uint64_t run = base[t];
+        for (uint32_t i = lo; i < hi; i++) {
+            run += p[i + 1];
+            p[i + 1] = run;
+        }
+    });
     cuts.assign(parts + 1, n);
     cuts[0] = 0;
     for (size_t r = 1; r < parts; r++) {
@@ -106,13 +137,16 @@ int run_shards(b2c_multi* m, const b2c_iovec* segs, const uint32_t* seg_begin, c
     for (size_t r = 0; r < parts; r++) {
         const uint32_t m0 = cuts[r], m1 = cuts[r + 1];
         if (m0 == m1) continue;
-        std::vector<uint32_t>& sb = m->sb[r];
-        sb.resize((size_t)(m1 - m0) + 1);
+        // the shard's block list starts at its first block: its worker re-bases seg_begin itself, then runs
+        std::vector<uint32_t>* sbp = &m->sb[r];
         const uint32_t s0 = seg_begin[m0];
-        for (uint32_t i = m0; i <= m1; i++) sb[i - m0] = seg_begin[i] - s0;
         const b2c_iovec* shard_segs = segs + s0;
-        const uint32_t* shard_sb = sb.data();
-        m->workers[r]->start([=, &fn](b2c_ctx* ctx) { return fn(r, ctx, m0, m1, shard_segs, shard_sb); });
+        m->workers[r]->start([=, &fn](b2c_ctx* ctx) {
+            sbp->resize((size_t)(m1 - m0) + 1);
+            uint32_t* sb = sbp->data();
+            for (uint32_t i = m0; i <= m1; i++) sb[i - m0] = seg_begin[i] - s0;
+            return fn(r, ctx, m0, m1, shard_segs, sb);
+        });
     }
     int rc = B2C_OK;
     for (size_t r = 0; r < parts; r++) {
@@ -196,9 +230,16 @@ int b2c_multi_snappy_compress_crc_batch(b2c_multi* m, const b2c_iovec* segs, con
     std::vector<uint32_t> cuts;
     split_by_bytes(m, segs, seg_begin, n, cuts);
     for (size_t r = 0; r < m->workers.size(); r++) {
+        uint64_t part_sum[8] = {0};
+        const uint32_t c0 = cuts[r];
+        pfor(cuts[r + 1] - c0, [&](uint32_t lo, uint32_t hi, unsigned t) {
+            uint64_t sum = 0;
+            for (uint32_t i = c0 + lo; i < c0 + hi; i++)
+                sum += b2c_snappy_max_compressed_length((size_t)(m->prefix[i + 1] - m->prefix[i] - 64)) + 5;
+            part_sum[t] = sum;
+        });
         uint64_t cap = 0;
-        for (uint32_t i = cuts[r]; i < cuts[r + 1]; i++)
-            cap += b2c_snappy_max_compressed_length((size_t)(m->prefix[i + 1] - m->prefix[i] - 64)) + 5;
+        for (uint64_t v : part_sum) cap += v;
         need[r + 1] = need[r] + ((cap + 255) & ~255ull);
     }
     if (need.back() > out_cap) {
@@ -237,17 +278,25 @@ int b2c_multi_snappy_decompress_verify_batch(b2c_multi* m, const b2c_iovec* segs
     const size_t parts = m->workers.size();
     std::vector<uint64_t> base(parts + 1, 0);
     for (size_t r = 0; r < parts; r++) {
+        uint64_t part_sum[8] = {0};
+        const uint32_t c0 = cuts[r];
+        pfor(cuts[r + 1] - c0, [&](uint32_t lo, uint32_t hi, unsigned t) {
+            uint64_t total = 0;
+            for (uint32_t i = c0 + lo; i < c0 + hi; i++) {
+                uint8_t head[5];
+                size_t got = 0;
+                for (uint32_t q = seg_begin[i]; q < seg_begin[i + 1] && got < 5; q++)
+                    for (size_t j = 0; j < segs[q].iov_len && got < 5; j++)
+                        head[got++] = static_cast<const uint8_t*>(segs[q].iov_base)[j];
+                uint32_t ulen = 0;
+                const uint64_t len = m->prefix[i + 1] - m->prefix[i] - 64;
+                const bool plausible = b2c_snappy_read_preamble(head, got, &ulen) > 0 && (uint64_t)ulen <= len * 64 / 3 + 64;
+                total += plausible ? ulen : 0;
+            }
+            part_sum[t] = total;
+        });
         uint64_t total = 0;
-        for (uint32_t i = cuts[r]; i < cuts[r + 1]; i++) {
-            uint8_t head[5];
-            size_t got = 0;
-            for (uint32_t q = seg_begin[i]; q < seg_begin[i + 1] && got < 5; q++)
-                for (size_t j = 0; j < segs[q].iov_len && got < 5; j++) head[got++] = static_cast<const uint8_t*>(segs[q].iov_base)[j];
-            uint32_t ulen = 0;
-            const uint64_t len = m->prefix[i + 1] - m->prefix[i] - 64;
-            const bool plausible = b2c_snappy_read_preamble(head, got, &ulen) > 0 && (uint64_t)ulen <= len * 64 / 3 + 64;
-            total += plausible ? ulen : 0;
-        }
+        for (uint64_t v : part_sum) total += v;
         base[r + 1] = base[r] + total;
     }
     if (base.back() > out_cap) {
