@@ -38,6 +38,7 @@ SYMBOLS = {
     "b2c_ctx_stream": (_vp, [_vp]),
     "b2c_ctx_sync": (C.c_int, [_vp]),
     "b2c_ctx_set_option": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "b2c_ctx_set_tunable": (C.c_int, [_vp, C.c_char_p, C.c_long]),
     "b2c_ctx_launch_count": (C.c_uint64, [_vp]),
     "b2c_dev_alloc": (C.c_int, [_vp, C.c_size_t, C.POINTER(_vp)]),
     "b2c_dev_free": (C.c_int, [_vp, _vp]),
@@ -282,6 +283,9 @@ class Codec:
 
     def set_option(self, option: int, value: int):
         self._check(self.lib.b2c_ctx_set_option(self.ctx, option, value))
+
+    def set_tunable(self, name: str, value: int):
+        self._check(self.lib.b2c_ctx_set_tunable(self.ctx, name.encode(), value))
 
     def sync(self):
         self._check(self.lib.b2c_ctx_sync(self.ctx))

@@ -517,6 +517,53 @@ static void lane_destroy(Lane& l) {
 
 using namespace b2c;
 
+// ---------------------------------------------------------------------------
+// tunables: which kernel variant runs, pipeline geometry.  The defaults are the fastest measured; the others stay
+// selectable (tests/test_gpu_parity.py checks every one for byte-exactness) because which one wins depends on the
+// batch shape.  Set before the first call that uses them.
+// ---------------------------------------------------------------------------
+static const char* const kTunableNames[] = {
+    "slab_mb", "host_threads", "trace", "batch_decode", "ring_decode", "block_decode", "lift_scan", "batch_decode_small",
+    "nt_gather", "gtab_wps", "small_kernels", "small_lpw_c", "small_lpw_d", "window", "window_stage", "window_smem64",
+    "window_wps", "gather_ctas", "gather_warps", "gather_chunk", "lockstep", "lockstep_lpw", "lockstep_d",
+    "lockstep_d_ctas", "async_gather"};
+
+static int apply_tunable(b2c_ctx* ctx, const char* name, long v) {
+    const std::string n(name);
+    if (n == "slab_mb") {  // bytes of payload per pipeline slab (fixes the size: no adaptation to the batch)
+        ctx->slab_bytes = std::max<size_t>(1, (size_t)v) << 20;
+        ctx->slab_fixed = true;
+    } else if (n == "host_threads") {
+        return b2c_ctx_set_option(ctx, B2C_OPT_HOST_THREADS, (int)std::max(0L, v));
+    } else if (n == "trace") ctx->trace = v != 0;
+    else if (n == "batch_decode") ctx->batch_decode = v != 0;
+    else if (n == "ring_decode") ctx->ring_decode = v != 0;
+    else if (n == "block_decode") ctx->block_decode = v != 0;
+    else if (n == "lift_scan") ctx->lift_scan = v != 0;
+    else if (n == "batch_decode_small") ctx->batch_decode_small = v != 0;
+    else if (n == "nt_gather") ctx->nt_gather = v != 0;
+    else if (n == "gtab_wps") ctx->gtab_warps_per_sm = (int)v;
+    else if (n == "small_kernels") ctx->small_kernels = v != 0;
+    else if (n == "small_lpw_c") ctx->small_lpw_compress = (int)v;
+    else if (n == "small_lpw_d") ctx->small_lpw_decompress = (int)v;
+    else if (n == "window") ctx->window_mask = (int)v;
+    else if (n == "window_stage") ctx->window_stage = v != 0;
+    else if (n == "window_smem64") ctx->window_smem64 = v != 0;
+    else if (n == "window_wps") ctx->window_warps_per_sm = (int)v;
+    else if (n == "gather_ctas") ctx->gather_ctas_per_sm = (int)std::max(1L, v);
+    else if (n == "gather_warps") ctx->gather_warps = (int)std::min(32L, std::max(1L, v));
+    else if (n == "gather_chunk") ctx->gather_chunk = (int)std::min(8192L, std::max(512L, v / 16 * 16));
+    else if (n == "lockstep") ctx->small_lockstep = v != 0;
+    else if (n == "lockstep_lpw") {
+        if (v == 4 || v == 8 || v == 16 || v == 32) ctx->lockstep_lpw = (int)v;
+        else return B2C_E_ARG;
+    } else if (n == "lockstep_d") ctx->lockstep_decode = v != 0;
+    else if (n == "lockstep_d_ctas") ctx->lockstep_decode_ctas = (int)std::min(8L, std::max(1L, v));
+    else if (n == "async_gather") ctx->async_gather = v != 0;
+    else return B2C_E_ARG;
+    return B2C_OK;
+}
+
 extern "C" {
 
 // ---------------------------------------------------------------------------
@@ -531,38 +578,13 @@ int b2c_ctx_create(int device, b2c_ctx** out) {
     b2c_ctx* ctx = new (std::nothrow) b2c_ctx();
     if (!ctx) return B2C_E_NOMEM;
     ctx->device = device;
-    if (const char* s = getenv("B2C_SLAB_MB")) {
-        ctx->slab_bytes = std::max<size_t>(1, (size_t)atol(s)) << 20;
-        ctx->slab_fixed = true;
+    // every tunable can also be set through the environment (B2C_<NAME IN CAPITALS>), read once here; the
+    // supported way is b2c_ctx_set_tunable
+    for (const char* name : kTunableNames) {
+        std::string env = "B2C_";
+        for (const char* c = name; *c; c++) env += (char)toupper((unsigned char)*c);
+        if (const char* v = getenv(env.c_str())) apply_tunable(ctx, name, atol(v));
     }
-    if (const char* s = getenv("B2C_HOST_THREADS")) ctx->host_threads = (unsigned)std::max(1L, atol(s));
-    if (const char* s = getenv("B2C_TRACE")) ctx->trace = atoi(s) != 0;
-    if (const char* s = getenv("B2C_BATCH_DECODE")) ctx->batch_decode = atoi(s) != 0;
-    if (const char* s = getenv("B2C_RING_DECODE")) ctx->ring_decode = atoi(s) != 0;
-    if (const char* s = getenv("B2C_BLOCK_DECODE")) ctx->block_decode = atoi(s) != 0;
-    if (const char* s = getenv("B2C_LIFT_SCAN")) ctx->lift_scan = atoi(s) != 0;
-    if (const char* s = getenv("B2C_BATCH_DECODE_SMALL")) ctx->batch_decode_small = atoi(s) != 0;
-    if (const char* s = getenv("B2C_NT_GATHER")) ctx->nt_gather = atoi(s) != 0;
-    if (const char* s = getenv("B2C_GTAB_WPS")) ctx->gtab_warps_per_sm = atoi(s);
-    if (const char* s = getenv("B2C_SMALL_KERNELS")) ctx->small_kernels = atoi(s) != 0;
-    if (const char* s = getenv("B2C_SMALL_LPW_C")) ctx->small_lpw_compress = atoi(s);
-    if (const char* s = getenv("B2C_WINDOW")) ctx->window_mask = atoi(s);
-    if (const char* s = getenv("B2C_WINDOW_STAGE")) ctx->window_stage = atoi(s) != 0;
-    if (const char* s = getenv("B2C_WINDOW_SMEM64")) ctx->window_smem64 = atoi(s) != 0;
-    if (const char* s = getenv("B2C_GATHER_CTAS")) ctx->gather_ctas_per_sm = std::max(1, atoi(s));
-    if (const char* s = getenv("B2C_GATHER_WARPS")) ctx->gather_warps = std::min(32, std::max(1, atoi(s)));
-    if (const char* s = getenv("B2C_GATHER_CHUNK")) ctx->gather_chunk = std::min(8192, std::max(512, atoi(s) / 16 * 16));
-    if (const char* s = getenv("B2C_LOCKSTEP")) ctx->small_lockstep = atoi(s) != 0;
-    if (const char* s = getenv("B2C_LOCKSTEP_D")) ctx->lockstep_decode = atoi(s) != 0;
-    if (const char* s = getenv("B2C_LOCKSTEP_D_CTAS")) ctx->lockstep_decode_ctas = std::min(8, std::max(1, atoi(s)));
-    if (const char* s = getenv("B2C_LOCKSTEP_LPW")) {
-        const int v = atoi(s);
-        if (v == 4 || v == 8 || v == 16 || v == 32) ctx->lockstep_lpw = v;
-    }
-    if (const char* s = getenv("B2C_WINDOW_WPS")) ctx->window_warps_per_sm = atoi(s);
-    if (const char* s = getenv("B2C_ASYNC_GATHER")) ctx->async_gather = atoi(s) != 0;
-    if (const char* s = getenv("B2C_SMALL2")) ctx->small_two_phase = atoi(s) != 0;
-    if (const char* s = getenv("B2C_SMALL_LPW_D")) ctx->small_lpw_decompress = atoi(s);
     int rc = B2C_OK;
     do {
         if ((e = cudaSetDevice(device)) != cudaSuccess) { rc = set_err(ctx, B2C_E_CUDA, "cudaSetDevice", e); break; }
@@ -604,6 +626,11 @@ void b2c_ctx_destroy(b2c_ctx* ctx) {
 const char* b2c_last_error(const b2c_ctx* ctx) { return ctx ? ctx->err.c_str() : "no context"; }
 int b2c_ctx_device(const b2c_ctx* ctx) { return ctx ? ctx->device : -1; }
 void* b2c_ctx_stream(b2c_ctx* ctx) { return ctx ? (void*)ctx->main.stream : nullptr; }
+int b2c_ctx_set_tunable(b2c_ctx* ctx, const char* name, long value) {
+    if (!ctx || !name) return B2C_E_ARG;
+    return apply_tunable(ctx, name, value);
+}
+
 uint64_t b2c_ctx_launch_count(const b2c_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
 int b2c_ctx_set_option(b2c_ctx* ctx, int option, int value) {

@@ -147,7 +147,6 @@ struct b2c_ctx {
     bool batch_decode_small = false; // B2C_BATCH_DECODE_SMALL=1: <=1 KiB slots use the warp batch decoder, not one lane per stream
     bool nt_gather = true;  // B2C_NT_GATHER=0: plain memcpy into staging
     bool async_gather = true;  // B2C_ASYNC_GATHER=0: the submitting thread waits for each slab's gather before anything else
-    bool small_two_phase = true;  // B2C_SMALL2=0 restores the one-phase kernel; <=1 KiB bodies compress as find (lane per body) then encode (warp per body)
     int window_warps_per_sm = 40;  // B2C_WINDOW_WPS: resident warps per SM of the orbit kernel on 64 KiB fragments (tables in HBM/L2; B2C_GTAB_WPS=0 keeps them in shared memory)
     bool window_stage = true;  // B2C_WINDOW_STAGE=0: the window compressor reads <=4 KiB fragments from HBM instead of staging them
     bool window_smem64 = false;  // B2C_WINDOW_SMEM64=1: 64 KiB fragments keep table + TMA-staged fragment in shared memory (one warp per CTA, 2 CTAs per SM); measured 7.6x slower than HBM/L2 tables with 40 warps per SM

@@ -7,10 +7,8 @@
 // own body, a few bodies per warp (LPW), all state in shared memory:
 //   compress:   u16 hash table [entry][slot] (64 KiB per CTA of 32 bodies) + each body in a
 //               contiguous slot fetched by one TMA bulk copy (33 KiB per CTA); two CTAs per SM =
-//               64 bodies in flight.  Default: snappy_compress_small2_kernel — lanes FIND matches
-//               and record them, warps ENCODE the records (see the comment above that kernel);
-//               snappy_compress_small_kernel (B2C_SMALL2=0) encodes from the lane's own loop
-//               through a 64-bit register funnel;
+//               64 bodies in flight.  snappy_compress_small2_kernel: lanes FIND matches and record
+//               them, warps ENCODE the records (see the comment above that kernel);
 //   decompress: each stream's output in a contiguous byte-addressed slot (33 KiB per CTA, 6 CTAs
 //               per SM), so back-references resolve at shared-memory latency; flushed with
 //               coalesced 16-byte stores.
@@ -68,31 +66,6 @@ __device__ __forceinline__ uint32_t hash_bytes_s(uint32_t bytes, uint32_t shift)
     return (bytes * 0x1e35a7bdu) >> shift;
 }
 
-// Output funnel: bytes are appended above `nacc` pending bytes; full words leave at the bottom.
-struct OutFunnel {
-    uint32_t* dst;   // 4-byte aligned
-    uint32_t acc;
-    uint32_t nacc;   // pending bytes (< 4 between pushes)
-    uint32_t words;  // words stored so far
-    __device__ __forceinline__ void push(uint32_t v, uint32_t k) {  // k in 1..4, v has no bits above 8k
-        const uint32_t sh = 8 * nacc;
-        const uint32_t lo = acc | (v << sh);
-        const uint32_t hi = __funnelshift_l(v, 0u, sh);  // v >> (32 - sh), 0 when sh == 0
-        nacc += k;
-        if (nacc >= 4) {
-            dst[words++] = lo;
-            acc = hi;
-            nacc -= 4;
-        } else {
-            acc = lo;
-        }
-    }
-    __device__ __forceinline__ uint32_t finish() {
-        if (nacc) dst[words] = acc;  // slot has MaxCompressedLength's 32 spare bytes
-        return words * 4 + nacc;
-    }
-};
-
 struct SmallCompressParams {
     const uint8_t* in;
     const uint64_t* off;
@@ -107,180 +80,11 @@ struct SmallCompressParams {
     uint32_t n_list;
 };
 
-// CompressFragment for one body by ONE lane.  `in_al` is 4-byte aligned and the body starts `bias`
-// (0..3) bytes after it; `tab` = this body's zeroed table, entries TSTRIDE u16 apart; `dst` 4-byte aligned.
-template <int TSTRIDE>
-__device__ __forceinline__ uint32_t small_compress_body(const uint8_t* in_al, const uint32_t bias, const uint32_t n,
-                                                         uint16_t* tab, uint32_t* dst) {
-    // 8 bytes starting at byte p of this body
-    auto ld64s = [&](uint32_t p) -> uint64_t {
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(in_al + ((p + bias) & ~3u));
-        const uint32_t a = w[0], b = w[1], c = w[2], sh = ((p + bias) & 3) * 8;
-        return ((uint64_t)__funnelshift_r(b, c, sh) << 32) | __funnelshift_r(a, b, sh);
-    };
-    auto ld32s = [&](uint32_t p) -> uint32_t {
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(in_al + ((p + bias) & ~3u));
-        return __funnelshift_r(w[0], w[1], ((p + bias) & 3) * 8);
-    };
-    uint32_t tsize = 256;  // GetHashTable sizing, snappy.cc:253-256
-    while (tsize < 16384u && tsize < n) tsize <<= 1;
-    const uint32_t shift = 32 - (31 - __clz(tsize));
-
-    OutFunnel o;
-    o.dst = dst;
-    o.acc = 0;
-    o.nacc = 0;
-    o.words = 0;
-
-    auto emit_literal = [&](uint32_t from, uint32_t len) {  // EmitLiteral, snappy.cc:156-196
-        const uint32_t n1 = len - 1;
-        if (n1 < 60) {
-            o.push(n1 << 2, 1);
-        } else if (n1 < 256) {
-            o.push((60u << 2) | (n1 << 8), 2);
-        } else {
-            o.push((61u << 2) | (n1 << 8), 3);
-        }
-        uint32_t i = 0;
-        for (; i + 4 <= len; i += 4) o.push(ld32s(from + i), 4);
-        if (i < len) o.push(ld32s(from + i) & ((1u << (8 * (len - i))) - 1u), len - i);
-    };
-
-    uint32_t next_emit = 0;
-    if (n >= 15) {  // kInputMarginBytes, snappy.cc:344-347
-        const uint32_t ip_limit = n - 15;
-        uint32_t ip = 1, skip = 32, nxt = 0;
-        bool probing = true, have_d = false;
-        uint64_t d = 0;  // bytes ip..ip+7 when have_d
-        // One loop for both the probe loop (snappy.cc:377-397) and the copy loop's "is there
-        // another match right here" test (snappy.cc:430-439): they perform the same table step.
-        for (;;) {
-            if (probing) {
-                nxt = ip + (skip++ >> 5);
-                if (nxt > ip_limit) break;  // snappy.cc:386-388
-            }
-            if (!have_d) d = ld64s(ip);
-            have_d = false;
-            const uint32_t cur = (uint32_t)d;
-            const uint32_t h = hash_bytes_s(cur, shift);
-            const uint32_t cand = tab[h * TSTRIDE];
-            tab[h * TSTRIDE] = (uint16_t)ip;
-            const uint64_t x = ld64s(cand) ^ d;
-            if ((uint32_t)x == 0) {
-                if (ip > next_emit) emit_literal(next_emit, ip - next_emit);  // snappy.cc:403
-                // FindMatchLength, snappy-internal.h:86-120.  ip + 15 < n here, so the first 8 bytes are in range.
-                uint32_t matched;
-                const uint32_t xh = (uint32_t)(x >> 32);
-                if (xh) {
-                    matched = 4 + ((uint32_t)(__ffs(xh) - 1) >> 3);
-                } else {
-                    matched = 8;
-                    for (;;) {
-                        const uint32_t rem = n - (ip + matched);
-                        if (rem == 0) break;
-                        const uint64_t y = ld64s(cand + matched) ^ ld64s(ip + matched);
-                        uint32_t nb = y ? (uint32_t)(__ffsll((long long)y) - 1) >> 3 : 8u;
-                        nb = min(nb, rem);
-                        matched += nb;
-                        if (nb < 8) break;
-                    }
-                }
-                // EmitCopy, snappy.cc:198-232
-                {
-                    const uint32_t offset = ip - cand;
-                    uint32_t len = matched;
-                    while (len >= 68) {
-                        o.push(0xfeu | (offset << 8), 3);
-                        len -= 64;
-                    }
-                    if (len > 64) {
-                        o.push((2u + (59u << 2)) | (offset << 8), 3);
-                        len -= 60;
-                    }
-                    if (len < 12 && offset < 2048)
-                        o.push((1u + ((len - 4) << 2) + ((offset >> 8) << 5)) | ((offset & 0xff) << 8), 2);
-                    else
-                        o.push((2u + ((len - 1) << 2)) | (offset << 8), 3);
-                }
-                ip += matched;
-                next_emit = ip;
-                if (ip >= ip_limit) break;  // snappy.cc:427-429
-                // snappy.cc:430-433: insert ip-1; one 4-word read yields both load32(ip-1) and bytes ip..ip+7
-                {
-                    const uint32_t q = ip - 1;
-                    const uint32_t* w = reinterpret_cast<const uint32_t*>(in_al + ((q + bias) & ~3u));
-                    const uint32_t a = w[0], b = w[1], c = w[2], e = w[3], sh = ((q + bias) & 3) * 8;
-                    const uint32_t p0 = __funnelshift_r(a, b, sh), p1 = __funnelshift_r(b, c, sh),
-                                   p2 = __funnelshift_r(c, e, sh);  // bytes q..q+11
-                    tab[hash_bytes_s(p0, shift) * TSTRIDE] = (uint16_t)q;
-                    d = ((uint64_t)__funnelshift_r(p1, p2, 8) << 32) | __funnelshift_r(p0, p1, 8);
-                    have_d = true;
-                }
-                probing = false;
-            } else if (probing) {
-                ip = nxt;
-            } else {  // snappy.cc:441-442: leave the copy loop, resume probing one byte on
-                ip += 1;
-                probing = true;
-                skip = 32;
-            }
-        }
-    }
-    if (next_emit < n) emit_literal(next_emit, n - next_emit);  // emit_remainder, snappy.cc:446-450
-    return o.finish();
-}
-
-template <int LPW>
-__global__ void __launch_bounds__(1024 / LPW) snappy_compress_small_kernel(SmallCompressParams P) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    SmallCompressSmem& sm = *reinterpret_cast<SmallCompressSmem*>(smem_raw);
-    const uint32_t lane = threadIdx.x & 31;
-    const uint32_t slot = (threadIdx.x >> 5) * LPW + lane;  // meaningful for lane < LPW
-    const uint32_t idx = blockIdx.x * 32 + slot;
-    const bool live = lane < LPW && idx < P.n_list;
-    // zero all 32 tables together (GetHashTable's memset, snappy.cc:269)
-    {
-        uint4* t4 = reinterpret_cast<uint4*>(sm.table);
-        for (uint32_t i = threadIdx.x; i < sizeof(sm.table) / 16; i += blockDim.x) t4[i] = make_uint4(0, 0, 0, 0);
-    }
-    uint32_t f = 0, n = 0;
-    const uint8_t* gin = nullptr;
-    if (live) {
-        f = P.frag_list ? P.frag_list[idx] : idx;
-        const uint32_t m = P.frag_msg ? P.frag_msg[f] : f;
-        const uint32_t k = P.frag_first ? f - P.frag_first[m] : 0u;
-        n = min(kFragBytes, P.len[m] - k * kFragBytes);
-        gin = P.in + P.off[m] + (size_t)k * kFragBytes;
-    }
-    // Stage this lane's body into its slot: a 16-byte-aligned body is fetched by ONE TMA bulk copy
-    // (cp.async.bulk global -> shared, completion counted on an mbarrier; no registers, no LSU
-    // instructions); other alignments fall back to word loads.
-    __shared__ uint64_t stage_bar;
-    if (threadIdx.x == 0) mbar_init(&stage_bar, blockDim.x);
-    __syncthreads();
-    uint8_t* in_b = sm.in + (size_t)slot * kSmallInStride;
-    if (live && n && (reinterpret_cast<uintptr_t>(gin) & 15) == 0) {
-        const uint32_t bytes = (n + 15u) & ~15u;
-        mbar_arrive_expect_tx(&stage_bar, bytes);
-        tma_bulk_g2s(in_b, gin, bytes, &stage_bar);
-    } else {
-        if (live)
-            for (uint32_t b = 0; b < n; b += 4) *reinterpret_cast<uint32_t*>(in_b + b) = ld32u(gin + b);
-        mbar_arrive(&stage_bar);
-    }
-    mbar_wait(&stage_bar, 0);
-    __syncthreads();  // the zeroed tables (generic stores of other threads) must be visible too
-    if (!live) return;
-    P.frag_clen[f] = small_compress_body<32>(
-        in_b, 0u, n, sm.table + slot,
-        reinterpret_cast<uint32_t*>(P.scratch + (P.frag_slot ? P.frag_slot[f] : (uint64_t)f * P.slot_stride)));
-}
-
 // ---------------------------------------------------------------------------
 // compress in two phases: FIND (one lane per body) then ENCODE (one warp per body)
 // ---------------------------------------------------------------------------
-// The chain through the hash table is what has to be serial; encoding what it found is not.  In
-// the one-phase kernel above a lane that finds a match spends ~100 further instructions pushing
+// The chain through the hash table is what has to be serial; encoding what it found is not.  In a
+// one-phase kernel (round 1) a lane that finds a match spends ~100 further instructions pushing
 // the literal and the copy through its output funnel while the other lanes of its warp wait
 // (divergence), so almost every trip through the loop pays for the encode path.  Here a lane only
 // RECORDS the match as one packed word (position | offset << 10 | length << 20; all < 1024 for
@@ -639,8 +443,6 @@ constexpr size_t kSmallDecompressSmem = (size_t)kSmallSlotBytes * 32;
 // ---------------------------------------------------------------------------
 template <int LPW>
 static int configure_one(b2c_ctx* ctx) {
-    B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_compress_small_kernel<LPW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)sizeof(SmallCompressSmem)));
     B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_compress_small2_kernel<LPW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)sizeof(SmallCompressSmem)));
     B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_decompress_small_kernel<LPW>,
@@ -674,7 +476,7 @@ int launch_compress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const u
     P.n_list = L.n_class[0];
     const uint32_t blocks = (P.n_list + 31) / 32;
     const size_t smem = sizeof(SmallCompressSmem);
-    if (ctx->small_two_phase) {  // find, then encode; persistent CTAs own their element lists
+    {  // find, then encode; persistent CTAs own their element lists
         const uint32_t grid = std::min<uint32_t>(blocks, (uint32_t)ctx->num_sms * 2);
         int rc;
         if ((rc = ws_reserve(ctx, lane, lane.ws_tab, (size_t)grid * 32 * kSmallMaxElems * 4))) return rc;
@@ -688,16 +490,7 @@ int launch_compress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const u
         }
         ctx->launches++;
         B2C_CUDA(ctx, cudaGetLastError());
-        return B2C_OK;
     }
-    switch (ctx->small_lpw_compress) {
-        case 4: snappy_compress_small_kernel<4><<<blocks, 256, smem, lane.stream>>>(P); break;
-        case 16: snappy_compress_small_kernel<16><<<blocks, 64, smem, lane.stream>>>(P); break;
-        case 32: snappy_compress_small_kernel<32><<<blocks, 32, smem, lane.stream>>>(P); break;
-        default: snappy_compress_small_kernel<8><<<blocks, 128, smem, lane.stream>>>(P); break;
-    }
-    ctx->launches++;
-    B2C_CUDA(ctx, cudaGetLastError());
     return B2C_OK;
 }
 

@@ -87,6 +87,13 @@ int b2c_ctx_sync(b2c_ctx* ctx);
  *     receiver, or one per device) never wait for each other; give each its share of the cores. */
 #define B2C_OPT_HOST_THREADS 2
 int b2c_ctx_set_option(b2c_ctx* ctx, int option, int value);
+/* Implementation tunables by name (kernel variants, pipeline geometry): "window_wps", "small_lpw_c", "slab_mb",
+ * "lockstep", ... -- the list and the meaning of each value are in csrc/b2c_api.cu (kTunableNames /
+ * apply_tunable).  The defaults are the fastest measured; every value is checked for byte-exact results by the
+ * GPU tests.  Each name can also be given through the environment as B2C_<NAME IN CAPITALS>, read once by
+ * b2c_ctx_create (a convenience for experiments).  Unknown names / invalid values: B2C_E_ARG.  No counterpart in
+ * the reference. */
+int b2c_ctx_set_tunable(b2c_ctx* ctx, const char* name, long value);
 /* Number of kernels this ctx has launched so far (bench.py's gpu_launches). */
 uint64_t b2c_ctx_launch_count(const b2c_ctx* ctx);
 

@@ -623,11 +623,12 @@ def test_e2e_zero_copy_refuses_pageable_blocks(codec):
 # ---------------------------------------------------------------- alternate kernel paths stay exact
 @pytest.mark.parametrize("env", [
     {"B2C_WINDOW": "7"},                                   # orbit compressor on every fragment class
-    {"B2C_WINDOW": "0"},                                   # 32-probe warp kernels for fragments > 1 KiB
     {"B2C_WINDOW": "7", "B2C_WINDOW_STAGE": "0", "B2C_GTAB_WPS": "0"},
-    {"B2C_SMALL2": "0"},                                   # one-phase small-body compressor
-    {"B2C_SMALL2": "1", "B2C_SMALL_LPW_C": "2"},           # two bodies per warp
+    {"B2C_WINDOW_SMEM64": "1"},                            # 64 KiB fragments: table + staged fragment in shared memory
+    {"B2C_SMALL_LPW_C": "2"},                              # two bodies per warp
     {"B2C_SMALL_KERNELS": "0"},                            # warp kernels for small bodies too
+    {"B2C_LOCKSTEP": "1"},                                 # lock-step state machines for bodies <= 1 KiB (8 per warp)
+    {"B2C_LOCKSTEP": "1", "B2C_LOCKSTEP_LPW": "32", "B2C_LOCKSTEP_D": "1"},  # 32 per warp; lock-step decoder
     {"B2C_GTAB_WPS": "0", "B2C_BATCH_DECODE": "0"},        # shared-memory tables; one tag per step
     {"B2C_BATCH_DECODE_SMALL": "1", "B2C_RING_DECODE": "1", "B2C_BLOCK_DECODE": "0"},
     {"B2C_LIFT_SCAN": "0"},                                # tag-by-tag block-boundary scan
@@ -673,5 +674,24 @@ def test_alternate_kernel_paths_agree(cpu, env):
         assert (crc == want_crc).all()
         w_out, w_off, w_len, _ = cpu.batch_compress(arena, off, ln, threads=4)
         assert (np.diff(o_off).astype(np.uint32) == w_len).all()
+    finally:
+        c.close()
+
+
+def test_tunables_by_name(cpu):
+    """b2c_ctx_set_tunable: the supported way to pick a kernel variant (the environment is only a shortcut to it)."""
+    import brpc_b200
+    c = brpc_b200.Codec(0)
+    try:
+        with pytest.raises(brpc_b200.B2CError):
+            c.set_tunable("no_such_tunable", 1)
+        with pytest.raises(brpc_b200.B2CError):
+            c.set_tunable("lockstep_lpw", 5)
+        arena, off, ln = O.corpus_batch("words", np.array([1024] * 300 + [5000, 70000], dtype=np.uint32), first_index=3)
+        want = [cpu.compress(arena[int(o):int(o) + int(l)]) for o, l in zip(off, ln)]
+        for name, value in (("lockstep", 1), ("lockstep", 0), ("window", 7), ("window", 6), ("small_lpw_c", 8)):
+            c.set_tunable(name, value)
+            packed, c_off = c.compress(arena, off, ln)
+            assert [packed[int(c_off[i]):int(c_off[i + 1])].tobytes() for i in range(len(ln))] == want, (name, value)
     finally:
         c.close()
