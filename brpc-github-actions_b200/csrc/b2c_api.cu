@@ -658,7 +658,7 @@ int b2c_ctx_sync(b2c_ctx* ctx) {
 int b2c_dev_alloc(b2c_ctx* ctx, size_t bytes, void** d_ptr) {
     if (!ctx || !d_ptr) return B2C_E_ARG;
     B2C_CUDA(ctx, cudaSetDevice(ctx->device));
-    cudaError_t e = cudaMalloc(d_ptr, bytes ? bytes : 1);
+    cudaError_t e = cudaMalloc(d_ptr, bytes + 16);  // room for the aligned unit that holds an arena's last byte
     if (e != cudaSuccess) return set_err(ctx, B2C_E_NOMEM, "cudaMalloc", e);
     return B2C_OK;
 }

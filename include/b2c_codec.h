@@ -25,6 +25,12 @@
  *     return when the results are in host memory.
  *   - thread safety: one ctx may be used by one thread at a time; create one
  *     ctx per worker thread (or guard it) — all ctxs on a device share it.
+ *   - device input arenas of the *_dev entry points (d_in, d_data) must be
+ *     readable for 16 bytes past b2c_layout_arena_bytes(layout): the kernels
+ *     fetch bodies in aligned 16-byte / 4-byte units and the unit that holds a
+ *     message's last byte may extend past it (the bytes are never used).
+ *     b2c_dev_alloc always leaves that room; with your own allocator add 16.
+ *     The *_batch entry points stage into their own padded buffers.
  */
 #ifndef B2C_CODEC_H_
 #define B2C_CODEC_H_
@@ -183,7 +189,12 @@ int b2c_crc32c_dev(b2c_ctx* ctx, const b2c_layout* layout, const void* d_data,
  *   - layouts with more than B2C_CRC32C_NOALLOC_MAX_CHUNKS chunks (sum over
  *     messages of max(1, ceil(len/4096))) are refused with B2C_E_CAPACITY;
  *   - the first call on each device looks up the array's device address; make
- *     that first call before starting any stream capture on that device;
+ *     that first call before starting any stream capture on that device, and
+ *     let it carry at least one message longer than 4 KiB: the CUDA runtime
+ *     loads a kernel's code on its first launch (which allocates), and only a
+ *     multi-chunk message launches both kernels of this entry point;
+ *   - the looked-up address is remembered per device ordinal for the life of
+ *     the process; it does not survive cudaDeviceReset;
  *   - all calls on a device share the one array: two calls whose kernels can
  *     overlap on the GPU (different contexts or streams) race — serialise them;
  *   - the array keeps whatever the previous call left; every slot a call reads

@@ -695,3 +695,35 @@ def test_tunables_by_name(cpu):
             assert [packed[int(c_off[i]):int(c_off[i + 1])].tobytes() for i in range(len(ln))] == want, (name, value)
     finally:
         c.close()
+
+
+def test_dev_entry_points_on_an_exactly_sized_arena(codec, cpu):
+    """The *_dev entry points may read the aligned unit that holds the arena's last byte (documented in
+    include/b2c_codec.h: 16 readable bytes past the arena, which b2c_dev_alloc provides): an arena whose last
+    message ends exactly at its end, uploaded without any padding of the harness's own."""
+    rng = np.random.default_rng(4)
+    for last in (1, 3, 1023, 1024, 4097, 65537):
+        ln = np.array([700, 1024, 13, last], dtype=np.uint32)
+        arena, off, ln = O.corpus_batch("words", ln, align=1)
+        arena = np.ascontiguousarray(arena[:int(off[-1]) + last])  # no slack at all
+        lay = codec.layout(off, ln)
+        d_in = codec.to_device(arena, pad=0)
+        d_crc = codec.alloc(4 * len(ln))
+        codec.crc32c_dev(lay, d_in, d_crc)
+        want, _ = cpu.batch_crc32c(arena, off, ln)
+        assert (codec.d2h(d_crc, 4 * len(ln), np.uint32) == want).all()
+        d_comp = codec.alloc(lay.max_compressed_bytes)
+        d_coff = codec.alloc(8 * (len(ln) + 1))
+        codec.compress_dev(lay, d_in, d_comp, d_coff)
+        c_off = codec.d2h(d_coff, 8 * (len(ln) + 1), np.uint64)
+        packed = codec.d2h(d_comp, int(c_off[-1]))
+        for i in range(len(ln)):
+            assert packed[int(c_off[i]):int(c_off[i + 1])].tobytes() == cpu.compress(arena[int(off[i]):int(off[i]) + int(ln[i])])
+        # decode from an exactly sized arena of streams into an exactly sized output arena
+        d_z = codec.to_device(packed, pad=0)
+        clay = codec.layout(c_off[:-1], np.diff(c_off).astype(np.uint32))
+        d_back = codec.alloc(len(arena))
+        d_st = codec.alloc(4 * len(ln))
+        codec.decompress_dev(clay, d_z, lay, d_back, d_st)
+        assert (codec.d2h(d_st, 4 * len(ln), np.int32) == 0).all()
+        assert codec.d2h(d_back, len(arena)).tobytes() == arena.tobytes()
