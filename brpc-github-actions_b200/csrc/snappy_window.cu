@@ -131,6 +131,20 @@ __device__ uint32_t compress_fragment_orbit(const In in, const uint32_t n, uint8
                 const uint32_t pl = __shfl_sync(kFullMask, pos, last), cl = __shfl_sync(kFullMask, c0, last);
                 uint32_t ml = __shfl_sync(kFullMask, m, last);
                 for (;;) {
+                    // a run-heavy fragment is ONE match of up to 64 KiB: compare 512 bytes per trip (four independent
+                    // pairs of loads per lane) while that much is left, 128 bytes per trip at the end
+                    if (pl + ml + 512 <= n) {
+                        uint32_t x = 0;
+#pragma unroll
+                        for (uint32_t k = 0; k < 4; k++) {
+                            const uint32_t q = ml + 128 * k + 4 * lane;
+                            x |= in.ld32(cl + q) ^ in.ld32(pl + q);
+                        }
+                        if (!__any_sync(kFullMask, x != 0)) {
+                            ml += 512;
+                            continue;
+                        }
+                    }
                     const uint32_t p2 = pl + ml + 4 * lane, p1 = cl + ml + 4 * lane;
                     const uint32_t vb = p2 < n ? min(4u, n - p2) : 0u;
                     uint32_t nb = 0;
