@@ -70,6 +70,7 @@ SYMBOLS = {
     "b2c_snappy_uncompressed_length_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     "b2c_snappy_decompress_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b2c_snappy_validate_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    "b2c_snappy_decodable_prefix_dev": (C.c_int, [_vp, _vp, _vp, _vp]),
     "b2c_snappy_decompress_verify_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b2c_multi_create": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(_vp)]),
     "b2c_multi_destroy": (None, [_vp]),
@@ -360,6 +361,14 @@ class Codec:
         self._check(self.lib.b2c_snappy_decompress_verify_dev(self.ctx, in_layout.h, d_in.ptr, out_layout.h, d_out.ptr,
                                                               d_masked_crc.ptr, d_ulen.ptr if d_ulen else None,
                                                               d_status.ptr))
+
+    def decodable_prefix(self, arena: np.ndarray, off, length) -> np.ndarray:
+        """[n][5] u32: returned size, sunk bytes, consumed, partial literal bytes, partial literal source"""
+        lay = self.layout(off, length)
+        d = self.to_device(arena)
+        d_out = self.alloc(20 * max(lay.n, 1))
+        self._check(self.lib.b2c_snappy_decodable_prefix_dev(self.ctx, lay.h, d.ptr, d_out.ptr))
+        return self.d2h(d_out, 20 * lay.n, np.uint32).reshape(-1, 5)
 
     def validate(self, arena: np.ndarray, off, length):
         lin = self.layout(off, length)

@@ -869,6 +869,12 @@ int b2c_snappy_validate_dev(b2c_ctx* ctx, const b2c_layout* L, const void* d_in,
     return launch_validate(ctx, ctx->main, L->v, static_cast<const uint8_t*>(d_in), d_ulen, d_status);
 }
 
+int b2c_snappy_decodable_prefix_dev(b2c_ctx* ctx, const b2c_layout* L, const void* d_in, uint32_t* d_out5) {
+    if (!ctx || !L || !d_out5) return B2C_E_ARG;
+    B2C_CUDA(ctx, cudaSetDevice(ctx->device));
+    return launch_prefix(ctx, ctx->main, L->v, static_cast<const uint8_t*>(d_in), d_out5);
+}
+
 int b2c_snappy_decompress_verify_dev(b2c_ctx* ctx, const b2c_layout* in, const void* d_in, const b2c_layout* out,
                                      void* d_out, const uint32_t* d_masked_crc, uint32_t* d_ulen, int32_t* d_status) {
     if (!ctx || !in || !out || !d_status || !d_masked_crc) return B2C_E_ARG;

@@ -189,6 +189,7 @@ int launch_ulen(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_
                 int32_t* d_status);
 int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint8_t* d_in, const LayoutView& out,
                       uint8_t* d_out, uint32_t* d_ulen, int32_t* d_status);
+int launch_prefix(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint32_t* d_out5);
 int launch_validate(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint32_t* d_ulen,
                     int32_t* d_status);
 int launch_decompress_verify(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint8_t* d_in,

@@ -968,6 +968,107 @@ __global__ void snappy_ulen_kernel(const uint8_t* __restrict__ in, const uint64_
     if (status) status[m] = k ? B2C_OK : B2C_CORRUPT;
 }
 
+// How far a stream decodes: snappy::UncompressAsMuchAsPossible (snappy.cc:1519-1524).  One thread per stream walks
+// the tags exactly as DecompressAllTags does (snappy.cc:716-787) and keeps the books of the writer that function
+// uses, SnappyScatteredWriter (snappy.cc:1323-1470) — blocks of min(64 KiB, expected - filled), a literal that does not
+// fit fills the current block before it is refused, a literal cut short by the end of the input is appended as far
+// as it goes — without moving any data.  Per stream it reports
+//   [0] what the reference returns (the writer's Size(): larger than what it wrote when a literal was refused after
+//       filling a block, because that block is then counted twice),
+//   [1] the bytes the reference's sink receives,
+//   [2] the stream offset up to which whole tags were applied,
+//   [3] the bytes of one more, partially applied literal, and [4] where in the stream its data starts.
+// A rarely used entry point (nothing in bRPC calls it): serial per stream, not a throughput kernel.
+__global__ void snappy_prefix_kernel(const uint8_t* __restrict__ in, const uint64_t* __restrict__ off,
+                                     const uint32_t* __restrict__ len, uint32_t n_msgs, uint32_t* __restrict__ out5) {
+    const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= n_msgs) return;
+    const uint8_t* src = in + off[m];
+    const uint32_t n = len[m];
+    uint32_t expected = 0;
+    uint32_t ip = read_preamble(src, n, &expected);
+    uint64_t full = 0, blocks = 0;  // full_size_, sum of the sizes of the allocated blocks
+    uint32_t bcap = 0, bused = 0;   // the current block: op_limit_ - op_base_, op_ptr_ - op_base_
+    uint32_t whole = 0, partial = 0, partial_src = 0, consumed = ip;
+    // SnappyScatteredWriter::Append; returns false on refusal, *wrote = bytes that did go in
+    auto append = [&](uint32_t l, uint32_t* wrote) -> bool {
+        *wrote = 0;
+        uint32_t avail = bcap - bused;
+        if (l <= avail) {
+            bused += l;
+            *wrote = l;
+            return true;
+        }
+        while (l > avail) {  // SlowAppend
+            bused += avail;
+            *wrote += avail;
+            full += bused;
+            l -= avail;
+            if (full + l > expected) return false;  // (bused stays: Size() counts this block twice, like the reference)
+            const uint32_t bsize = (uint32_t)min((uint64_t)65536, (uint64_t)expected - full);
+            blocks += bsize;
+            bcap = bsize;
+            bused = 0;
+            avail = bsize;
+        }
+        bused += l;
+        *wrote += l;
+        return true;
+    };
+    if (ip) {
+        while (ip < n) {
+            const uint32_t c = src[ip], kind = c & 3;
+            const uint32_t extra = kind == 0 ? (c >= 0xf0 ? (c >> 2) - 59 : 0) : kind == 1 ? 1 : kind == 2 ? 2 : 4;
+            if (n - ip < 1 + extra) break;  // RefillTag: the tag is cut short
+            uint32_t trailer = 0;
+            for (uint32_t i = 0; i < extra; i++) trailer |= (uint32_t)src[ip + 1 + i] << (8 * i);
+            uint32_t wrote = 0;
+            if (kind == 0) {
+                uint32_t l = (c >> 2) + 1;
+                if (l >= 61) l = trailer + 1u;
+                const uint32_t data = ip + 1 + extra, avail_in = n - data;
+                if (avail_in < l) {  // premature end of input: what is there is appended, then the decoder stops
+                    append(avail_in, &wrote);
+                    partial = wrote;
+                    partial_src = data;
+                    break;
+                }
+                if (!append(l, &wrote)) {
+                    partial = wrote;
+                    partial_src = data;
+                    break;
+                }
+                whole += l;
+                ip = data + l;
+            } else {
+                uint32_t l, offset;
+                if (kind == 1) {
+                    l = ((c >> 2) & 7) + 4;
+                    offset = ((c >> 5) << 8) | trailer;
+                } else {
+                    l = (c >> 2) + 1;
+                    offset = trailer;
+                }
+                // AppendFromSelf: the fast path needs no check beyond the block; the slow path checks first
+                const uint64_t cur = full + bused;
+                const bool fast = offset - 1u < bused && bcap - bused >= l + 10;
+                if (!fast && ((uint64_t)offset - 1u >= cur || (uint64_t)expected - cur < l)) break;
+                append(l, &wrote);  // cannot be refused after the checks above
+                whole += l;
+                ip += 1 + extra;
+            }
+            consumed = ip;
+        }
+    }
+    const uint64_t size = full + bused;
+    out5[5 * m + 0] = (uint32_t)size;
+    out5[5 * m + 1] = (uint32_t)min(size, blocks);
+    out5[5 * m + 2] = consumed;
+    out5[5 * m + 3] = partial;
+    out5[5 * m + 4] = partial_src;
+    (void)whole;
+}
+
 // IsValidCompressed for a batch: the batched decoder's parse + checks, no data movement.
 __global__ void __launch_bounds__(256) snappy_validate_kernel(const uint8_t* __restrict__ in,
                                                               const uint64_t* __restrict__ off,
@@ -1003,6 +1104,14 @@ __global__ void snappy_verify_crc_kernel(const uint32_t* __restrict__ crc, const
     const uint32_t c = crc[m];
     const uint32_t masked = ((c >> 15) | (c << 17)) + 0xa282ead8u;  // crc32c::Mask, crc32c.h:38-41
     if (ulen[m] != cap[m] || masked != masked_want[m]) status[m] = B2C_CRC_MISMATCH;
+}
+
+int launch_prefix(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint32_t* d_out5) {
+    if (L.n == 0) return B2C_OK;
+    snappy_prefix_kernel<<<(L.n + 63) / 64, 64, 0, lane.stream>>>(d_in, L.d_off, L.d_len, L.n, d_out5);
+    ctx->launches++;
+    B2C_CUDA(ctx, cudaGetLastError());
+    return B2C_OK;
 }
 
 int launch_validate(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const uint8_t* d_in, uint32_t* d_ulen,

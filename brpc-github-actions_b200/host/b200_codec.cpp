@@ -352,6 +352,55 @@ bool IsValidCompressed(Source* compressed) {
     return IsValidCompressedBuffer(in.data(), in.size());
 }
 
+size_t UncompressAsMuchAsPossible(Source* compressed, Sink* uncompressed) {
+    const std::string in = drain(compressed);
+    if (in.empty()) return 0;
+    b2c_ctx* ctx = Context::local().get();
+    // how far does it decode?  (b2c_snappy_decodable_prefix_dev keeps the reference writer's books on the device)
+    const uint64_t off = 0;
+    const uint32_t len = (uint32_t)in.size();
+    b2c_layout* lay = nullptr;
+    void *d_in = nullptr, *d_out = nullptr;
+    uint32_t r[5] = {0, 0, 0, 0, 0};
+    int rc = b2c_layout_create(ctx, 1, &off, &len, &lay);
+    if (rc == B2C_OK) rc = b2c_dev_alloc(ctx, in.size(), &d_in);
+    if (rc == B2C_OK) rc = b2c_dev_alloc(ctx, sizeof(r), &d_out);
+    if (rc == B2C_OK) rc = b2c_memcpy_h2d(ctx, d_in, in.data(), in.size());
+    if (rc == B2C_OK) rc = b2c_snappy_decodable_prefix_dev(ctx, lay, d_in, static_cast<uint32_t*>(d_out));
+    if (rc == B2C_OK) rc = b2c_memcpy_d2h(ctx, r, d_out, sizeof(r));
+    if (rc == B2C_OK) rc = b2c_ctx_sync(ctx);
+    if (d_in) b2c_dev_free(ctx, d_in);
+    if (d_out) b2c_dev_free(ctx, d_out);
+    if (lay) b2c_layout_destroy(lay);
+    if (rc != B2C_OK) fail(ctx, "b2c_snappy_decodable_prefix_dev", rc);
+    const uint32_t sunk = r[1], consumed = r[2], partial = r[3], psrc = r[4];
+    if (sunk) {
+        // the prefix as a stream of its own: varint(sunk) || the whole tags || the partially applied literal
+        size_t k = 0;
+        while (k < in.size() && (unsigned char)in[k] >= 128) k++;
+        k++;
+        std::string z;
+        for (uint32_t v = sunk;; v >>= 7) {
+            if (v < 128) {
+                z.push_back((char)v);
+                break;
+            }
+            z.push_back((char)((v & 0x7f) | 0x80));
+        }
+        z.append(in, k, consumed - k);
+        if (partial) {
+            z.push_back((char)(63 << 2));
+            const uint32_t n1 = partial - 1;
+            for (int i = 0; i < 4; i++) z.push_back((char)(n1 >> (8 * i)));
+            z.append(in, psrc, partial);
+        }
+        std::string out(sunk, '\0');
+        if (!RawUncompress(z.data(), z.size(), &out[0])) fail(ctx, "UncompressAsMuchAsPossible: the sound prefix did not decode", B2C_E_ARG);
+        uncompressed->Append(out.data(), out.size());
+    }
+    return r[0];
+}
+
 }  // namespace snappy
 
 namespace crc32c {

@@ -123,6 +123,10 @@ size_t Compress(Source* source, Sink* sink);
 bool Uncompress(Source* compressed, Sink* uncompressed);
 bool GetUncompressedLength(Source* source, uint32_t* result);  // consumes the preamble, snappy.cc:870-873
 bool IsValidCompressed(Source* compressed);
+// snappy.h:104 / snappy.cc:1519-1524: decodes as far as the stream is sound, appends that prefix to the sink and returns
+// what the reference returns (its writer's Size(), which exceeds the appended bytes in the one case where the
+// reference's writer counts a block twice: a literal refused after it filled the current block).
+size_t UncompressAsMuchAsPossible(Source* compressed, Sink* uncompressed);
 }  // namespace snappy
 
 namespace crc32c {

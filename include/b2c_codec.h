@@ -238,6 +238,15 @@ int b2c_snappy_decompress_dev(b2c_ctx* ctx, const b2c_layout* in_layout, const v
 int b2c_snappy_validate_dev(b2c_ctx* ctx, const b2c_layout* in_layout, const void* d_in, uint32_t* d_ulen,
                             int32_t* d_status);
 
+/* How far each stream decodes — the bookkeeping of snappy::UncompressAsMuchAsPossible (snappy.cc:1519-1524, writer
+ * snappy.cc:1323-1470) without moving data.  d_out5[5*i + ...]: [0] the value the reference returns, [1] the number
+ * of bytes its sink receives, [2] the stream offset up to which whole tags were applied, [3] the bytes of one more,
+ * partially applied literal and [4] where in the stream that literal's data starts.  The decoded prefix itself is
+ * then the decode of varint(d[1]) || stream[preamble, d[2]) || literal(stream[d[4], d[4] + d[3])), which the host
+ * mirror b200::snappy::UncompressAsMuchAsPossible builds and runs through b2c_snappy_decompress_batch.  One thread
+ * per stream: a rarely used entry point, not a throughput path. */
+int b2c_snappy_decodable_prefix_dev(b2c_ctx* ctx, const b2c_layout* in_layout, const void* d_in, uint32_t* d_out5);
+
 /* Decompress and verify in one call — the unit of the snappy framing format's
  * compressed chunk (src/butil/third_party/snappy/framing_format.txt:39-59,82-92):
  * d_status[i] = B2C_OK iff stream i decodes (as b2c_snappy_decompress_dev) AND

@@ -204,9 +204,23 @@ def reference() -> Codec | None:
                                                  C.POINTER(C.c_size_t)]
         L.b2r_snappy_uncompress_string.restype = C.c_int
         L.b2r_snappy_uncompress_string.argtypes = [_u8p, C.c_size_t]
+        L.b2r_snappy_uncompress_as_much.restype = C.c_size_t
+        L.b2r_snappy_uncompress_as_much.argtypes = [_u8p, C.c_size_t, _u8p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.b2r_crc32c_is_fast.restype = C.c_int
         L.b2r_crc32c_is_fast.argtypes = []
     return _ref
+
+
+def ref_uncompress_as_much(data):
+    """The reference's snappy::UncompressAsMuchAsPossible on one stream: (returned value, bytes its sink received).
+    Reference library only (the port has no such entry)."""
+    ref = reference()
+    a = _as_u8(data) if len(data) else np.zeros(1, dtype=np.uint8)
+    cap = max(64, len(data) * 22 + 70000)
+    out = np.empty(cap, dtype=np.uint8)
+    sunk = C.c_size_t(0)
+    r = ref.lib.b2r_snappy_uncompress_as_much(_ptr(a, _u8p), len(data), _ptr(out, _u8p), cap, C.byref(sunk))
+    return int(r), out[: sunk.value].tobytes()
 
 
 def best() -> Codec:

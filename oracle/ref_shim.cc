@@ -108,6 +108,18 @@ int b2r_snappy_uncompress_sink(const uint8_t* in, size_t n, size_t chunk, uint8_
     return ok ? 1 : 0;
 }
 
+// snappy::UncompressAsMuchAsPossible (snappy.cc:1519-1524): returns what the reference returns; the bytes its
+// sink received go to out (up to cap) and their count to *sunk.
+size_t b2r_snappy_uncompress_as_much(const uint8_t* in, size_t n, uint8_t* out, size_t cap, size_t* sunk) {
+    sn::ByteArraySource src(reinterpret_cast<const char*>(in), n);
+    std::string s;
+    StringSink sink(&s);
+    const size_t r = sn::UncompressAsMuchAsPossible(&src, &sink);
+    if (sunk) *sunk = s.size();
+    if (!s.empty()) memcpy(out, s.data(), s.size() < cap ? s.size() : cap);
+    return r;
+}
+
 int b2r_snappy_is_valid(const uint8_t* in, size_t n) {
     sn::ByteArraySource src(reinterpret_cast<const char*>(in), n);
     return sn::IsValidCompressed(&src) ? 1 : 0;

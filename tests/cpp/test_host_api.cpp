@@ -415,6 +415,19 @@ static void source_sink() {
             ChunkedSource csrc(cut, 100);
             StringSink junk;
             CHECK(!b200::snappy::Uncompress(&csrc, &junk));
+            // ... and UncompressAsMuchAsPossible yields the body's prefix as far as the stream is sound
+            // (Python test test_decodable_prefix_* compares the same kernel with the reference's function stream by stream)
+            for (size_t keep : {want.size() - 2, want.size() / 2, (size_t)5}) {
+                std::string part = want.substr(0, keep);
+                ChunkedSource psrc(part, 333);
+                StringSink got;
+                const size_t produced = b200::snappy::UncompressAsMuchAsPossible(&psrc, &got);
+                CHECK(produced == got.got.size() && produced <= n && got.got == body.substr(0, produced));
+                if (keep == want.size() - 2) CHECK(produced + 70000 >= n && produced < n);
+            }
+            ChunkedSource fsrc(want, 4096);
+            StringSink all;
+            CHECK(b200::snappy::UncompressAsMuchAsPossible(&fsrc, &all) == n && all.got == body);
         }
     }
 }

@@ -727,3 +727,71 @@ def test_dev_entry_points_on_an_exactly_sized_arena(codec, cpu):
         codec.decompress_dev(clay, d_z, lay, d_back, d_st)
         assert (codec.d2h(d_st, 4 * len(ln), np.int32) == 0).all()
         assert codec.d2h(d_back, len(arena)).tobytes() == arena.tobytes()
+
+
+def test_decodable_prefix_matches_uncompress_as_much_as_possible(codec):
+    """b2c_snappy_decodable_prefix_dev against the reference's snappy::UncompressAsMuchAsPossible (snappy.cc:1519-1524):
+    the value it returns, the number of bytes its sink receives, and — decoding the prefix the kernel describes
+    through the normal decoder — those bytes themselves.  Truncated, damaged and lying streams, and the case where the
+    reference's writer counts a block twice."""
+    if O.reference() is None:
+        pytest.skip("needs oracle/_ref (the reference's own code)")
+    cpu = O.best()
+    rng = np.random.default_rng(17)
+
+    def lit(b):
+        n1 = len(b) - 1
+        if n1 < 60:
+            return bytes([n1 << 2]) + b
+        if n1 < 256:
+            return bytes([60 << 2, n1]) + b
+        if n1 < 65536:
+            return bytes([61 << 2]) + n1.to_bytes(2, "little") + b
+        return bytes([62 << 2]) + n1.to_bytes(3, "little") + b
+
+    streams = [b"", b"\x00", bytes([100]) + lit(b"a" * 30) + lit(b"b" * 150),               # literal refused after filling a block
+               bytes([100]) + lit(b"a" * 30) + bytes([2 | (39 << 2), 10, 0]) + bytes([2 | (59 << 2), 5, 0]),  # copy overruns
+               bytes([100]) + lit(b"a" * 30) + bytes([2 | (39 << 2), 0, 0]),                       # offset 0
+               bytes([10]) + lit(b"x" * 20), bytes([0x80, 0x80, 0x10]) + lit(b"q" * 70000)[:50000]]  # too long; cut literal
+    for t in range(300):
+        body = O.corpus(("words", "az09", "rand62")[t % 3], int(rng.integers(1, 200000)), index=t).tobytes()
+        z = bytearray(cpu.compress(body))
+        how = t % 4
+        if how == 0:
+            z = z[: int(rng.integers(1, len(z) + 1))]
+        elif how == 1:
+            z[int(rng.integers(0, len(z)))] ^= 1 << int(rng.integers(0, 8))
+        elif how == 2 and len(z) > 8:
+            a = int(rng.integers(4, len(z)))
+            z[a:a + 3] = bytes(rng.integers(0, 256, len(z[a:a + 3]), dtype=np.uint8))
+        streams.append(bytes(z))
+    arena, off, ln = pack_tight(streams)
+    got = codec.decodable_prefix(arena, off, ln)
+    synth, want_bytes = [], []
+    for i, s in enumerate(streams):
+        want_ret, sunk = O.ref_uncompress_as_much(s)
+        ret, nsunk, consumed, partial, psrc = (int(x) for x in got[i])
+        assert (ret, nsunk) == (want_ret, len(sunk)), (i, len(s), ret, nsunk, want_ret, len(sunk))
+        # the prefix as a stream of its own: varint(sunk) || whole tags || the partially applied literal
+        k = 0
+        while k < len(s) and s[k] >= 128:
+            k += 1
+        k += 1
+        v, pre = nsunk, bytearray()
+        while v >= 128:
+            pre.append((v & 0x7f) | 0x80)
+            v >>= 7
+        pre.append(v)
+        z = bytes(pre) + s[k:consumed]
+        if partial:
+            z += bytes([63 << 2]) + (partial - 1).to_bytes(4, "little") + s[psrc:psrc + partial]
+        synth.append(z)
+        want_bytes.append(sunk)
+    arena2, off2, ln2 = pack_tight(synth)
+    caps = np.array([len(b) for b in want_bytes], dtype=np.uint32)
+    o_off = np.zeros(len(caps), dtype=np.uint64)
+    o_off[1:] = np.cumsum(caps[:-1].astype(np.uint64))
+    out, ulen, st = codec.decompress(arena2, off2, ln2, o_off, caps)
+    assert (st == 0).all(), np.nonzero(st)[0][:10]
+    for i, b in enumerate(want_bytes):
+        assert out[int(o_off[i]):int(o_off[i]) + len(b)].tobytes() == b, i
