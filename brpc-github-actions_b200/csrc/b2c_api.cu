@@ -525,7 +525,7 @@ using namespace b2c;
 static const char* const kTunableNames[] = {
     "slab_mb", "host_threads", "trace", "batch_decode", "ring_decode", "block_decode", "lift_scan", "batch_decode_small",
     "nt_gather", "gtab_wps", "small_kernels", "small_lpw_c", "small_lpw_d", "window", "window_stage", "window_smem64",
-    "window_wps", "gather_ctas", "gather_warps", "gather_chunk", "lockstep", "lockstep_lpw", "lockstep_d",
+    "window_wps", "gather_ctas", "gather_warps", "gather_chunk", "lockstep", "lockstep_global", "lockstep_lpw", "lockstep_d",
     "lockstep_d_ctas", "async_gather"};
 
 static int apply_tunable(b2c_ctx* ctx, const char* name, long v) {
@@ -554,6 +554,7 @@ static int apply_tunable(b2c_ctx* ctx, const char* name, long v) {
     else if (n == "gather_warps") ctx->gather_warps = (int)std::min(32L, std::max(1L, v));
     else if (n == "gather_chunk") ctx->gather_chunk = (int)std::min(8192L, std::max(512L, v / 16 * 16));
     else if (n == "lockstep") ctx->small_lockstep = v != 0;
+    else if (n == "lockstep_global") ctx->lockstep_global = (int)std::min(32L, std::max(0L, v));
     else if (n == "lockstep_lpw") {
         if (v == 4 || v == 8 || v == 16 || v == 32) ctx->lockstep_lpw = (int)v;
         else return B2C_E_ARG;

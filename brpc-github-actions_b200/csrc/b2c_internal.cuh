@@ -151,6 +151,7 @@ struct b2c_ctx {
     bool window_stage = true;  // B2C_WINDOW_STAGE=0: the window compressor reads <=4 KiB fragments from HBM instead of staging them
     bool window_smem64 = false;  // B2C_WINDOW_SMEM64=1: 64 KiB fragments keep table + TMA-staged fragment in shared memory (one warp per CTA, 2 CTAs per SM); measured 7.6x slower than HBM/L2 tables with 40 warps per SM
     bool small_lockstep = false;  // B2C_LOCKSTEP=1: bodies <= 1 KiB compress with the branch-free lock-step state machines of snappy_lockstep.cu (measured slower than the lane-per-body loops of snappy_small.cu: 15.5 vs 11.0 ms per GiB of 1 KiB `words` bodies)
+    int lockstep_global = 0;     // tunable lockstep_global: > 0 = the lock-step compressor keeps tables and staged bodies in global memory (L2), that many 64-body CTAs resident per SM
     int lockstep_lpw = 8;        // B2C_LOCKSTEP_LPW: bodies per warp of the lock-step compressor (4, 8, 16, 32)
     int window_mask = 6;    // B2C_WINDOW: bit c set = fragment class c (0: <=1 KiB, 1: <=4 KiB, 2: <=64 KiB) compresses with the orbit kernel (snappy_window.cu)
 };

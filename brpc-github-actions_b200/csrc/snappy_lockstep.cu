@@ -28,6 +28,7 @@ struct LockstepParams {
     uint32_t* frag_clen;
     uint32_t n_list;
     uint32_t* elists;  // [resident warps * LPW][ls::kMaxElems]
+    uint32_t* gscratch;  // non-null: tables and staged bodies live here (L2 / HBM), one ls::kGroupWords region per resident 64 slots / 2
 };
 
 struct InInterleaved {  // a body in the interleaved layout: word w at col[w * 32]
@@ -75,13 +76,16 @@ __device__ __forceinline__ void stage_body_warp(uint32_t* __restrict__ col, cons
 }
 
 template <int LPW>
-__global__ void __launch_bounds__(32 * kLsSlotsPerCta / LPW, 1) snappy_compress_lockstep_kernel(LockstepParams P) {
+__global__ void __launch_bounds__(32 * kLsSlotsPerCta / LPW) snappy_compress_lockstep_kernel(LockstepParams P) {
     extern __shared__ __align__(16) uint32_t ls_smem[];
     constexpr uint32_t kWarps = kLsSlotsPerCta / LPW;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t slot0 = warp * LPW;  // first of this warp's slots within the CTA
-    uint32_t* tab = ls_smem + (size_t)(slot0 / ls::kSlots) * ls::kGroupWords + (slot0 % ls::kSlots);  // column of slot0
+    // shared memory (64 slots per SM-resident CTA) or, for the many-more-bodies-in-flight variant, global memory that
+    // the L2 keeps: the lane code is the same, only where its table and body columns live differs
+    uint32_t* base = P.gscratch ? P.gscratch + (size_t)blockIdx.x * (kLsSlotsPerCta / ls::kSlots) * ls::kGroupWords : ls_smem;
+    uint32_t* tab = base + (size_t)(slot0 / ls::kSlots) * ls::kGroupWords + (slot0 % ls::kSlots);  // column of slot0
     uint32_t* body = tab + ls::kTabWords * ls::kSlots;
     const uint32_t gw = blockIdx.x * kWarps + warp;
     uint32_t* my_lists = P.elists + (size_t)gw * LPW * ls::kMaxElems;
@@ -187,16 +191,21 @@ int launch_compress_lockstep(b2c_ctx* ctx, Lane& lane, const LayoutView& L, cons
     P.n_list = L.n_class[0];
     const uint32_t lpw = (uint32_t)ctx->lockstep_lpw;
     const uint32_t ctas = (P.n_list + kLsSlotsPerCta - 1) / kLsSlotsPerCta;
-    const uint32_t grid = std::min<uint32_t>(ctas, (uint32_t)ctx->num_sms);
+    const uint32_t per_sm = ctx->lockstep_global > 0 ? (uint32_t)ctx->lockstep_global : 1u;  // resident CTAs per SM
+    const uint32_t grid = std::min<uint32_t>(ctas, (uint32_t)ctx->num_sms * per_sm);
     int rc;
-    if ((rc = ws_reserve(ctx, lane, lane.ws_tab, (size_t)grid * kLsSlotsPerCta * ls::kMaxElems * 4))) return rc;
+    const size_t list_bytes = (size_t)grid * kLsSlotsPerCta * ls::kMaxElems * 4;
+    const size_t scratch_bytes = ctx->lockstep_global > 0 ? (size_t)grid * kLockstepSmem : 0;
+    if ((rc = ws_reserve(ctx, lane, lane.ws_tab, list_bytes + scratch_bytes + 256))) return rc;
     P.elists = static_cast<uint32_t*>(lane.ws_tab.p);
+    P.gscratch = scratch_bytes ? reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(lane.ws_tab.p) + ((list_bytes + 255) & ~size_t(255))) : nullptr;
+    const size_t smem_bytes = scratch_bytes ? 0 : kLockstepSmem;
     const uint32_t threads = 32 * kLsSlotsPerCta / lpw;
     switch (lpw) {
-        case 4: snappy_compress_lockstep_kernel<4><<<grid, threads, kLockstepSmem, lane.stream>>>(P); break;
-        case 16: snappy_compress_lockstep_kernel<16><<<grid, threads, kLockstepSmem, lane.stream>>>(P); break;
-        case 32: snappy_compress_lockstep_kernel<32><<<grid, threads, kLockstepSmem, lane.stream>>>(P); break;
-        default: snappy_compress_lockstep_kernel<8><<<grid, threads, kLockstepSmem, lane.stream>>>(P); break;
+        case 4: snappy_compress_lockstep_kernel<4><<<grid, threads, smem_bytes, lane.stream>>>(P); break;
+        case 16: snappy_compress_lockstep_kernel<16><<<grid, threads, smem_bytes, lane.stream>>>(P); break;
+        case 32: snappy_compress_lockstep_kernel<32><<<grid, threads, smem_bytes, lane.stream>>>(P); break;
+        default: snappy_compress_lockstep_kernel<8><<<grid, threads, smem_bytes, lane.stream>>>(P); break;
     }
     ctx->launches++;
     B2C_CUDA(ctx, cudaGetLastError());
