@@ -137,6 +137,7 @@ struct b2c_ctx {
     bool lift_scan = true;           // B2C_LIFT_SCAN=0: find the 64 KiB block boundaries with the tag-by-tag scan
     bool block_decode = true;        // B2C_BLOCK_DECODE=0: never split large streams into 64 KiB blocks
     bool ring_attr_done = false;
+    bool seg_dp_attr_done = false;
     bool gather_attr_done = false;
     bool lsd_attr_done = false;
     bool lockstep_decode = false;  // B2C_LOCKSTEP_D=1: slots <= 1 KiB decode with the lock-step state machine of snappy_lockstep_dec.cuh (measured slower than the lane-per-stream loops of snappy_small.cu: 6.8 vs 5.2 ms per GiB of 1 KiB `words` bodies)

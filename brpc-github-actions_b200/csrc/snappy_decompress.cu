@@ -406,56 +406,58 @@ __device__ int decode_message_batched(const uint8_t* __restrict__ in, const uint
         uint32_t pending = __ballot_sync(kFull, is_copy);
         const uint32_t src_pos = out_pos - offset;                         // meaningful for copies
         const uint32_t src_end = offset >= len ? src_pos + len : out_pos;  // bytes read lie in [src_pos, src_end)
-        if (__any_sync(kFull, is_copy && len > 16)) {
-            // long copies (runs, repeated records): one tag at a time, 32 bytes per instruction
-            while (pending) {
-                const uint32_t l = __ffs(pending) - 1;
+        // The first copy that has not run yet goes alone, 32 bytes per instruction, when it is long (runs, repeated
+        // records); otherwise it and every short copy whose source lies entirely below its output position run
+        // together, one lane per tag (their sources are final: everything before the first pending copy is written).
+        while (pending) {
+            const uint32_t first = __ffs(pending) - 1;
+            const uint32_t ln = __shfl_sync(kFull, len, first);
+            const uint32_t frontier = __shfl_sync(kFull, out_pos, first);
+            if (ln > 16) {
                 pending &= pending - 1;
-                const uint32_t d0 = __shfl_sync(kFull, out_pos, l), s0 = __shfl_sync(kFull, src_pos, l),
-                               ln = __shfl_sync(kFull, len, l), of = __shfl_sync(kFull, offset, l);
-                uint8_t v0 = 0, v1 = 0;
+                const uint32_t s0 = __shfl_sync(kFull, src_pos, first), of = __shfl_sync(kFull, offset, first);
                 const uint32_t i0 = lane, i1 = lane + 32;
-                if (i0 < ln) v0 = out.ld(s0 + (of >= ln ? i0 : i0 % of));
-                if (i1 < ln) v1 = out.ld(s0 + (of >= ln ? i1 : i1 % of));
-                if (i0 < ln) out.st(d0 + i0, v0);
-                if (i1 < ln) out.st(d0 + i1, v1);
+                uint8_t v0 = 0, v1 = 0;
+                if (of >= ln) {
+                    if (i0 < ln) v0 = out.ld(s0 + i0);
+                    if (i1 < ln) v1 = out.ld(s0 + i1);
+                } else {  // pattern of `of` bytes repeated, as IncrementalCopy (snappy.cc:98-103)
+                    if (i0 < ln) v0 = out.ld(s0 + i0 % of);
+                    if (i1 < ln) v1 = out.ld(s0 + i1 % of);
+                }
+                if (i0 < ln) out.st(frontier + i0, v0);
+                if (i1 < ln) out.st(frontier + i1, v1);
                 __syncwarp();
+                continue;
             }
-        } else {
-            // short copies: one lane per tag, in dependency rounds — a copy runs once its source lies
-            // entirely below the output position of the first copy that has not run yet
-            while (pending) {
-                const uint32_t first = __ffs(pending) - 1;
-                const uint32_t frontier = __shfl_sync(kFull, out_pos, first);
-                const bool ready = ((pending >> lane) & 1u) && (lane == first || src_end <= frontier);
-                if (ready) {
-                    if (offset >= 4) {
-                        // the 4 source bytes of a round precede its first destination byte (also when the copy overlaps
-                        // itself: IncrementalCopy reads what it wrote `offset` bytes ago, snappy.cc:98-103), so they are
-                        // loaded together: one memory round trip per 4 bytes instead of per byte
-                        uint32_t i = 0;
-                        for (; i + 4 <= len; i += 4) {
-                            const uint8_t b0 = out.ld(src_pos + i), b1 = out.ld(src_pos + i + 1), b2 = out.ld(src_pos + i + 2),
-                                          b3 = out.ld(src_pos + i + 3);
-                            out.st(out_pos + i, b0);
-                            out.st(out_pos + i + 1, b1);
-                            out.st(out_pos + i + 2, b2);
-                            out.st(out_pos + i + 3, b3);
-                        }
-                        for (; i < len; i++) out.st(out_pos + i, out.ld(src_pos + i));
-                    } else if (offset >= len) {
-                        for (uint32_t i = 0; i < len; i++) out.st(out_pos + i, out.ld(src_pos + i));
-                    } else {  // pattern of `offset` bytes repeated, as IncrementalCopy (snappy.cc:98-103)
-                        uint32_t j = 0;
-                        for (uint32_t i = 0; i < len; i++) {
-                            out.st(out_pos + i, out.ld(src_pos + j));
-                            if (++j == offset) j = 0;
-                        }
+            const bool ready = ((pending >> lane) & 1u) && len <= 16 && (lane == first || src_end <= frontier);
+            if (ready) {
+                if (offset >= 4) {
+                    // the 4 source bytes of a round precede its first destination byte (also when the copy overlaps
+                    // itself: IncrementalCopy reads what it wrote `offset` bytes ago, snappy.cc:98-103), so they are
+                    // loaded together: one memory round trip per 4 bytes instead of per byte
+                    uint32_t i = 0;
+                    for (; i + 4 <= len; i += 4) {
+                        const uint8_t b0 = out.ld(src_pos + i), b1 = out.ld(src_pos + i + 1), b2 = out.ld(src_pos + i + 2),
+                                      b3 = out.ld(src_pos + i + 3);
+                        out.st(out_pos + i, b0);
+                        out.st(out_pos + i + 1, b1);
+                        out.st(out_pos + i + 2, b2);
+                        out.st(out_pos + i + 3, b3);
+                    }
+                    for (; i < len; i++) out.st(out_pos + i, out.ld(src_pos + i));
+                } else if (offset >= len) {
+                    for (uint32_t i = 0; i < len; i++) out.st(out_pos + i, out.ld(src_pos + i));
+                } else {  // pattern of `offset` bytes repeated, as IncrementalCopy (snappy.cc:98-103)
+                    uint32_t j = 0;
+                    for (uint32_t i = 0; i < len; i++) {
+                        out.st(out_pos + i, out.ld(src_pos + j));
+                        if (++j == offset) j = 0;
                     }
                 }
-                pending &= ~__ballot_sync(kFull, ready);
-                __syncwarp();
             }
+            pending &= ~__ballot_sync(kFull, ready);
+            __syncwarp();
         }
         produced = batch_end;
         ip = __shfl_sync(kFull, wbase + my_pos + adv, count - 1);
@@ -676,14 +678,24 @@ __device__ bool lift_walk(const uint8_t* __restrict__ in, const uint32_t n, cons
     return true;
 }
 
-constexpr uint32_t kSegBytes = 8192;  // stream bytes per segment (32 windows)
-constexpr uint32_t kSegWins = kSegBytes / kLiftWin;
+constexpr uint32_t kSegBytes = 8192;  // stream bytes per segment
+// A table entry answers, for ONE stream position p of a segment taken as the start of an element: following the chain
+// from p, where does it leave the segment and how much output does it produce on the way.
+//   bits 0-13  E  >= kSegBytes: the chain leaves the segment and stands at segment-relative position E (< 16384, so
+//                 anywhere in the NEXT segment); < kSegBytes: it STOPS in front of position E of this segment, which
+//                 is the stream's end, an element cut short, or an element that reaches beyond the next segment (a long
+//                 literal): whoever follows the chain looks at that position itself
+//   bits 14-31 S  output bytes of the elements passed (at most 64 bytes per 3 stream bytes: < 2^18)
+constexpr uint32_t kDpEBits = 14, kDpEMask = (1u << kDpEBits) - 1u;
+constexpr uint32_t kDpRing = 128;  // entries per thread kept in shared memory: the last 64 finished + the 64 in the making
+constexpr uint32_t kDpNear = 64;   // a successor at most this far ahead is still in the ring
+constexpr uint32_t kDpThreads = 128;
 
 struct SegScanParams {
     DecompressParams D;
     uint32_t* seg_cnt;        // [n_list]    segments of the w-th listed stream (0: not scanned)
     const uint64_t* seg_base; // [n_list+1]  exclusive scan of seg_cnt
-    uint2* seg_tab;           // [segments][256]  (absolute exit position or kLiftBad, output sum) per entry offset
+    uint32_t* seg_tab;        // [segments][kSegBytes]  one entry per stream position
     uint2* bnd;               // [output blocks]  where to start looking for the block's first tag: (stream pos, output before it)
     uint32_t seg_cap;         // capacity of seg_tab in segments
 };
@@ -746,61 +758,139 @@ __global__ void __launch_bounds__(256) snappy_seg_count_kernel(SegScanParams Q) 
     }
 }
 
-// KA: one CTA per segment.  Its 8 warps lift the segment's 32 windows; then thread t follows the chain that enters the
-// segment at offset t (< 256) through the window tables until it leaves the segment.
-__global__ void __launch_bounds__(256) snappy_seg_tables_kernel(SegScanParams Q) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    uint32_t* TN = reinterpret_cast<uint32_t*>(smem_raw);             // [32][256]
-    uint32_t* TS = TN + kSegWins * kLiftWin;                           // [32][256]
-    uint32_t* words = TS + kSegWins * kLiftWin;                        // [8][72]
-    const DecompressParams& P = Q.D;
-    const uint64_t g = blockIdx.x;
-    if (g >= Q.seg_base[P.n_list] || g >= Q.seg_cap) return;
-    uint32_t lo = 0, hi = P.n_list;  // the listed stream w with seg_base[w] <= g < seg_base[w+1]
-    while (hi - lo > 1) {
-        const uint32_t mid = (lo + hi) >> 1;
-        if (Q.seg_base[mid] <= g) lo = mid;
-        else hi = mid;
-    }
-    const uint32_t w = lo, seg = (uint32_t)(g - Q.seg_base[w]);
-    const uint32_t m = P.list ? P.list[w] : w;
-    const uint8_t* in = P.in + P.in_off[m];
-    const uint32_t n = P.in_len[m];
-    const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const uint32_t sbase = seg * kSegBytes;
-    for (uint32_t wi = wib; wi < kSegWins; wi += 8)
-        lift_window(in, n, sbase + wi * kLiftWin, TN + wi * kLiftWin, TS + wi * kLiftWin, words + wib * 72, lane);
-    __syncthreads();
-    uint32_t pos = threadIdx.x, sum = 0;  // segment-relative
-    bool bad = false;
-    for (uint32_t it = 0; it < kSegWins + 1 && pos < kSegBytes; it++) {
-        const uint32_t wi = pos >> 8, e = pos & (kLiftWin - 1);
-        const uint32_t N = TN[wi * kLiftWin + e], S = TS[wi * kLiftWin + e];
-        if (N == kLiftBad) {
-            bad = true;
-            break;
+// KA: one THREAD per segment, from its last position to its first: the entry of p is the entry of p's successor plus
+// p's own output (or "leaves here" / "stops here"), so one backward sweep fills the table with a few dozen
+// instructions per stream byte and no search.  The successor of p is nearly always within 64 bytes (every element but
+// a literal of more than 60 bytes is), where the thread's ring in shared memory still holds its entry (slot-major,
+// lanes adjacent: conflict-free); otherwise the entry is read back from the table, to which every finished run of 64
+// entries is flushed as 16-byte stores.  Positions are taken four at a time: an element is at least 2 bytes, so the
+// entries of p and p - 1 depend on neither each other nor on anything newer, and their lookups go out together.
+struct DpElem {
+    uint32_t nx;    // successor inside the segment whose entry is to be added (when `look`)
+    uint32_t add;   // what to add to it; the whole entry otherwise
+    bool look;
+};
+__device__ __forceinline__ DpElem dp_decode(const uint32_t lo, const uint32_t hi, const uint32_t q, const uint32_t avail) {
+    const uint32_t c = lo & 0xffu, kind = c & 3u, l = c >> 2;
+    uint32_t size = kind == 1 ? 2u : kind == 2 ? 3u : 5u;
+    uint32_t o = kind == 1 ? (l & 7u) + 4u : l + 1u;
+    bool ok = q < avail;
+    if (kind == 0) {
+        size = l + 2u;
+        if (l >= 60u) {
+            const uint32_t ex = l - 59u;
+            uint32_t v = __funnelshift_r(lo, hi, 8);
+            if (ex < 4u) v &= (1u << (8u * ex)) - 1u;
+            ok = ok && v < kDpEMask;  // else it reaches beyond the next segment (or its length wraps): stop
+            o = v + 1u;
+            size = 1u + ex + o;
         }
-        sum = sum + S < sum ? 0xffffffffu : sum + S;
-        if (N == e) {  // the stream's end
-            pos = n - sbase;
-            break;
-        }
-        pos = (wi << 8) + N;  // an element never ends past n, so this stays below 2^32
     }
-    Q.seg_tab[g * kLiftWin + threadIdx.x] = make_uint2(bad ? kLiftBad : sbase + pos, sum);
+    ok = ok && size <= avail - q;  // else cut short by the stream's end
+    const uint32_t nx = q + size;
+    ok = ok && nx <= kDpEMask;
+    DpElem e;
+    e.look = ok && nx < kSegBytes;
+    e.nx = nx;
+    e.add = !ok ? q : e.look ? (o << kDpEBits) : ((o << kDpEBits) | nx);
+    return e;
 }
 
-// KB: one warp per scanned stream hops from segment to segment through the tables (a chain that enters a segment
-// beyond its first window -- after a long literal -- is walked window by window to the segment's end instead), checks
-// that it ends at the stream's end with the announced output, and notes for every block boundary where to look for it.
-__global__ void __launch_bounds__(256) snappy_seg_chain_kernel(SegScanParams Q) {
-    __shared__ LiftScratch scratch[8];
+__global__ void __launch_bounds__(kDpThreads) snappy_seg_dp_kernel(SegScanParams Q) {
+    extern __shared__ __align__(16) uint32_t dp_ring[];  // [warp][slot][lane]
     const DecompressParams& P = Q.D;
     const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const uint32_t w = blockIdx.x * (blockDim.x >> 5) + wib;
+    const uint32_t rbase = wib * (kDpRing * 32) + lane;
+    const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= Q.seg_base[P.n_list] || g >= Q.seg_cap) return;
+    uint32_t lo_w = 0, hi_w = P.n_list;  // the listed stream w with seg_base[w] <= g < seg_base[w+1]
+    while (hi_w - lo_w > 1) {
+        const uint32_t mid = (lo_w + hi_w) >> 1;
+        if (Q.seg_base[mid] <= g) lo_w = mid;
+        else hi_w = mid;
+    }
+    const uint32_t w = lo_w, seg = (uint32_t)(g - Q.seg_base[w]);
+    const uint32_t m = P.list ? P.list[w] : w;
+    const uint32_t n = P.in_len[m];
+    const uint32_t sbase = seg * kSegBytes;
+    const uint8_t* sp = P.in + P.in_off[m] + sbase;
+    const uint32_t avail = n - sbase;  // > 0; positions >= avail lie at or past the stream's end
+    uint32_t* tab = Q.seg_tab + g * kSegBytes;
+    // stream bytes [q16, q16 + 16) as four words, whatever the alignment; a word that starts at or past the end is 0
+    auto load16 = [&](int q16, uint32_t (&out)[4]) {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(sp + q16);
+        const uint32_t* a4 = reinterpret_cast<const uint32_t*>(a & ~uintptr_t(3));
+        const uint32_t sh = (uint32_t)(a & 3) * 8;
+        uint32_t x[5];
+#pragma unroll
+        for (int k = 0; k < 5; k++) x[k] = q16 + 4 * (k ? k - 1 : 0) < (int)avail ? a4[k] : 0u;  // at most 7 bytes past the end
+#pragma unroll
+        for (int k = 0; k < 4; k++) out[k] = q16 + 4 * k < (int)avail ? __funnelshift_r(x[k], x[k + 1], sh) : 0u;
+    };
+    uint32_t cur[4], nxt[4];
+    load16((int)kSegBytes, cur);  // the look-ahead of the last positions
+    uint32_t prev_lo = cur[0], prev_hi = cur[1];  // stream bytes [q + 4, q + 12) of the group at q
+    load16((int)kSegBytes - 16, nxt);
+#pragma unroll 1
+    for (int q16 = (int)kSegBytes - 16; q16 >= 0; q16 -= 16) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) cur[k] = nxt[k];
+        if (q16 >= 16) load16(q16 - 16, nxt);  // one block ahead: its latency hides behind 16 positions
+#pragma unroll
+        for (int k = 3; k >= 0; k--) {
+            const uint32_t q = (uint32_t)q16 + 4 * k;  // positions q + 3, q + 2, q + 1, q
+            const uint32_t w32 = cur[k];
+            DpElem e[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const uint32_t lo = j ? __funnelshift_r(w32, prev_lo, 8 * j) : w32;
+                const uint32_t hi = j ? __funnelshift_r(prev_lo, prev_hi, 8 * j) : prev_lo;
+                e[j] = dp_decode(lo, hi, q + j, avail);
+            }
+#pragma unroll
+            for (int half = 1; half >= 0; half--) {
+                uint32_t t[2];
+#pragma unroll
+                for (int i = 0; i < 2; i++) {
+                    const int j = 2 * half + i;
+                    t[i] = 0;
+                    if (e[j].look)
+                        t[i] = e[j].nx - (q + j) <= kDpNear ? dp_ring[rbase + (e[j].nx & (kDpRing - 1)) * 32]
+                                                           : __ldcg(tab + e[j].nx);
+                }
+#pragma unroll
+                for (int i = 0; i < 2; i++) {
+                    const int j = 2 * half + i;
+                    dp_ring[rbase + ((q + j) & (kDpRing - 1)) * 32] = t[i] + e[j].add;
+                }
+            }
+            prev_hi = prev_lo;
+            prev_lo = w32;
+        }
+        if ((q16 & 63) == 0) {  // entries [q16, q16 + 64) are final
+            uint4* dst = reinterpret_cast<uint4*>(tab + q16);
+            const uint32_t r0 = rbase + ((uint32_t)q16 & (kDpRing - 1)) * 32;
+#pragma unroll 4
+            for (uint32_t i = 0; i < 16; i++)
+                dst[i] = make_uint4(dp_ring[r0 + (4 * i) * 32], dp_ring[r0 + (4 * i + 1) * 32],
+                                    dp_ring[r0 + (4 * i + 2) * 32], dp_ring[r0 + (4 * i + 3) * 32]);
+        }
+    }
+}
+
+__device__ __forceinline__ uint64_t element_at(const uint8_t* __restrict__ in, uint32_t n, uint32_t pos, uint32_t* o) {
+    return lift_element(ld32u(in + pos), pos + 4 < n ? in[pos + 4] : 0u, n - pos, o);
+}
+
+// KB: one thread per scanned stream hops from segment to segment through the table (decoding itself the elements the
+// table stops at), checks that the chain ends at the stream's end with the announced output, and notes for every block
+// boundary the hop it lies in.
+__global__ void __launch_bounds__(kDpThreads) snappy_seg_chain_kernel(SegScanParams Q) {
+    const DecompressParams& P = Q.D;
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= P.n_list) return;
     const uint64_t g0 = Q.seg_base[w];
-    if (Q.seg_base[w + 1] == g0) return;  // not scanned
+    if (Q.seg_base[w + 1] == g0 || Q.seg_base[w + 1] > Q.seg_cap) return;  // not scanned (stays with the whole-stream decoder)
     const uint32_t m = P.list ? P.list[w] : w;
     const uint8_t* in = P.in + P.in_off[m];
     const uint32_t n = P.in_len[m];
@@ -809,57 +899,74 @@ __global__ void __launch_bounds__(256) snappy_seg_chain_kernel(SegScanParams Q) 
     const uint32_t k = read_preamble(in, n, &tmp);
     const uint32_t f0 = P.out_frag_first[m];
     const uint32_t nblk = (expected + kFragBytes - 1) / kFragBytes;
-    if (lane == 0) P.blk_ip[f0] = k;
+    P.blk_ip[f0] = k;
     uint32_t pos = k, cum = 0, nb = 1;
-    bool ok = Q.seg_base[w + 1] <= Q.seg_cap;
-    while (ok && pos < n) {
-        const uint32_t seg = pos / kSegBytes, e = pos - seg * kSegBytes;
+    bool ok = true;
+    while (pos < n) {
+        const uint32_t seg = pos / kSegBytes, q = pos - seg * kSegBytes;
+        const uint32_t t = Q.seg_tab[(g0 + seg) * kSegBytes + q];
+        const uint32_t E = t & kDpEMask, S = t >> kDpEBits;
         const uint32_t pos0 = pos, cum0 = cum;
-        if (e < kLiftWin) {
-            const uint2 t = Q.seg_tab[(g0 + seg) * kLiftWin + e];
-            if (t.x == kLiftBad || t.y > expected - cum) {
+        if (S > expected - cum) {
+            ok = false;
+            break;
+        }
+        cum += S;
+        pos = seg * kSegBytes + E;
+        if (E < kSegBytes && pos < n) {  // an element the table does not take
+            uint32_t o = 0;
+            const uint64_t size = element_at(in, n, pos, &o);
+            if (size == 0 || o > expected - cum) {
                 ok = false;
                 break;
             }
-            pos = t.x;
-            cum += t.y;
-        } else {
-            ok = lift_walk(in, n, expected, pos, cum, (uint64_t)(seg + 1) * kSegBytes, 0u, nullptr, scratch[wib], lane);
-            if (!ok) break;
+            cum += o;
+            pos += (uint32_t)size;  // <= n
         }
         while (nb < nblk && (uint64_t)cum >= (uint64_t)nb * kFragBytes) {  // boundary in (cum0, cum]
-            if (lane == 0) Q.bnd[f0 + nb] = make_uint2(pos0, cum0);
+            Q.bnd[f0 + nb] = make_uint2(pos0, cum0);
             nb++;
         }
     }
-    if (lane == 0 && ok && pos == n && cum == expected && nb == nblk) {
+    if (ok && pos == n && cum == expected && nb == nblk) {
         P.mode[m] = kModeBlocks;
         P.status[m] = B2C_OK;
         if (P.ulen) P.ulen[m] = expected;
     }
 }
 
-// KC: one warp per block boundary walks from the noted position to the tag that starts the block.
-__global__ void __launch_bounds__(256) snappy_seg_boundary_kernel(SegScanParams Q) {
-    __shared__ LiftScratch scratch[8];
+// KC: one thread per block boundary walks, element by element, from the noted position to the tag that starts the
+// block (at most one segment and one long element away).
+__global__ void __launch_bounds__(kDpThreads) snappy_seg_boundary_kernel(SegScanParams Q) {
     const DecompressParams& P = Q.D;
-    const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const uint32_t f = blockIdx.x * (blockDim.x >> 5) + wib;
+    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= P.n_blocks) return;
     const uint32_t m = P.out_frag_msg[f];
     if (P.mode[m] != kModeBlocks) return;
     const uint32_t kb = f - P.out_frag_first[m];
     if (kb == 0) return;
     const uint32_t expected = P.ulen_tmp[m];
-    if ((uint64_t)kb * kFragBytes >= expected) return;
+    const uint64_t want = (uint64_t)kb * kFragBytes;
+    if (want >= expected) return;
+    const uint8_t* in = P.in + P.in_off[m];
+    const uint32_t n = P.in_len[m];
     const uint2 start = Q.bnd[f];
-    uint32_t pos = start.x, cum = start.y, found = 0xffffffffu;
-    const bool ok = lift_walk(P.in + P.in_off[m], P.in_len[m], expected, pos, cum, ~0ull, kb * kFragBytes, &found,
-                              scratch[wib], lane);
-    if (lane == 0) {
-        if (ok && found != 0xffffffffu) P.blk_ip[f] = found;
-        else P.mode[m] = kModeWhole;  // an element straddles the boundary: not splittable
+    uint32_t pos = start.x;
+    uint64_t cum = start.y;
+    bool found = false;
+    while (pos < n) {
+        if (cum == want) {
+            found = true;
+            break;
+        }
+        uint32_t o = 0;
+        const uint64_t size = element_at(in, n, pos, &o);
+        if (size == 0 || cum + o > want) break;  // cut short, or an element straddles the boundary: not splittable
+        cum += o;
+        pos += (uint32_t)size;
     }
+    if (found) P.blk_ip[f] = pos;
+    else P.mode[m] = kModeWhole;
 }
 
 // Pass 2 for large slots: every 64 KiB block of a splittable stream is decoded by its own warp.
@@ -1206,12 +1313,12 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
                 Q.D = P;
                 const size_t seg_cap = (size_t)(in.payload / kSegBytes) + P.n_list + 1;
                 const size_t scan_tmp = ((size_t)(P.n_list + 1023) / 1024 + 2) * 8;
-                const size_t tab_bytes = seg_cap * kLiftWin * sizeof(uint2);
+                const size_t tab_bytes = seg_cap * kSegBytes * sizeof(uint32_t);  // 4 bytes per stream byte
                 const size_t need = tab_bytes + (size_t)out.n_frags * sizeof(uint2) + ((size_t)P.n_list + 1) * 8 +
                                     (size_t)P.n_list * 4 + scan_tmp + 256;
                 if ((rc = ws_reserve(ctx, lane, lane.ws_tab, need))) return rc;
                 uint8_t* wsb = static_cast<uint8_t*>(lane.ws_tab.p);
-                Q.seg_tab = reinterpret_cast<uint2*>(wsb);
+                Q.seg_tab = reinterpret_cast<uint32_t*>(wsb);
                 Q.bnd = reinterpret_cast<uint2*>(wsb + tab_bytes);
                 uint64_t* seg_base = reinterpret_cast<uint64_t*>(wsb + tab_bytes + (size_t)out.n_frags * sizeof(uint2));
                 Q.seg_base = seg_base;
@@ -1221,12 +1328,16 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
                 snappy_seg_count_kernel<<<sblocks, 256, 0, lane.stream>>>(Q);
                 ctx->launches++;
                 if ((rc = launch_scan_u32_u64(ctx, lane, Q.seg_cnt, P.n_list, seg_base, tmp))) return rc;
-                const int tab_smem = (int)(2 * kSegWins * kLiftWin * 4 + 8 * 72 * 4);
-                B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_seg_tables_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                   tab_smem));
-                snappy_seg_tables_kernel<<<(uint32_t)Q.seg_cap, 256, tab_smem, lane.stream>>>(Q);
-                snappy_seg_chain_kernel<<<sblocks, 256, 0, lane.stream>>>(Q);
-                snappy_seg_boundary_kernel<<<(P.n_blocks + 7) / 8, 256, 0, lane.stream>>>(Q);
+                const int dp_smem = (int)((kDpThreads / 32) * kDpRing * 32 * sizeof(uint32_t));
+                if (!ctx->seg_dp_attr_done) {
+                    B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_seg_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                       dp_smem));
+                    ctx->seg_dp_attr_done = true;
+                }
+                snappy_seg_dp_kernel<<<(uint32_t)((Q.seg_cap + kDpThreads - 1) / kDpThreads), kDpThreads, dp_smem,
+                                       lane.stream>>>(Q);
+                snappy_seg_chain_kernel<<<(P.n_list + kDpThreads - 1) / kDpThreads, kDpThreads, 0, lane.stream>>>(Q);
+                snappy_seg_boundary_kernel<<<(P.n_blocks + kDpThreads - 1) / kDpThreads, kDpThreads, 0, lane.stream>>>(Q);
                 ctx->launches += 2;  // + the chain kernel counted with the blocks kernel below
             } else {
                 snappy_scan_kernel<<<sblocks, 256, 8 * kScratchSlot, lane.stream>>>(P);
