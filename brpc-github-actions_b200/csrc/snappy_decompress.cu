@@ -678,14 +678,17 @@ __device__ bool lift_walk(const uint8_t* __restrict__ in, const uint32_t n, cons
     return true;
 }
 
-constexpr uint32_t kSegBytes = 8192;  // stream bytes per segment
+constexpr uint32_t kSegBytes = 2048;  // stream bytes per segment
 // A table entry answers, for ONE stream position p of a segment taken as the start of an element: following the chain
 // from p, where does it leave the segment and how much output does it produce on the way.
-//   bits 0-13  E  >= kSegBytes: the chain leaves the segment and stands at segment-relative position E (< 16384, so
-//                 anywhere in the NEXT segment); < kSegBytes: it STOPS in front of position E of this segment, which
-//                 is the stream's end, an element cut short, or an element that reaches beyond the next segment (a long
+//   bits 0-13  E  >= kSegBytes: the chain leaves the segment and stands at segment-relative position E (< 16384: in
+//                 one of the next segments); < kSegBytes: it STOPS in front of position E of this segment, which is
+//                 the stream's end, an element cut short, or an element that reaches further than E can say (a long
 //                 literal): whoever follows the chain looks at that position itself
-//   bits 14-31 S  output bytes of the elements passed (at most 64 bytes per 3 stream bytes: < 2^18)
+//   bits 14-31 S  output bytes of the elements passed (at most 64 bytes per 3 stream bytes, and one last element of
+//                 less than 16 KiB: < 2^18)
+// Short segments: the sweep is one thread's serial work, a block boundary is then searched element by element inside
+// one segment, and the hop count of the chain (stream bytes / kSegBytes) stays in the hundreds for a 4 MiB body.
 constexpr uint32_t kDpEBits = 14, kDpEMask = (1u << kDpEBits) - 1u;
 constexpr uint32_t kDpRing = 128;  // entries per thread kept in shared memory: the last 64 finished + the 64 in the making
 constexpr uint32_t kDpNear = 64;   // a successor at most this far ahead is still in the ring
@@ -959,6 +962,8 @@ __global__ void __launch_bounds__(kDpThreads) snappy_seg_boundary_kernel(SegScan
             found = true;
             break;
         }
+        // 32 lanes walk 32 different streams: without this, some lane misses the L1 at nearly every step
+        if (pos + 384 < n) asm volatile("prefetch.global.L1 [%0];" ::"l"(in + pos + 384));
         uint32_t o = 0;
         const uint64_t size = element_at(in, n, pos, &o);
         if (size == 0 || cum + o > want) break;  // cut short, or an element straddles the boundary: not splittable
