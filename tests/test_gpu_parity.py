@@ -542,6 +542,48 @@ def test_c5_shape_fragments_decompress_verify(codec, cpu, kind):
     assert set(np.nonzero(st)[0].tolist()) == {3, n - 1} and int(st[3]) == 3
 
 
+def test_large_streams_with_literals_of_every_length_and_damage(codec, cpu):
+    """Streams of 0.2-2.5 MiB whose elements come in every size the block-boundary pass tells apart (short elements,
+    literals of 61-255 / 256-2047 / 2048+ bytes that jump over its near window, its segments and the range of a table
+    entry), whole and damaged: status and bytes must equal the reference's."""
+    rng = np.random.default_rng(77)
+    bodies = []
+    for t, total in enumerate((200_000, 700_000, 2_500_000)):
+        parts, have = [], 0
+        while have < total:
+            if rng.random() < 0.5:
+                n = int(rng.integers(50, 4000))
+                parts.append(O.corpus("words", n, int(rng.integers(0, 1 << 20))).tobytes())
+            else:
+                n = int(rng.choice([61, 70, 200, 256, 300, 2040, 2100, 9000, 17000, 70000]))
+                parts.append(O.corpus("rand62", n, int(rng.integers(0, 1 << 20))).tobytes())
+            have += n
+        bodies.append(b"".join(parts))
+    base = [cpu.compress(np.frombuffer(b, dtype=np.uint8)) for b in bodies]
+    streams = list(base)
+    for t in range(60):
+        z = bytearray(base[t % len(base)])
+        mode = t % 3
+        if mode == 0:
+            z[int(rng.integers(8, len(z)))] ^= 1 << int(rng.integers(0, 8))
+        elif mode == 1:
+            del z[int(rng.integers(len(z) // 2, len(z))):]
+        else:
+            at = int(rng.integers(8, len(z) - 4))
+            z[at:at + 2] = bytes(rng.integers(0, 256, 2, dtype=np.uint8))
+        streams.append(bytes(z))
+    caps = [len(bodies[i % len(bodies)]) for i in range(len(streams))]
+    out, o_off, ulen, status = _decompress(codec, streams, caps=caps)
+    n_ok = 0
+    for i, z in enumerate(streams):
+        ok, want = cpu.uncompress(z, cap=caps[i])
+        assert (status[i] == 0) == ok, (i, int(status[i]), ok)
+        if ok:
+            n_ok += 1
+            assert_bytes_equal(out[int(o_off[i]):int(o_off[i]) + len(want)].tobytes(), want, f"large stream {i}")
+    assert n_ok >= 3
+
+
 def test_large_foreign_stream_falls_back_to_whole_message_decode(codec):
     # a > 64 KiB stream whose copies reach across 64 KiB output boundaries (legal, but never produced by the
     # reference compressor): the boundary scan must refuse to split it and the result must still be exact
@@ -625,6 +667,8 @@ def test_e2e_zero_copy_refuses_pageable_blocks(codec):
     {"B2C_WINDOW": "7"},                                   # orbit compressor on every fragment class
     {"B2C_WINDOW": "7", "B2C_WINDOW_STAGE": "0", "B2C_GTAB_WPS": "0"},
     {"B2C_WINDOW_SMEM64": "1"},                            # 64 KiB fragments: table + staged fragment in shared memory
+    {"B2C_WINDOW_WIDE": "1"},                              # 64 KiB fragments: 16-byte table entries with the candidate's bytes
+    {"B2C_LOCKSTEP": "1", "B2C_LOCKSTEP_GLOBAL": "4"},     # lock-step compressor with its state in global memory
     {"B2C_SMALL_LPW_C": "2"},                              # two bodies per warp
     {"B2C_SMALL_KERNELS": "0"},                            # warp kernels for small bodies too
     {"B2C_LOCKSTEP": "1"},                                 # lock-step state machines for bodies <= 1 KiB (8 per warp)
