@@ -163,6 +163,7 @@ __device__ __forceinline__ uint64_t warp_incl_scan_u64(uint64_t v, uint32_t lane
 // small slots, or the final HBM slot).
 struct LinearOut {
     static constexpr bool kMovesData = true;
+    static constexpr bool kLinear = true;  // byte p lives at base[p]: copy loops may walk raw pointers
     uint8_t* base;
     __device__ __forceinline__ void on_tag(bool, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {}
     __device__ __forceinline__ uint8_t ld(uint32_t p) const { return base[p]; }
@@ -183,6 +184,7 @@ struct LinearOut {
 // are read back from HBM, where the ring is flushed in 16-byte stores as it fills.
 struct RingOut {
     static constexpr bool kMovesData = true;
+    static constexpr bool kLinear = false;
     __device__ __forceinline__ void on_tag(bool, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {}
     uint8_t* ring;      // 65536 bytes of shared memory
     uint8_t* gout;      // final slot in HBM
@@ -238,6 +240,7 @@ struct RingOut {
 // blocks, snappy.h:193-203); its blocks can then be decoded independently, one warp each.
 struct ScanOut {
     static constexpr bool kMovesData = false;
+    static constexpr bool kLinear = false;
     uint32_t* blk_ip;  // [nblk] stream offset where output block k starts
     uint32_t nblk;
     uint32_t bad;      // per-lane: something prevents splitting
@@ -414,8 +417,30 @@ __device__ int decode_message_batched(const uint8_t* __restrict__ in, const uint
             const uint32_t ln = __shfl_sync(kFull, len, first);
             const uint32_t frontier = __shfl_sync(kFull, out_pos, first);
             if (ln > 16) {
-                pending &= pending - 1;
                 const uint32_t s0 = __shfl_sync(kFull, src_pos, first), of = __shfl_sync(kFull, offset, first);
+                if constexpr (Out::kLinear) {
+                    // A run (zero fill, a repeated record) arrives as consecutive copies with one offset: together
+                    // they say out[p] = out[p - of] for every p of the run, i.e. ONE copy of their total length.  It
+                    // is made by doubling: what is already there is a whole number of periods, so it can be appended
+                    // to itself 32 bytes per instruction (source and destination of one step never overlap).
+                    const uint32_t same = __ballot_sync(kFull, is_copy && offset == of) >> first;
+                    const uint32_t run = same == kFull ? 32u - first : (uint32_t)__ffs(~same) - 1u;  // >= 1
+                    const uint32_t lastl = first + run - 1;
+                    const uint32_t total = __shfl_sync(kFull, out_pos + len, lastl) - frontier;
+                    if (run >= 2 && total >= 128) {
+                        uint8_t* d0 = out.base + frontier;
+                        const uint8_t* sp = d0 - of;
+                        for (uint32_t done = 0; done < total;) {
+                            const uint32_t nmove = min(total - done, of + done);
+                            for (uint32_t i = lane; i < nmove; i += 32) d0[done + i] = sp[i];
+                            __syncwarp();
+                            done += nmove;
+                        }
+                        pending &= ~(((run == 32u ? 0u : (1u << run)) - 1u) << first);
+                        continue;
+                    }
+                }
+                pending &= pending - 1;
                 const uint32_t i0 = lane, i1 = lane + 32;
                 uint8_t v0 = 0, v1 = 0;
                 if (of >= ln) {
@@ -432,7 +457,24 @@ __device__ int decode_message_batched(const uint8_t* __restrict__ in, const uint
             }
             const bool ready = ((pending >> lane) & 1u) && len <= 16 && (lane == first || src_end <= frontier);
             if (ready) {
-                if (offset >= 4) {
+                if constexpr (Out::kLinear) {
+                    // the same three cases as below on raw pointers: one 64-bit address per copy instead of one per byte
+                    uint8_t* d = out.base + out_pos;
+                    const uint8_t* sp = d - offset;
+                    uint8_t* const de = d + len;
+                    if (offset >= 4) {
+                        for (; d + 4 <= de; d += 4, sp += 4) {
+                            const uint8_t b0 = sp[0], b1 = sp[1], b2 = sp[2], b3 = sp[3];
+                            d[0] = b0;
+                            d[1] = b1;
+                            d[2] = b2;
+                            d[3] = b3;
+                        }
+                        for (; d < de; d++, sp++) *d = *sp;
+                    } else {  // offset 1-3: every byte repeats the one `offset` back, also across the pattern's end
+                        for (; d < de; d++, sp++) *d = *sp;
+                    }
+                } else if (offset >= 4) {
                     // the 4 source bytes of a round precede its first destination byte (also when the copy overlaps
                     // itself: IncrementalCopy reads what it wrote `offset` bytes ago, snappy.cc:98-103), so they are
                     // loaded together: one memory round trip per 4 bytes instead of per byte
