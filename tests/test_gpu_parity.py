@@ -255,6 +255,26 @@ def test_decompress_corrupted_streams_agree_with_oracle(codec, cpu):
     assert 0 < n_ok < len(streams)
 
 
+def test_decompress_runs_of_every_period(codec, cpu):
+    """Runs: consecutive copies with one offset are decoded as one period extension; every period from 1 byte to more
+    than a batch of copies produces, in slots of every decoder class, must still give the reference's bytes."""
+    rng = np.random.default_rng(5)
+    msgs = []
+    for period in (1, 2, 3, 4, 5, 7, 16, 36, 63, 64, 65, 100, 255, 1000, 2047, 2048, 5000):
+        pat = rng.integers(0, 256, period, dtype=np.uint8).tobytes()
+        for total in (900, 7000, 66000, 300000):
+            body = (pat * (total // period + 1))[:total]
+            if total > 7000:  # a run interrupted by other data now and then
+                body = body[:total // 2] + O.corpus("words", 300, period).tobytes() + body[total // 2:]
+            msgs.append(body)
+    streams = [cpu.compress(np.frombuffer(m, dtype=np.uint8)) for m in msgs]
+    out, o_off, ulen, status = _decompress(codec, streams)
+    assert (status == 0).all(), np.nonzero(status)[0]
+    for i, m in enumerate(msgs):
+        assert int(ulen[i]) == len(m)
+        assert_bytes_equal(out[int(o_off[i]):int(o_off[i]) + len(m)].tobytes(), m, f"run {i}")
+
+
 def test_decompress_too_small_and_ulen(codec, cpu):
     streams = [cpu.compress(O.corpus("words", n, n)) for n in (100, 1000, 10000)]
     out, o_off, ulen, status = _decompress(codec, streams, caps=[100, 999, 20000])
