@@ -57,6 +57,15 @@ int ws_reserve(b2c_ctx* ctx, Lane& lane, DevBuf& b, size_t bytes) {
     return B2C_OK;
 }
 
+int next_work_counter(b2c_ctx* ctx, Lane& lane, uint32_t** ctr) {
+    int rc = ws_reserve(ctx, lane, lane.ws_ctr, 64 * sizeof(uint32_t));
+    if (rc) return rc;
+    uint32_t* p = static_cast<uint32_t*>(lane.ws_ctr.p) + (lane.ctr_next++ & 63u);
+    B2C_CUDA(ctx, cudaMemsetAsync(p, 0, sizeof(uint32_t), lane.stream));
+    *ctr = p;
+    return B2C_OK;
+}
+
 // Grow-only pinned buffer; the first `keep` bytes survive a growth.
 static int pin_reserve(b2c_ctx* ctx, Lane& lane, PinBuf& b, size_t bytes, size_t keep = 0) {
     if (bytes <= b.cap) return B2C_OK;
@@ -503,7 +512,7 @@ static int lane_create(b2c_ctx* ctx, Lane& l) {
 
 static void lane_destroy(Lane& l) {
     if (l.stream) cudaStreamSynchronize(l.stream);
-    for (DevBuf* b : {&l.ws_frag, &l.ws_misc, &l.ws_tab, &l.ws_wide, &l.d_in, &l.d_out})
+    for (DevBuf* b : {&l.ws_frag, &l.ws_misc, &l.ws_tab, &l.ws_wide, &l.ws_ctr, &l.d_in, &l.d_out})
         if (b->p) cudaFree(b->p);
     for (PinBuf* b : {&l.h_in, &l.h_out})
         if (b->p) cudaFreeHost(b->p);

@@ -33,6 +33,8 @@ struct Lane {
     DevBuf ws_tab;    // hash tables of the 64 KiB-fragment compressor (one 32 KiB table per resident warp)
     DevBuf ws_wide;   // ... its wide-entry tables (256 KiB per resident warp); written by that kernel alone
     uint32_t wide_epoch = 0;  // epochs handed out since ws_wide was last zeroed
+    DevBuf ws_ctr;    // 64 work counters handed out in turn to kernels whose warps pull their work items
+    uint32_t ctr_next = 0;
     DevBuf d_in;      // e2e: device input arena (+ layout blob)
     DevBuf d_out;     // e2e: device output arena (+ result metadata)
     PinBuf h_in;      // e2e: pinned staging, host -> device
@@ -174,6 +176,9 @@ namespace b2c {
 
 int set_err(b2c_ctx* ctx, int code, const char* what, cudaError_t e);
 int ws_reserve(b2c_ctx* ctx, Lane& lane, DevBuf& b, size_t bytes);
+// A zeroed u32 in device memory for ONE launch on lane.stream (warps take work items with atomicAdd instead of a fixed
+// share: items differ in size, and many are skipped).  64 are in rotation; stream order keeps a reused one safe.
+int next_work_counter(b2c_ctx* ctx, Lane& lane, uint32_t** ctr);
 
 #define B2C_CUDA(ctx, call)                                         \
     do {                                                            \

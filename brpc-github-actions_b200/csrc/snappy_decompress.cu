@@ -527,6 +527,7 @@ struct DecompressParams {
     uint32_t* mode;                  // [n] kModeWhole / kModeBlocks / kModeDone
     uint32_t* ulen_tmp;              // [n] uncompressed lengths for the block kernel
     uint32_t n_blocks;
+    uint32_t* work_ctr;              // warps take the next stream / block from here (null: one each, by index)
 };
 
 enum : uint32_t { kModeWhole = 0, kModeBlocks = 1, kModeDone = 2 };
@@ -1021,23 +1022,29 @@ __global__ void __launch_bounds__(256, 5) snappy_decompress_blocks_kernel(Decomp
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t wib = threadIdx.x >> 5;
-    const uint32_t f = blockIdx.x * (blockDim.x >> 5) + wib;
-    if (f >= P.n_blocks) return;
-    const uint32_t m = P.out_frag_msg[f];
-    if (P.mode[m] != kModeBlocks) return;
-    const uint32_t kblk = f - P.out_frag_first[m];
-    const uint32_t expected = P.ulen_tmp[m];
-    const uint32_t begin = kblk * kFragBytes;
-    if (begin >= expected) return;
-    const uint32_t block_len = min(kFragBytes, expected - begin);
-    const uint32_t ip0 = P.blk_ip[f];
-    const uint32_t ip1 = begin + kFragBytes < expected ? P.blk_ip[f + 1] : P.in_len[m];
-    LinearOut lo{P.out + P.out_off[m] + begin};
     BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * kScratchSlot);
-    const int st = decode_message_batched(P.in + P.in_off[m], ip1, ip0, lo, block_len, lane, sc);
-    // a block that does not decode on its own: the stream is corrupt, or merely not splittable (a copy that reaches
-    // back across the block's start); the whole-stream decoder, launched next, redoes it and decides
-    if (st != B2C_OK && lane == 0) P.mode[m] = kModeWhole;
+    // resident warps pull blocks: the list holds every block of the batch, those of streams decoded elsewhere included
+    for (;;) {
+        uint32_t f = 0;
+        if (lane == 0) f = atomicAdd(P.work_ctr, 1u);
+        f = __shfl_sync(kFull, f, 0);
+        if (f >= P.n_blocks) return;
+        const uint32_t m = P.out_frag_msg[f];
+        if (P.mode[m] != kModeBlocks) continue;
+        const uint32_t kblk = f - P.out_frag_first[m];
+        const uint32_t expected = P.ulen_tmp[m];
+        const uint32_t begin = kblk * kFragBytes;
+        if (begin >= expected) continue;
+        const uint32_t block_len = min(kFragBytes, expected - begin);
+        const uint32_t ip0 = P.blk_ip[f];
+        const uint32_t ip1 = begin + kFragBytes < expected ? P.blk_ip[f + 1] : P.in_len[m];
+        LinearOut lo{P.out + P.out_off[m] + begin};
+        __syncwarp();
+        const int st = decode_message_batched(P.in + P.in_off[m], ip1, ip0, lo, block_len, lane, sc);
+        // a block that does not decode on its own: the stream is corrupt, or merely not splittable (a copy that reaches
+        // back across the block's start); the whole-stream decoder, launched next, redoes it and decides
+        if (st != B2C_OK && lane == 0) P.mode[m] = kModeWhole;
+    }
 }
 
 
@@ -1045,10 +1052,15 @@ __global__ void __launch_bounds__(256, 5) snappy_decompress_kernel(DecompressPar
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t wib = threadIdx.x >> 5;
-    const uint32_t w = blockIdx.x * (blockDim.x >> 5) + wib;
+    // resident warps pull streams (their sizes differ, and those decoded block-parallel are only skipped)
+    for (;;) {
+    uint32_t w = 0;
+    if (lane == 0) w = atomicAdd(P.work_ctr, 1u);
+    w = __shfl_sync(kFull, w, 0);
     if (w >= P.n_list) return;
     const uint32_t m = P.list ? P.list[w] : w;
-    if (P.mode && P.mode[m] != kModeWhole) return;  // decoded block-parallel, or already rejected by the scan
+    if (P.mode && P.mode[m] != kModeWhole) continue;  // decoded block-parallel, or already rejected by the scan
+    __syncwarp();
     const uint8_t* in = P.in + P.in_off[m];
     const uint32_t n = P.in_len[m];
     uint8_t* gout = P.out + P.out_off[m];
@@ -1108,6 +1120,7 @@ __global__ void __launch_bounds__(256, 5) snappy_decompress_kernel(DecompressPar
     if (lane == 0) {
         P.status[m] = st;
         if (P.ulen) P.ulen[m] = expected;
+    }
     }
 }
 
@@ -1340,6 +1353,7 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
         P.mode = nullptr;
         P.ulen_tmp = nullptr;
         P.n_blocks = 0;
+        P.work_ctr = nullptr;
         P.batched = ctx->batch_decode ? 1u : 0u;
         if (c == 2 && ctx->batch_decode && ctx->block_decode && out.d_frag_msg) {
             // large slots: scan for block boundaries, decode splittable streams one warp per 64 KiB block
@@ -1389,8 +1403,10 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
             } else {
                 snappy_scan_kernel<<<sblocks, 256, 8 * kScratchSlot, lane.stream>>>(P);
             }
-            const uint32_t bblocks = (P.n_blocks + 7) / 8;
+            if ((rc = next_work_counter(ctx, lane, &P.work_ctr))) return rc;
+            const uint32_t bblocks = std::min<uint32_t>((P.n_blocks + 7) / 8, (uint32_t)ctx->num_sms * 5u);
             snappy_decompress_blocks_kernel<<<bblocks, 256, 8 * kScratchSlot, lane.stream>>>(P);
+            P.work_ctr = nullptr;
             ctx->launches += 2;
             B2C_CUDA(ctx, cudaGetLastError());
         }
@@ -1406,7 +1422,12 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
                 ctx->ring_attr_done = true;
             }
         }
-        const uint32_t blocks = (P.n_list + wpb - 1) / wpb;
+        {
+            int rc = next_work_counter(ctx, lane, &P.work_ctr);
+            if (rc) return rc;
+        }
+        // enough CTAs to fill every SM whatever the class's shared memory allows; the others find the list empty
+        const uint32_t blocks = std::min<uint32_t>((P.n_list + wpb - 1) / wpb, (uint32_t)ctx->num_sms * (P.ring ? 3u : 8u));
         snappy_decompress_kernel<<<blocks, wpb * 32, smem, lane.stream>>>(P);
         ctx->launches++;
         B2C_CUDA(ctx, cudaGetLastError());

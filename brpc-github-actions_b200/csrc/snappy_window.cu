@@ -272,6 +272,7 @@ struct WindowParams {
     uint16_t* gtab;          // 16384 entries per resident warp when table_entries == 0
     uint4* gwide;            // kWide: 16384 16-byte entries per resident warp
     uint32_t epoch_base;     // kWide: the k-th fragment of a warp in this launch has epoch epoch_base + 1 + k (< 65536)
+    uint32_t* work_ctr;      // warps take the next listed fragment from here (null: every total-th one)
 };
 
 __device__ __forceinline__ uint32_t smem_addr32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -303,7 +304,12 @@ __global__ void __launch_bounds__(256, kWide ? 5 : 0) snappy_compress_orbit_kern
     uint32_t parity = 0;
     uint32_t epoch = P.epoch_base;
     uint4* wide = kWide ? P.gwide + (size_t)gw * 16384 : nullptr;
-    for (uint32_t w = gw; w < P.n_list; w += total) {
+    for (uint32_t w = gw;; w += total) {
+        if (P.work_ctr) {  // fragments differ in length (the last one of a body): whoever is free takes the next
+            if (lane == 0) w = atomicAdd(P.work_ctr, 1u);
+            w = __shfl_sync(kFullMask, w, 0);
+        }
+        if (w >= P.n_list) break;
         ++epoch;
         const uint32_t f = P.frag_list ? P.frag_list[w] : w;
         const uint32_t m = P.frag_msg ? P.frag_msg[f] : f;
@@ -437,6 +443,11 @@ int launch_compress_window(b2c_ctx* ctx, Lane& lane, const LayoutView& L, int c,
         int rc;
         if ((rc = ws_reserve(ctx, lane, lane.ws_tab, (size_t)blocks * wpb * 32768))) return rc;
         P.gtab = static_cast<uint16_t*>(lane.ws_tab.p);
+    }
+    P.work_ctr = nullptr;
+    if (!wide) {  // (the wide tables count their epochs per warp: fixed shares)
+        int rc = next_work_counter(ctx, lane, &P.work_ctr);
+        if (rc) return rc;
     }
     const size_t smem = (size_t)wpb * per_warp;
     if (wide)
