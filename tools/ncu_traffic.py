@@ -10,7 +10,7 @@ import json
 import sys
 
 OPS = (("crc32c_chunks", "crc32c"), ("snappy_compress", "compress"), ("snappy_decompress", "decompress"),
-       ("snappy_gather_kernel", "pack"))
+       ("snappy_seg_", "decompress"), ("snappy_gather_kernel", "pack"))  # an op of several kernels: their sum
 
 
 def to_bytes(value, unit):
@@ -18,7 +18,7 @@ def to_bytes(value, unit):
     return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}[unit]
 
 
-out = {"_source": "ncu --set full --clock-control none captures of tools/devbench.py (profiles/r2_ncu_full_key_metrics_*.txt)"}
+out = {"_source": "ncu --set full --clock-control none captures of tools/devbench.py, one launch of every kernel of the op (profiles/r2_ncu_full_key_metrics_*.txt)"}
 for spec in sys.argv[1:]:
     key, path = spec.split("=")
     rows = list(csv.reader(open(path)))
@@ -32,6 +32,6 @@ for spec in sys.argv[1:]:
             if pat in name:
                 rd = to_bytes(r[ix["dram__bytes_read.sum"]], units[ix["dram__bytes_read.sum"]])
                 wr = to_bytes(r[ix["dram__bytes_write.sum"]], units[ix["dram__bytes_write.sum"]])
-                out[f"{key}/{op}"] = int(rd + wr)
+                out[f"{key}/{op}"] = out.get(f"{key}/{op}", 0) + int(rd + wr)
                 break
 print(json.dumps(out, indent=1))
