@@ -44,31 +44,10 @@ __device__ __forceinline__ uint32_t flush_queue(const In& in, const uint2* queue
 
 // CompressFragment by one warp.  `T` = `tsize` zeroed u16 slots (shared or global memory); `queue` = kQueue
 // uint2 of shared memory private to the warp.
-// kWide: the table lives in HBM as 16-byte entries {position | epoch << 16, the 12 input bytes at that position}.  A
-// probe then brings the candidate's bytes with it: a round waits for ONE memory round trip (the table sector) instead
-// of two dependent ones (table, then the candidate's bytes), and a match is known up to kCapWide = 12 bytes without
-// touching the input again (longer ones are finished by the capped-match loop).  The epoch, one per fragment a warp
-// compresses, stands for the zero-fill: an entry of another epoch reads as the empty slot, i.e. position 0.
-static constexpr uint32_t kCapWide = 12;
-__device__ __forceinline__ uint32_t prefix12(uint32_t a0, uint32_t a1, uint32_t a2, uint32_t b0, uint32_t b1, uint32_t b2) {
-    const uint32_t x0 = a0 ^ b0, x1 = a1 ^ b1, x2 = a2 ^ b2;
-    const uint32_t x = x0 ? x0 : x1 ? x1 : x2;
-    const uint32_t base = x0 ? 0u : x1 ? 4u : 8u;
-    return x ? base + ((uint32_t)(__ffs(x) - 1) >> 3) : 12u;
-}
-
-template <bool kWide, class In>
+template <class In>
 __device__ uint32_t compress_fragment_orbit(const In in, const uint32_t n, uint8_t* __restrict__ out, uint16_t* T,
-                                            const uint32_t tsize, uint2* queue, const uint32_t lane,
-                                            uint4* TW = nullptr, const uint32_t epoch = 0) {
-    constexpr uint32_t kCap = kWide ? kCapWide : b2c::kCap;
+                                            const uint32_t tsize, uint2* queue, const uint32_t lane) {
     const uint32_t shift = 32 - (31 - __clz(tsize));
-    uint32_t f0 = 0, f1 = 0, f2 = 0;  // kWide: the bytes at position 0, what an empty slot points at
-    if (kWide && n >= 15) {
-        f0 = in.ld32(0);
-        f1 = in.ld32(4);
-        f2 = in.ld32(8);
-    }
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t op = 0, next_emit = 0, emitted = 0, cnt = 0;
     if (n >= 15) {  // kInputMarginBytes, snappy.cc:344-347
@@ -100,30 +79,17 @@ __device__ uint32_t compress_fragment_orbit(const In in, const uint32_t n, uint8
             if (!__shfl_sync(kFullMask, (int)vis_ok, 0)) break;  // the chain stops here: emit_remainder
             // ---- every lane's table step against the snapshot ----
             uint32_t h = 0, c0 = 0, m = 0;
-            uint32_t d0 = 0, d1 = 0, d2 = 0;  // kWide: the 12 bytes at pos (pos <= n - 16)
             if (vis_ok) {
-                if constexpr (kWide) {
-                    const uint64_t d8 = in.ld64(pos);
-                    d0 = (uint32_t)d8;
-                    d1 = (uint32_t)(d8 >> 32);
-                    d2 = in.ld32(pos + 8);
-                    h = hash_w(d0, shift);
-                    const uint4 e = TW[h];
-                    const bool live = (e.x >> 16) == epoch;
-                    c0 = live ? (e.x & 0xffffu) : 0u;
-                    m = prefix12(live ? e.y : f0, live ? e.z : f1, live ? e.w : f2, d0, d1, d2);
-                } else {
-                    const uint64_t d8 = in.ld64(pos);
-                    h = hash_w((uint32_t)d8, shift);
-                    c0 = T[h];
-                    m = prefix8(in.ld64(c0), d8);
-                    while (m >= 8 && m < kCap) {  // FindMatchLength, 8 bytes per trip (pos + 8 < n: pos <= n - 16)
-                        const uint32_t rem = n - (pos + m);
-                        if (rem == 0) break;
-                        const uint32_t nb = min(prefix8(in.ld64(c0 + m), in.ld64(pos + m)), rem);
-                        m += nb;
-                        if (nb < 8) break;
-                    }
+                const uint64_t d8 = in.ld64(pos);
+                h = hash_w((uint32_t)d8, shift);
+                c0 = T[h];
+                m = prefix8(in.ld64(c0), d8);
+                while (m >= 8 && m < kCap) {  // FindMatchLength, 8 bytes per trip (pos + 8 < n: pos <= n - 16)
+                    const uint32_t rem = n - (pos + m);
+                    if (rem == 0) break;
+                    const uint32_t nb = min(prefix8(in.ld64(c0 + m), in.ld64(pos + m)), rem);
+                    m += nb;
+                    if (nb < 8) break;
                 }
             }
             // ---- cut the window at the first repeated hash ----
@@ -198,30 +164,14 @@ __device__ uint32_t compress_fragment_orbit(const In in, const uint32_t n, uint8
             }
             const uint32_t endv = pos + m;
             // ---- inserts: visited positions (snappy.cc:394), then each copy's last byte (snappy.cc:430-433) ----
-            if (visited) {
-                if constexpr (kWide) TW[h] = make_uint4(pos | (epoch << 16), d0, d1, d2);
-                else T[h] = (uint16_t)pos;
-            }
+            if (visited) T[h] = (uint16_t)pos;
             __syncwarp();
             const bool vcopy = visited && hit;
             const bool tail = vcopy && endv < ip_limit;
-            uint32_t hq = 0, t0 = 0, t1 = 0, t2 = 0;
-            if (tail) {
-                if constexpr (kWide) {
-                    const uint64_t t8 = in.ld64(endv - 1);  // endv + 11 < n
-                    t0 = (uint32_t)t8;
-                    t1 = (uint32_t)(t8 >> 32);
-                    t2 = in.ld32(endv + 7);
-                } else {
-                    t0 = in.ld32(endv - 1);
-                }
-                hq = hash_w(t0, shift);
-            }
+            uint32_t hq = 0;
+            if (tail) hq = hash_w(in.ld32(endv - 1), shift);
             const uint32_t grp = __match_any_sync(kFullMask, tail ? hq : (0x80000000u | lane));
-            if (tail && lane == 31 - (uint32_t)__clz(grp)) {  // the later position wins
-                if constexpr (kWide) TW[hq] = make_uint4((endv - 1) | (epoch << 16), t0, t1, t2);
-                else T[hq] = (uint16_t)(endv - 1);
-            }
+            if (tail && lane == 31 - (uint32_t)__clz(grp)) T[hq] = (uint16_t)(endv - 1);  // the later position wins
             __syncwarp();
             // ---- queue the copies, in order ----
             const uint32_t cm = __ballot_sync(kFullMask, vcopy);
@@ -270,8 +220,6 @@ struct WindowParams {
     uint32_t table_entries;  // per-warp table capacity in shared memory (0: tables in `gtab`)
     uint32_t in_stride;      // per-warp staged-input bytes (0: read the fragment from HBM)
     uint16_t* gtab;          // 16384 entries per resident warp when table_entries == 0
-    uint4* gwide;            // kWide: 16384 16-byte entries per resident warp
-    uint32_t epoch_base;     // kWide: the k-th fragment of a warp in this launch has epoch epoch_base + 1 + k (< 65536)
     uint32_t* work_ctr;      // warps take the next listed fragment from here (null: every total-th one)
 };
 
@@ -279,10 +227,10 @@ __device__ __forceinline__ uint32_t smem_addr32(const void* p) { return (uint32_
 
 // Persistent warps, one fragment at a time.  Shared memory per warp: element queue, then the u16 table
 // (unless it lives in HBM/L2), then the staged fragment (if staged).
-template <bool kStage, bool kWide = false>
+template <bool kStage>
 // (256, 5): the HBM-table variant lives on resident warps (40 per SM = 48 registers per thread); the vector copies of
 // long literals must not cost it a fifth of them
-__global__ void __launch_bounds__(256, kWide ? 5 : 0) snappy_compress_orbit_kernel(WindowParams P) {
+__global__ void __launch_bounds__(256) snappy_compress_orbit_kernel(WindowParams P) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     __shared__ uint64_t bars[8];
     const uint32_t lane = threadIdx.x & 31;
@@ -302,15 +250,12 @@ __global__ void __launch_bounds__(256, kWide ? 5 : 0) snappy_compress_orbit_kern
     }
     __syncwarp();
     uint32_t parity = 0;
-    uint32_t epoch = P.epoch_base;
-    uint4* wide = kWide ? P.gwide + (size_t)gw * 16384 : nullptr;
     for (uint32_t w = gw;; w += total) {
         if (P.work_ctr) {  // fragments differ in length (the last one of a body): whoever is free takes the next
             if (lane == 0) w = atomicAdd(P.work_ctr, 1u);
             w = __shfl_sync(kFullMask, w, 0);
         }
         if (w >= P.n_list) break;
-        ++epoch;
         const uint32_t f = P.frag_list ? P.frag_list[w] : w;
         const uint32_t m = P.frag_msg ? P.frag_msg[f] : f;
         const uint32_t k = P.frag_first ? f - P.frag_first[m] : 0u;
@@ -318,7 +263,7 @@ __global__ void __launch_bounds__(256, kWide ? 5 : 0) snappy_compress_orbit_kern
         const uint8_t* gin = P.in + P.off[m] + (size_t)k * kFragBytes;
         uint32_t tsize = 256;  // GetHashTable sizing, snappy.cc:253-256
         while (tsize < 16384u && tsize < n) tsize <<= 1;
-        if (!kWide) {
+        {
             uint4* t4 = reinterpret_cast<uint4*>(table);
             for (uint32_t i = lane; i < tsize / 8; i += 32) t4[i] = make_uint4(0, 0, 0, 0);
         }
@@ -359,10 +304,10 @@ __global__ void __launch_bounds__(256, kWide ? 5 : 0) snappy_compress_orbit_kern
                 : "memory");
             parity ^= 1;
             __syncwarp();
-            clen = compress_fragment_orbit<false>(InShared{stage}, n, out, table, tsize, queue, lane);
+            clen = compress_fragment_orbit(InShared{stage}, n, out, table, tsize, queue, lane);
         } else {
             __syncwarp();
-            clen = compress_fragment_orbit<kWide>(InGlobal{gin}, n, out, table, tsize, queue, lane, wide, epoch);
+            clen = compress_fragment_orbit(InGlobal{gin}, n, out, table, tsize, queue, lane);
         }
         if (lane == 0) P.frag_clen[f] = clen;
         __syncwarp();
@@ -374,8 +319,6 @@ int window_kernels_configure(b2c_ctx* ctx) {
                                        100 * 1024));
     B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_compress_orbit_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        64 * 1024));
-    B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_compress_orbit_kernel<false, true>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
     return B2C_OK;
 }
 
@@ -420,39 +363,17 @@ int launch_compress_window(b2c_ctx* ctx, Lane& lane, const LayoutView& L, int c,
     const size_t per_warp = kQueue * sizeof(uint2) + (size_t)P.table_entries * 2 + P.in_stride;
     const uint32_t want_blocks = (uint32_t)ctx->num_sms * resident;
     const uint32_t blocks = std::min<uint32_t>(want_blocks, (P.n_list + wpb - 1) / wpb);
-    P.gwide = nullptr;
-    P.epoch_base = 0;
-    const bool wide = P.table_entries == 0 && ctx->window_wide;
-    if (wide) {
-        // 256 KiB of 16-byte entries per resident warp, never zero-filled: the epoch in every entry tells whose it is.
-        // The buffer is this lane's alone (nothing else may write into it), zeroed when it is allocated and when the
-        // 16-bit epochs run out.
-        const size_t need = (size_t)blocks * wpb * 16384 * sizeof(uint4);
-        const uint32_t per_warp_frags = (P.n_list + blocks * wpb - 1) / (blocks * wpb);
-        int rc;
-        const bool fresh = need > lane.ws_wide.cap;
-        if ((rc = ws_reserve(ctx, lane, lane.ws_wide, need))) return rc;
-        if (fresh || lane.wide_epoch + per_warp_frags > 65000u) {
-            B2C_CUDA(ctx, cudaMemsetAsync(lane.ws_wide.p, 0, lane.ws_wide.cap, lane.stream));
-            lane.wide_epoch = 0;
-        }
-        P.gwide = static_cast<uint4*>(lane.ws_wide.p);
-        P.epoch_base = lane.wide_epoch;
-        lane.wide_epoch += per_warp_frags;
-    } else if (P.table_entries == 0) {
+    if (P.table_entries == 0) {
         int rc;
         if ((rc = ws_reserve(ctx, lane, lane.ws_tab, (size_t)blocks * wpb * 32768))) return rc;
         P.gtab = static_cast<uint16_t*>(lane.ws_tab.p);
     }
-    P.work_ctr = nullptr;
-    if (!wide) {  // (the wide tables count their epochs per warp: fixed shares)
+    {
         int rc = next_work_counter(ctx, lane, &P.work_ctr);
         if (rc) return rc;
     }
     const size_t smem = (size_t)wpb * per_warp;
-    if (wide)
-        snappy_compress_orbit_kernel<false, true><<<blocks, wpb * 32, smem, lane.stream>>>(P);
-    else if (P.in_stride)
+    if (P.in_stride)
         snappy_compress_orbit_kernel<true><<<blocks, wpb * 32, smem, lane.stream>>>(P);
     else
         snappy_compress_orbit_kernel<false><<<blocks, wpb * 32, smem, lane.stream>>>(P);

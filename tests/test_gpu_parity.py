@@ -687,7 +687,6 @@ def test_e2e_zero_copy_refuses_pageable_blocks(codec):
     {"B2C_WINDOW": "7"},                                   # orbit compressor on every fragment class
     {"B2C_WINDOW": "7", "B2C_WINDOW_STAGE": "0", "B2C_GTAB_WPS": "0"},
     {"B2C_WINDOW_SMEM64": "1"},                            # 64 KiB fragments: table + staged fragment in shared memory
-    {"B2C_WINDOW_WIDE": "1"},                              # 64 KiB fragments: 16-byte table entries with the candidate's bytes
     {"B2C_LOCKSTEP": "1", "B2C_LOCKSTEP_GLOBAL": "4"},     # lock-step compressor with its state in global memory
     {"B2C_SMALL_LPW_C": "2"},                              # two bodies per warp
     {"B2C_SMALL_KERNELS": "0"},                            # warp kernels for small bodies too
