@@ -533,7 +533,7 @@ using namespace b2c;
 // ---------------------------------------------------------------------------
 static const char* const kTunableNames[] = {
     "slab_mb", "host_threads", "trace", "batch_decode", "ring_decode", "block_decode", "lift_scan", "batch_decode_small",
-    "nt_gather", "gtab_wps", "small_kernels", "small_lpw_c", "small_lpw_d", "window", "window_stage", "window_smem64", "window_pipe",
+    "nt_gather", "gtab_wps", "small_kernels", "small_lpw_c", "small_lpw_d", "window", "window_stage", "window_smem64",
     "window_wps", "gather_ctas", "gather_warps", "gather_chunk", "lockstep", "lockstep_global", "lockstep_lpw", "lockstep_d",
     "lockstep_d_ctas", "async_gather"};
 
@@ -558,7 +558,6 @@ static int apply_tunable(b2c_ctx* ctx, const char* name, long v) {
     else if (n == "window") ctx->window_mask = (int)v;
     else if (n == "window_stage") ctx->window_stage = v != 0;
     else if (n == "window_smem64") ctx->window_smem64 = v != 0;
-    else if (n == "window_pipe") ctx->window_pipe = v != 0;
     else if (n == "window_wps") ctx->window_warps_per_sm = (int)v;
     else if (n == "gather_ctas") ctx->gather_ctas_per_sm = (int)std::max(1L, v);
     else if (n == "gather_warps") ctx->gather_warps = (int)std::min(32L, std::max(1L, v));

@@ -152,7 +152,6 @@ struct b2c_ctx {
     bool async_gather = true;  // B2C_ASYNC_GATHER=0: the submitting thread waits for each slab's gather before anything else
     int window_warps_per_sm = 40;  // B2C_WINDOW_WPS: resident warps per SM of the orbit kernel on 64 KiB fragments (tables in HBM/L2; B2C_GTAB_WPS=0 keeps them in shared memory)
     bool window_stage = true;  // B2C_WINDOW_STAGE=0: the window compressor reads <=4 KiB fragments from HBM instead of staging them
-    bool window_pipe = true;     // B2C_WINDOW_PIPE=0: 64 KiB fragments probe their table in the round that needs it (snappy_window.cu)
     bool window_smem64 = false;  // B2C_WINDOW_SMEM64=1: 64 KiB fragments keep table + TMA-staged fragment in shared memory (one warp per CTA, 2 CTAs per SM); measured 7.6x slower than HBM/L2 tables with 40 warps per SM
     bool small_lockstep = false;  // B2C_LOCKSTEP=1: bodies <= 1 KiB compress with the branch-free lock-step state machines of snappy_lockstep.cu (measured slower than the lane-per-body loops of snappy_small.cu: 15.5 vs 11.0 ms per GiB of 1 KiB `words` bodies)
     int lockstep_global = 0;     // tunable lockstep_global: > 0 = the lock-step compressor keeps tables and staged bodies in global memory (L2), that many 64-body CTAs resident per SM

@@ -44,61 +44,18 @@ __device__ __forceinline__ uint32_t flush_queue(const In& in, const uint2* queue
 
 // CompressFragment by one warp.  `T` = `tsize` zeroed u16 slots (shared or global memory); `queue` = kQueue
 // uint2 of shared memory private to the warp.
-//
-// kPipe (tables in HBM): the table probes are taken ONE ROUND AHEAD.  While the chain advances byte by byte the warp
-// keeps, in two registers pairs per lane, the probe (hash, slot content) of the 64 positions from ip on: window A =
-// [ip, ip + 32), look-ahead S = [ip + 32, ip + 64).  At the end of a round both are rotated by the chain's advance and
-// the positions that entered are probed; those loads are first needed a round later, so the round no longer waits for
-// the table (HBM latency), only for the candidates' bytes.  A probe is the slot's content when it was taken; every
-// insert since is FORWARDED into it (an insert with the same hash replaces the content, exactly as it did in the
-// table), so an entry is always what a fresh probe would return.  The forwarding goes through `fwd`, 1024 words of
-// shared memory per warp keyed by the hash's low bits: inserting lanes leave (hash, position) there, every lane looks
-// its two hashes up; two different hashes of one round in one slot (rare) fall back to a broadcast loop.
-// tools/orbit_pipe_model.py is the model (byte-identical to the oracle; 3 of 2,524 rounds of a `words` fragment still
-// wait for a probe).
-static constexpr uint32_t kFwdSlots = 1024;
-
-// The probes taken ahead travel by cp.async (LDGSTS) into a word of shared memory per lane: ptxas makes a loop wait
-// for every register load still under way at its back-edge, so a probe kept in a register would be waited for in the
-// round that issued it; an asynchronous copy is only waited for where cp.async.wait_all stands, one round later.
-__device__ __forceinline__ void probe_async(uint32_t* slot, const uint16_t* T, uint32_t h) {
-    const uint32_t sa = (uint32_t)__cvta_generic_to_shared(slot);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(T + (h & ~1u)) : "memory");
-}
-__device__ __forceinline__ void probes_landed() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-
-template <bool kPipe, class In>
+template <class In>
 __device__ uint32_t compress_fragment_orbit(const In in, const uint32_t n, uint8_t* __restrict__ out, uint16_t* T,
-                                            const uint32_t tsize, uint2* queue, const uint32_t lane,
-                                            uint32_t* fwd = nullptr) {
+                                            const uint32_t tsize, uint2* queue, const uint32_t lane) {
     const uint32_t shift = 32 - (31 - __clz(tsize));
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t op = 0, next_emit = 0, emitted = 0, cnt = 0;
-    // kPipe: probes of positions ip + lane (A) and ip + 32 + lane (S); bit j of VA / VS: lane j's is there
-    uint32_t hA = 0, cA = 0, hS = 0, cS = 0, VA = 0, VS = 0;
-    uint32_t FA = 0;  // lanes of A probed at the end of the last round: there, but not to be waited for
-    uint32_t QA = 0, QS = 0;  // lanes whose probe is still on its way to slotA / slotS
-    uint32_t* slotA = fwd + kFwdSlots + lane;
-    uint32_t* slotS = slotA + 32;
-    auto land = [&]() {  // bring the probes that were under way into cA / cS
-        if (QA | QS) {
-            probes_landed();
-            if ((QA >> lane) & 1u) cA = (*slotA >> ((hA & 1u) * 16)) & 0xffffu;
-            if ((QS >> lane) & 1u) cS = (*slotS >> ((hS & 1u) * 16)) & 0xffffu;
-            QA = QS = 0;
-        }
-    };
-    if (kPipe) {
-        for (uint32_t i = lane; i < kFwdSlots; i += 32) fwd[i] = 0;  // (hash 0, position 0) = what an untouched slot holds
-        __syncwarp();
-    }
     if (n >= 15) {  // kInputMarginBytes, snappy.cc:344-347
         const uint32_t ip_limit = n - 15;
         // `s` is the reference's `skip` with one extra state: 31 right after a copy (the copy loop's own table
         // step, snappy.cc:430-439, advances one byte on a miss and is followed by a fresh skip = 32 sequence).
         uint32_t ip = 1, s = 32;
         for (;;) {
-            const uint32_t ip0 = ip;
             // ---- the window: positions, and whether the chain may stand on them (snappy.cc:386-388) ----
             const uint32_t k1 = s <= 32 ? 32u : (s < 64 ? 64u - s : 0u);  // leading probes that advance one byte
             const bool consecutive = k1 >= 16;
@@ -118,38 +75,14 @@ __device__ uint32_t compress_fragment_orbit(const In in, const uint32_t n, uint8
                 }
                 pos = ip + incl - step;
             }
-            bool have = false;  // kPipe: this round's probes are in hA / cA already
-            if (kPipe) {
-                if (!consecutive) {
-                    if (QA | QS) probes_landed();
-                    VA = VS = FA = QA = QS = 0;
-                } else if (VA & 1u) {
-                    if (QA & 1u) land();  // the first position's probe is the one under way: nothing to do but wait
-                    // no waiting: the window ends at the first position whose probe is missing or only just under way
-                    // (unless the first one's is: then it and its neighbours are waited for)
-                    const uint32_t inr = __ballot_sync(kFullMask, pos + 1 <= ip_limit);
-                    const uint32_t miss = inr & ((FA & 1u) ? ~VA : (~VA | FA));
-                    if (miss) W = min(W, (uint32_t)__ffs(miss) - 1);
-                    have = true;
-                }
-            }
             const bool vis_ok = lane < W && pos + step <= ip_limit;
             if (!__shfl_sync(kFullMask, (int)vis_ok, 0)) break;  // the chain stops here: emit_remainder
             // ---- every lane's table step against the snapshot ----
             uint32_t h = 0, c0 = 0, m = 0;
             if (vis_ok) {
                 const uint64_t d8 = in.ld64(pos);
-                if (kPipe && have) {
-                    h = hA;
-                    c0 = cA;
-                } else {
-                    h = hash_w((uint32_t)d8, shift);
-                    c0 = T[h];
-                    if (kPipe) {
-                        hA = h;
-                        cA = c0;
-                    }
-                }
+                h = hash_w((uint32_t)d8, shift);
+                c0 = T[h];
                 m = prefix8(in.ld64(c0), d8);
                 while (m >= 8 && m < kCap) {  // FindMatchLength, 8 bytes per trip (pos + 8 < n: pos <= n - 16)
                     const uint32_t rem = n - (pos + m);
@@ -158,11 +91,6 @@ __device__ uint32_t compress_fragment_orbit(const In in, const uint32_t n, uint8
                     m += nb;
                     if (nb < 8) break;
                 }
-            }
-            if (kPipe && consecutive && !have) {
-                const uint32_t vm = __ballot_sync(kFullMask, vis_ok);
-                VA |= vm;
-                QA &= ~vm;  // probed afresh: whatever is under way for these lanes is void
             }
             // ---- cut the window at the first repeated hash ----
             const uint32_t same = __match_any_sync(kFullMask, vis_ok ? h : (0x80000000u | lane));
@@ -243,41 +171,8 @@ __device__ uint32_t compress_fragment_orbit(const In in, const uint32_t n, uint8
             uint32_t hq = 0;
             if (tail) hq = hash_w(in.ld32(endv - 1), shift);
             const uint32_t grp = __match_any_sync(kFullMask, tail ? hq : (0x80000000u | lane));
-            const bool tw = tail && lane == 31 - (uint32_t)__clz(grp);  // the later position wins
-            if (tw) T[hq] = (uint16_t)(endv - 1);
+            if (tail && lane == 31 - (uint32_t)__clz(grp)) T[hq] = (uint16_t)(endv - 1);  // the later position wins
             __syncwarp();
-            constexpr uint32_t kFm = kFwdSlots - 1;
-            if (kPipe) {  // every insert goes into `fwd` too, whatever the round: a tag there must be that hash's LATEST insert
-                if (visited) fwd[h & kFm] = (h << 16) | pos;
-                __syncwarp();
-                if (tw) fwd[hq & kFm] = (hq << 16) | (endv - 1);
-                __syncwarp();
-            }
-            if (kPipe && consecutive) {
-                land();  // (issued a round ago)
-                // ---- forward this round's inserts into the probes held in registers (table order: visited, then tails) ----
-                const bool lost = (visited && (fwd[h & kFm] >> 16) != h) || (tw && (fwd[hq & kFm] >> 16) != hq);
-                if (!__any_sync(kFullMask, lost)) {
-                    // a slot whose tag is a lane's hash holds the LATEST insert of that hash: what the table holds
-                    const uint32_t eA = fwd[hA & kFm], eS = fwd[hS & kFm];
-                    if ((eA >> 16) == hA) cA = eA & 0xffffu;
-                    if ((eS >> 16) == hS) cS = eS & 0xffffu;
-                } else {  // two hashes of this round share a slot: one insert at a time
-                    for (uint32_t mk = V; mk; mk &= mk - 1) {
-                        const uint32_t l = __ffs(mk) - 1;
-                        const uint32_t hv = __shfl_sync(kFullMask, h, l), pv = __shfl_sync(kFullMask, pos, l);
-                        if (hA == hv) cA = pv;
-                        if (hS == hv) cS = pv;
-                    }
-                    for (uint32_t mk = __ballot_sync(kFullMask, tw); mk; mk &= mk - 1) {
-                        const uint32_t l = __ffs(mk) - 1;
-                        const uint32_t hv = __shfl_sync(kFullMask, hq, l), pv = __shfl_sync(kFullMask, endv - 1, l);
-                        if (hA == hv) cA = pv;
-                        if (hS == hv) cS = pv;
-                    }
-                }
-                __syncwarp();
-            }
             // ---- queue the copies, in order ----
             const uint32_t cm = __ballot_sync(kFullMask, vcopy);
             if (vcopy) queue[cnt + __popc(cm & lt)] = make_uint2(pos | ((pos - c0) << 16), m);
@@ -303,49 +198,8 @@ __device__ uint32_t compress_fragment_orbit(const In in, const uint32_t n, uint8
                 ip = __shfl_sync(kFullMask, pos + step, last);
                 if (__shfl_sync(kFullMask, (int)stop, last)) break;
             }
-            if (kPipe) {
-                const uint32_t k1n = s <= 32 ? 32u : (s < 64 ? 64u - s : 0u);
-                if (k1n >= 16) {  // the next round goes byte by byte: have its window and look-ahead probed
-                    if (consecutive) {  // slide both by the chain's advance
-                        const uint32_t adv = ip - ip0, src = lane + adv;
-                        const uint32_t a_h = __shfl_sync(kFullMask, hA, src & 31), a_c = __shfl_sync(kFullMask, cA, src & 31);
-                        const uint32_t s_h = __shfl_sync(kFullMask, hS, src & 31), s_c = __shfl_sync(kFullMask, cS, src & 31);
-                        const uint64_t vall = adv < 64 ? (((uint64_t)VS << 32) | VA) >> adv : 0ull;
-                        VA = (uint32_t)vall;
-                        VS = (uint32_t)(vall >> 32);
-                        hA = src < 32 ? a_h : s_h;
-                        cA = src < 32 ? a_c : s_c;
-                        hS = s_h;
-                        cS = s_c;
-                    } else {
-                        VA = VS = 0;
-                    }
-                    const uint32_t pA = ip + lane, pS = ip + 32 + lane;
-                    const bool inA = pA + 1 <= ip_limit, inS = pS + 1 <= ip_limit;
-                    FA = __ballot_sync(kFullMask, inA) & ~VA;
-                    if (FA) {  // (only after an advance of more than 32)
-                        if ((FA >> lane) & 1u) {
-                            hA = hash_w(in.ld32(pA), shift);
-                            probe_async(slotA, T, hA);
-                        }
-                        QA = FA;
-                    }
-                    const bool ps = inS && !((VS >> lane) & 1u);
-                    if (ps) {
-                        hS = hash_w(in.ld32(pS), shift);
-                        probe_async(slotS, T, hS);
-                    }
-                    QS = __ballot_sync(kFullMask, ps);
-                    VA = __ballot_sync(kFullMask, inA);
-                    VS = __ballot_sync(kFullMask, inS);
-                } else {
-                    if (QA | QS) probes_landed();
-                    VA = VS = FA = QA = QS = 0;
-                }
-            }
         }
     }
-    if (kPipe && (QA | QS)) probes_landed();  // nothing may still be writing into this warp's slots
     if (cnt) op = flush_queue(in, queue, cnt, emitted, out, op, lane);
     return emit_remainder_warp(in, next_emit, n, out, op, lane);  // snappy.cc:446-450
 }
@@ -367,14 +221,13 @@ struct WindowParams {
     uint32_t in_stride;      // per-warp staged-input bytes (0: read the fragment from HBM)
     uint16_t* gtab;          // 16384 entries per resident warp when table_entries == 0
     uint32_t* work_ctr;      // warps take the next listed fragment from here (null: every total-th one)
-    uint32_t fwd_bytes;      // kPipe: bytes of forwarding table per warp in shared memory (else 0)
 };
 
 __device__ __forceinline__ uint32_t smem_addr32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // Persistent warps, one fragment at a time.  Shared memory per warp: element queue, then the u16 table
 // (unless it lives in HBM/L2), then the staged fragment (if staged).
-template <bool kStage, bool kPipe = false>
+template <bool kStage>
 // (256, 5): the HBM-table variant lives on resident warps (40 per SM = 48 registers per thread); the vector copies of
 // long literals must not cost it a fifth of them
 __global__ void __launch_bounds__(256) snappy_compress_orbit_kernel(WindowParams P) {
@@ -384,13 +237,11 @@ __global__ void __launch_bounds__(256) snappy_compress_orbit_kernel(WindowParams
     const uint32_t wib = threadIdx.x >> 5;
     const uint32_t gw = blockIdx.x * (blockDim.x >> 5) + wib;
     const uint32_t total = gridDim.x * (blockDim.x >> 5);
-    const size_t per_warp = kQueue * sizeof(uint2) + P.fwd_bytes + (size_t)P.table_entries * 2 + P.in_stride;
+    const size_t per_warp = kQueue * sizeof(uint2) + (size_t)P.table_entries * 2 + P.in_stride;
     uint8_t* my = smem_raw + (size_t)wib * per_warp;
     uint2* queue = reinterpret_cast<uint2*>(my);
-    uint32_t* fwd = reinterpret_cast<uint32_t*>(my + kQueue * sizeof(uint2));
-    uint8_t* after = my + kQueue * sizeof(uint2) + P.fwd_bytes;
-    uint16_t* table = P.table_entries ? reinterpret_cast<uint16_t*>(after) : P.gtab + (size_t)gw * 16384;
-    uint8_t* stage = after + (size_t)P.table_entries * 2;
+    uint16_t* table = P.table_entries ? reinterpret_cast<uint16_t*>(my + kQueue * sizeof(uint2)) : P.gtab + (size_t)gw * 16384;
+    uint8_t* stage = my + kQueue * sizeof(uint2) + (size_t)P.table_entries * 2;
     uint64_t* bar = &bars[wib];
     if (kStage && lane == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr32(bar)), "r"(1) : "memory");
@@ -453,10 +304,10 @@ __global__ void __launch_bounds__(256) snappy_compress_orbit_kernel(WindowParams
                 : "memory");
             parity ^= 1;
             __syncwarp();
-            clen = compress_fragment_orbit<false>(InShared{stage}, n, out, table, tsize, queue, lane);
+            clen = compress_fragment_orbit(InShared{stage}, n, out, table, tsize, queue, lane);
         } else {
             __syncwarp();
-            clen = compress_fragment_orbit<kPipe>(InGlobal{gin}, n, out, table, tsize, queue, lane, fwd);
+            clen = compress_fragment_orbit(InGlobal{gin}, n, out, table, tsize, queue, lane);
         }
         if (lane == 0) P.frag_clen[f] = clen;
         __syncwarp();
@@ -468,8 +319,6 @@ int window_kernels_configure(b2c_ctx* ctx) {
                                        100 * 1024));
     B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_compress_orbit_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        64 * 1024));
-    B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_compress_orbit_kernel<false, true>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
     return B2C_OK;
 }
 
@@ -508,12 +357,10 @@ int launch_compress_window(b2c_ctx* ctx, Lane& lane, const LayoutView& L, int c,
         resident = std::max(1, ctx->window_warps_per_sm / 8);
         P.table_entries = 0;
     } else {
-        const size_t pw = kQueue * sizeof(uint2) + (size_t)P.table_entries * 2 + P.in_stride;  // (fwd_bytes = 0 here)
+        const size_t pw = kQueue * sizeof(uint2) + (size_t)P.table_entries * 2 + P.in_stride;
         resident = std::max<uint32_t>(1, (uint32_t)((220u << 10) / (pw * wpb + 1024)));
     }
-    const bool pipe = P.table_entries == 0 && ctx->window_pipe;
-    P.fwd_bytes = pipe ? (kFwdSlots + 64) * sizeof(uint32_t) : 0u;  // forwarding table + a probe slot per lane for A and S
-    const size_t per_warp = kQueue * sizeof(uint2) + P.fwd_bytes + (size_t)P.table_entries * 2 + P.in_stride;
+    const size_t per_warp = kQueue * sizeof(uint2) + (size_t)P.table_entries * 2 + P.in_stride;
     const uint32_t want_blocks = (uint32_t)ctx->num_sms * resident;
     const uint32_t blocks = std::min<uint32_t>(want_blocks, (P.n_list + wpb - 1) / wpb);
     if (P.table_entries == 0) {
@@ -526,9 +373,7 @@ int launch_compress_window(b2c_ctx* ctx, Lane& lane, const LayoutView& L, int c,
         if (rc) return rc;
     }
     const size_t smem = (size_t)wpb * per_warp;
-    if (pipe)
-        snappy_compress_orbit_kernel<false, true><<<blocks, wpb * 32, smem, lane.stream>>>(P);
-    else if (P.in_stride)
+    if (P.in_stride)
         snappy_compress_orbit_kernel<true><<<blocks, wpb * 32, smem, lane.stream>>>(P);
     else
         snappy_compress_orbit_kernel<false><<<blocks, wpb * 32, smem, lane.stream>>>(P);
