@@ -41,6 +41,8 @@ struct AggregatorOptions {
     uint32_t max_batch = 8192;   // messages per GPU call
     uint32_t max_wait_us = 100;  // how long the first message of a batch may wait for company
     bool pooled_output = true;   // results as slices of a page-locked slab (false: heap buffers, one copy)
+    uint32_t workers = 2;        // batches in flight: each worker thread has its own codec context (own streams and
+                                 // staging), so the next batch forms and starts while the last one is on the GPU
 };
 
 struct StdSync {  // how a CALLER waits for its result
@@ -87,14 +89,16 @@ public:
         uint64_t calls = 0, batches = 0, largest_batch = 0, failed_batches = 0;
     };
 
-    explicit BasicBatchAggregator(const Options& opt = Options()) : opt_(opt), thread_([this] { worker(); }) {}
+    explicit BasicBatchAggregator(const Options& opt = Options()) : opt_(opt) {
+        for (uint32_t i = 0; i < (opt_.workers ? opt_.workers : 1u); i++) threads_.emplace_back([this] { worker(); });
+    }
     ~BasicBatchAggregator() {
         {
             std::lock_guard<std::mutex> g(mu_);
             stop_ = true;
         }
         queue_cv_.notify_all();
-        thread_.join();
+        for (std::thread& t : threads_) t.join();
     }
     BasicBatchAggregator(const BasicBatchAggregator&) = delete;
     BasicBatchAggregator& operator=(const BasicBatchAggregator&) = delete;
@@ -278,6 +282,7 @@ private:
                     batch.push_back(queue_.front());
                     queue_.pop_front();
                 }
+                if (batch.empty()) continue;  // another worker took them all
                 stats_.batches++;
                 if (batch.size() > stats_.largest_batch) stats_.largest_batch = batch.size();
             }
@@ -326,7 +331,7 @@ private:
     std::deque<Request*> queue_;
     bool stop_ = false;
     Stats stats_;
-    std::thread thread_;  // last member: started when everything above exists
+    std::vector<std::thread> threads_;  // last member: started when everything above exists
 };
 
 using BatchAggregator = BasicBatchAggregator<StdSync>;
