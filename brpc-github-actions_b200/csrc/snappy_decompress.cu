@@ -470,7 +470,13 @@ __device__ int decode_message_batched(const uint8_t* __restrict__ in, const uint
                             d[2] = b2;
                             d[3] = b3;
                         }
-                        for (; d < de; d++, sp++) *d = *sp;
+                        const uint32_t r = (uint32_t)(de - d);  // 0-3 bytes left: loaded together, one round trip
+                        if (r) {
+                            const uint8_t b0 = sp[0], b1 = r > 1 ? sp[1] : (uint8_t)0, b2 = r > 2 ? sp[2] : (uint8_t)0;
+                            d[0] = b0;
+                            if (r > 1) d[1] = b1;
+                            if (r > 2) d[2] = b2;
+                        }
                     } else {  // offset 1-3: every byte repeats the one `offset` back, also across the pattern's end
                         for (; d < de; d++, sp++) *d = *sp;
                     }

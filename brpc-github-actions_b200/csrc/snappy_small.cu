@@ -359,12 +359,12 @@ __global__ void __launch_bounds__(1024 / LPW, 6) snappy_decompress_small_kernel(
             // made them take turns (a literal path run for 1.9 of 8 lanes on `words`).
             const uint8_t* obg = ob;  // generic pointer to the slot, for the common source pointer
             asm volatile("" : "+l"(obg));  // converted once, kept
+            uint32_t x = ip < n ? ld32u(in + ip) : 0u;  // tag byte + up to 3 trailer bytes
             for (;;) {
                 if (ip == n) {  // clean eof: snappy.cc:867
                     if (op != expected) st = B2C_CORRUPT;
                     break;
                 }
-                const uint32_t x = ld32u(in + ip);  // tag byte + up to 3 trailer bytes
                 const uint32_t c = x & 0xff;
                 const uint32_t kind = c & 3;
                 const bool is_lit = kind == 0;
@@ -397,6 +397,9 @@ __global__ void __launch_bounds__(1024 / LPW, 6) snappy_decompress_small_kernel(
                 if (bad || expected - op < len) { st = B2C_CORRUPT; break; }
                 const uint8_t* sp = is_lit ? in + ip : obg + op - offset;  // may overlap d: no restrict
                 uint8_t* d = ob + op;
+                // the next tag's bytes are asked for now: they arrive while this element's bytes are moved
+                const uint32_t nip = is_lit ? ip + len : ip;
+                const uint32_t xn = nip < n ? ld32u(in + nip) : 0u;
                 uint32_t i = 0;
                 if (is_lit || offset >= 4) {  // the 4 source bytes of a round precede its first destination byte
                     for (; i + 4 <= len; i += 4) {
@@ -406,10 +409,19 @@ __global__ void __launch_bounds__(1024 / LPW, 6) snappy_decompress_small_kernel(
                         d[i + 2] = b2;
                         d[i + 3] = b3;
                     }
+                    const uint32_t r = len - i;  // 0-3 bytes left: loaded together, one wait instead of one per byte
+                    if (r) {
+                        const uint8_t b0 = sp[i], b1 = r > 1 ? sp[i + 1] : (uint8_t)0, b2 = r > 2 ? sp[i + 2] : (uint8_t)0;
+                        d[i] = b0;
+                        if (r > 1) d[i + 1] = b1;
+                        if (r > 2) d[i + 2] = b2;
+                    }
+                } else {
+                    for (; i < len; i++) d[i] = sp[i];  // IncrementalCopy, snappy.cc:98-103
                 }
-                for (; i < len; i++) d[i] = sp[i];  // IncrementalCopy, snappy.cc:98-103
                 op += len;
-                if (is_lit) ip += len;
+                ip = nip;
+                x = xn;
             }
         }
         P.status[m] = st;
