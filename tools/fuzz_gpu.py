@@ -116,6 +116,29 @@ def main():
         for b in (d_in, d_crc):
             b.free()
         del lay
+        # ---- the host-buffer calls (block lists of random block size through the slab pipeline), every third round
+        if rounds % 3 == 0 and len(lens):
+            seg_bytes = int(rng.choice([64, 700, 4096, 8160, 65536, 1 << 20]))
+            segs, sb = brpc_b200.make_iovecs(arena, off, lens, seg_bytes=seg_bytes)
+            hout = np.empty(int(sum(32 + int(l) + int(l) // 6 + 5 for l in lens)), dtype=np.uint8)
+            h_off, h_crc = codec.compress_crc_batch(segs, sb, hout, masked=True)
+            assert np.array_equal(h_off, c_off), f"round {rounds}: host-call offsets differ"
+            assert np.array_equal(hout[:int(c_off[-1])], packed[:int(c_off[-1])]), f"round {rounds}: host-call bytes differ"
+            masked = ((want_crc >> np.uint32(15)) | (want_crc << np.uint32(17))) + np.uint32(0xa282ead8)
+            assert np.array_equal(h_crc, masked), f"round {rounds}: host-call checksums differ"
+            zsegs, zsb = brpc_b200.make_iovecs(hout, c_off[:-1].astype(np.uint64), np.diff(c_off).astype(np.uint32),
+                                               seg_bytes=int(rng.choice([100, 8160, 1 << 20])))
+            wrong = masked.copy()
+            flip = int(rng.integers(0, len(lens)))
+            wrong[flip] ^= np.uint32(1)
+            back = np.empty(int(lens.astype(np.uint64).sum()) + 64, dtype=np.uint8)
+            b_off, b_st = codec.decompress_verify_batch(zsegs, zsb, wrong, back)
+            for i in range(len(lens)):
+                if i == flip:
+                    assert b_st[i] != 0, f"round {rounds}: a wrong checksum went unnoticed"
+                    continue
+                assert b_st[i] == 0, f"round {rounds}: host-call receiver status {b_st[i]} for message {i}"
+                assert back[int(b_off[i]):int(b_off[i + 1])].tobytes() == bodies[i], f"round {rounds}: host-call body {i}"
         rounds += 1
         msgs += len(lens)
         total += int(lens.sum())
