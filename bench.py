@@ -657,7 +657,12 @@ def run_ours(args, rank, local_rank, world):
                                  "HBM bound (see DESIGN.md)"},
             "ops": head["ops"], "compression_ratio": head["compression_ratio"],
             "messages_per_s": n_msgs * world * args.steps / (head["ms_per_step"] * args.steps * 1e-3),
-            "parity": head["parity"], "cpu_baseline": head["cpu_baseline"],
+            "parity": head["parity"],
+            # the CPU figure is the parity checker's own time; with several ranks all of them run their checkers on the
+            # same cores at once, so only the 1-GPU line carries it as a baseline (`--impl reference` times it alone)
+            "cpu_baseline": head["cpu_baseline"] if world == 1 else
+            {**head["cpu_baseline"], "contended": True,
+             "note": f"{world} ranks ran their checkers at once on these cores: not a baseline; see the 1-GPU line or --impl reference"},
             **({"decompress_verify": head["decompress_verify"]} if "decompress_verify" in head else {}),
             "workloads": workloads,
         }
