@@ -409,9 +409,27 @@ __device__ int decode_message_batched(const uint8_t* __restrict__ in, const uint
         uint32_t pending = __ballot_sync(kFull, is_copy);
         const uint32_t src_pos = out_pos - offset;                         // meaningful for copies
         const uint32_t src_end = offset >= len ? src_pos + len : out_pos;  // bytes read lie in [src_pos, src_end)
+        // Which copies of this batch does a copy read from?  Outputs are contiguous in tag order, so the tags whose
+        // output overlaps [src_pos, src_end) form a range [a, b] of lanes, found by two binary searches over the lanes'
+        // output positions.  A copy may run as soon as no copy of its range is still to run: the rounds below are then
+        // as many as the longest chain of copies reading copies (2-3 on text, where a source lies ~15 tags back),
+        // not one per copy that happens to precede a source.
+        uint32_t deps = 0;
+        {
+            const uint32_t out_end = out_pos + len;
+            uint32_t na = 0, nb = 0;  // tags that end at or before src_pos; tags that begin at or before src_end - 1
+#pragma unroll
+            for (uint32_t stp = 16; stp; stp >>= 1) {
+                const uint32_t ca = na + stp, cb = nb + stp;
+                const uint32_t ea = __shfl_sync(kFull, out_end, (ca - 1) & 31), pb = __shfl_sync(kFull, out_pos, (cb - 1) & 31);
+                if (ca <= count && ea <= src_pos) na = ca;
+                if (cb <= count && pb < src_end) nb = cb;
+            }
+            if (is_copy && nb > na) deps = (nb >= 32 ? 0xffffffffu : (1u << nb) - 1u) & ~((1u << na) - 1u);
+            deps &= pending & ((1u << lane) - 1u);
+        }
         // The first copy that has not run yet goes alone, 32 bytes per instruction, when it is long (runs, repeated
-        // records); otherwise it and every short copy whose source lies entirely below its output position run
-        // together, one lane per tag (their sources are final: everything before the first pending copy is written).
+        // records); otherwise every short copy none of whose sources is still to be written runs, one lane per tag.
         while (pending) {
             const uint32_t first = __ffs(pending) - 1;
             const uint32_t ln = __shfl_sync(kFull, len, first);
@@ -455,7 +473,7 @@ __device__ int decode_message_batched(const uint8_t* __restrict__ in, const uint
                 __syncwarp();
                 continue;
             }
-            const bool ready = ((pending >> lane) & 1u) && len <= 16 && (lane == first || src_end <= frontier);
+            const bool ready = ((pending >> lane) & 1u) && len <= 16 && (deps & pending) == 0;
             if (ready) {
                 if constexpr (Out::kLinear) {
                     // the same three cases as below on raw pointers: one 64-bit address per copy instead of one per byte
