@@ -1072,6 +1072,11 @@ __global__ void __launch_bounds__(256, 5) snappy_decompress_blocks_kernel(Decomp
 }
 
 
+// One instantiation per way of decoding, so that each carries only its own decoder's registers (they are all at the
+// 48-register limit of 5 CTAs per SM): kSmemSlot: slots that fit a per-warp shared-memory buffer, batched; kGlobal: batched,
+// straight into HBM; kRing: batched through the 64 KiB ring; kPlain: one tag per step (tunable batch_decode = 0).
+enum : int { kSmemSlot = 0, kGlobal = 1, kRing = 2, kPlain = 3 };
+template <int kPath>
 __global__ void __launch_bounds__(256, 5) snappy_decompress_kernel(DecompressParams P) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31;
@@ -1096,12 +1101,12 @@ __global__ void __launch_bounds__(256, 5) snappy_decompress_kernel(DecompressPar
         st = B2C_CORRUPT;
     } else if (expected > cap) {
         st = B2C_TOO_SMALL;
-    } else if (P.smem_per_warp && expected <= P.smem_per_warp) {
+    } else if ((kPath == kSmemSlot || kPath == kPlain) && P.smem_per_warp && expected <= P.smem_per_warp) {
         uint8_t* sbuf = smem_raw + (size_t)wib * (P.smem_per_warp + kScratchSlot);
         BatchScratch& sc = *reinterpret_cast<BatchScratch*>(sbuf + P.smem_per_warp);
         LinearOut lo{sbuf};
-        st = P.batched ? decode_message_batched(in, n, k, lo, expected, lane, sc)
-                       : decode_message_warp(in, n, k, sbuf, expected, lane);
+        if constexpr (kPath == kSmemSlot) st = decode_message_batched(in, n, k, lo, expected, lane, sc);
+        else st = decode_message_warp(in, n, k, sbuf, expected, lane);
         __syncwarp();
         if (st == B2C_OK) {
             // flush: bytes to 16-byte alignment of the destination, then 16-byte stores
@@ -1130,15 +1135,16 @@ __global__ void __launch_bounds__(256, 5) snappy_decompress_kernel(DecompressPar
             if (lane < expected - done) gout[done + lane] = sbuf[done + lane];
         }
     } else {
-        BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * (P.smem_per_warp + kScratchSlot) + P.smem_per_warp);
-        if (P.ring) {
+        if constexpr (kPath == kRing) {
             RingOut ro{smem_raw + (size_t)wib * (65536 + kScratchSlot), gout, 0u, 0u, 0u};
             BatchScratch& rsc = *reinterpret_cast<BatchScratch*>(ro.ring + 65536);
             st = decode_message_batched(in, n, k, ro, expected, lane, rsc);
-        } else {
+        } else if constexpr (kPath == kGlobal) {
+            BatchScratch& sc = *reinterpret_cast<BatchScratch*>(smem_raw + (size_t)wib * (P.smem_per_warp + kScratchSlot) + P.smem_per_warp);
             LinearOut lo{gout};
-            st = P.batched ? decode_message_batched(in, n, k, lo, expected, lane, sc)
-                           : decode_message_warp(in, n, k, gout, expected, lane);
+            st = decode_message_batched(in, n, k, lo, expected, lane, sc);
+        } else {  // kPlain, or a slot larger than its class allows (the lists are built by capacity: does not happen)
+            st = decode_message_warp(in, n, k, gout, expected, lane);
         }
     }
     if (lane == 0) {
@@ -1441,7 +1447,7 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
             wpb = 1;
             smem = 65536 + kScratchSlot;
             if (!ctx->ring_attr_done) {
-                B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_decompress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                B2C_CUDA(ctx, cudaFuncSetAttribute(snappy_decompress_kernel<kRing>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                    (int)smem));
                 ctx->ring_attr_done = true;
             }
@@ -1452,7 +1458,10 @@ int launch_decompress(b2c_ctx* ctx, Lane& lane, const LayoutView& in, const uint
         }
         // enough CTAs to fill every SM whatever the class's shared memory allows; the others find the list empty
         const uint32_t blocks = std::min<uint32_t>((P.n_list + wpb - 1) / wpb, (uint32_t)ctx->num_sms * (P.ring ? 3u : 8u));
-        snappy_decompress_kernel<<<blocks, wpb * 32, smem, lane.stream>>>(P);
+        if (!P.batched) snappy_decompress_kernel<kPlain><<<blocks, wpb * 32, smem, lane.stream>>>(P);
+        else if (P.ring) snappy_decompress_kernel<kRing><<<blocks, wpb * 32, smem, lane.stream>>>(P);
+        else if (P.smem_per_warp) snappy_decompress_kernel<kSmemSlot><<<blocks, wpb * 32, smem, lane.stream>>>(P);
+        else snappy_decompress_kernel<kGlobal><<<blocks, wpb * 32, smem, lane.stream>>>(P);
         ctx->launches++;
         B2C_CUDA(ctx, cudaGetLastError());
     }
