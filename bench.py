@@ -194,8 +194,8 @@ OPS = ("crc32c", "compress", "decompress", "pack")  # order of B2C_PROF_* in inc
 def kernel_names(max_len: int) -> dict:
     small = max_len <= 1024
     return {"crc32c": "crc32c_chunks_kernel" + ("" if max_len <= 4096 else " + crc32c_combine_kernel"),
-            "compress": ("snappy_compress_small2_kernel<4>" if small else
-                         "snappy_compress_orbit_kernel (fragments > 1 KiB) + snappy_compress_small2_kernel<4> (<= 1 KiB)"),
+            "compress": ("snappy_compress_small2_kernel<8>" if small else
+                         "snappy_compress_orbit_kernel (fragments > 1 KiB) + snappy_compress_small2_kernel<8> (<= 1 KiB)"),
             "decompress": ("snappy_decompress_small_kernel<8>" if small else
                            "snappy_decompress_kernel / snappy_seg_* + snappy_decompress_blocks_kernel (+ small kernel for slots <= 1 KiB)"),
             "pack": "snappy_message_sizes_kernel + scan + snappy_gather_kernel"}

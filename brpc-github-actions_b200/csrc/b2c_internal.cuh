@@ -127,7 +127,7 @@ struct b2c_ctx {
     std::vector<uint32_t> bp_len, tmp_cap, tmp_cap2;
     int gtab_warps_per_sm = 16;  // B2C_GTAB_WPS: resident warps per SM of the HBM-table compressor (0 = shared-memory tables); 16 keeps all tables L2-resident
     bool small_kernels = true;  // B2C_SMALL_KERNELS=0 routes <=1 KiB bodies through the warp kernels
-    int small_lpw_compress = 4, small_lpw_decompress = 8;  // bodies per warp (B2C_SMALL_LPW_C / _D: 4, 8, 16, 32)
+    int small_lpw_compress = 8, small_lpw_decompress = 8;  // bodies per warp (B2C_SMALL_LPW_C / _D: 2 (compress only), 4, 8, 16, 32); measured with 3 CTAs of 32 bodies per SM: 4: 10.5, 8: 10.0, 16: 12.9 ms per GiB of `words`
     // tunables (environment: B2C_SLAB_MB, B2C_HOST_THREADS, B2C_TRACE)
     size_t slab_bytes = 32u << 20;
     bool slab_fixed = false;  // B2C_SLAB_MB given: no adaptation to the batch's message sizes

@@ -25,8 +25,13 @@ constexpr uint32_t kSmallMax = 1024;
 // serial chains of different bodies then interleave in the schedulers instead of being
 // executed in lock-step (ncu on LPW=32: 10 of 32 lanes active, 0.2 IPC per warp, 2 warps/SM).
 constexpr uint32_t kSmallInStride = kSmallMax + 32;  // per-slot input buffer: 1 KiB + slack for 16-byte reads past the end
+// The hash table of a body holds positions below 1024: 10 bits.  They are kept as a byte (low 8 bits, tlo) and two
+// bits packed four entries to a byte (thi), 1.25 KiB per body instead of 2: a CTA of 32 bodies then takes 73 KiB and
+// THREE of them fit an SM (96 bodies in flight instead of 64; the kernel waits on its own dependent chains, 56 %
+// issue-active with 4 warps per scheduler).  Each body's tables are its own (slot-major): only its lane touches them.
 struct SmallCompressSmem {
-    uint16_t table[1024 * 32];              // [entry][slot]
+    uint8_t tlo[1024 * 32];                 // [slot][entry]      low 8 bits
+    uint8_t thi[256 * 32];                  // [slot][entry / 4]  bits 8-9, entry & 3 selects the pair
     uint8_t in[kSmallInStride * 32];        // [slot][byte], filled by TMA bulk copies
 };
 
@@ -94,20 +99,26 @@ struct SmallCompressParams {
 // order are the reference's, only the moment they are written changes.
 // The table is addressed as a 32-bit shared-memory address kept opaque to the compiler, which
 // otherwise re-derives it from the input slot's address on every trip (2 extra instructions per access).
-__device__ __forceinline__ uint32_t tab_swap(uint32_t addr, uint32_t v) {  // returns the old entry, stores v
-    uint16_t old;
-    asm volatile("ld.shared.u16 %0, [%1];\n\tst.shared.u16 [%1], %2;" : "=h"(old) : "r"(addr), "h"((uint16_t)v) : "memory");
-    return old;
+__device__ __forceinline__ uint32_t tab_swap(uint32_t lo_s, uint32_t hi_s, uint32_t h, uint32_t v) {  // returns the old entry, stores v
+    uint32_t lo, hb;
+    const uint32_t al = lo_s + h, ah = hi_s + (h >> 2), sh = (h & 3u) * 2u;
+    asm volatile("ld.shared.u8 %0, [%2];\n\tld.shared.u8 %1, [%3];" : "=r"(lo), "=r"(hb) : "r"(al), "r"(ah) : "memory");
+    const uint32_t nhb = (hb & ~(3u << sh)) | ((v >> 8) << sh);  // (bfe / bfi are emulated on sm_100a and measured slower)
+    asm volatile("st.shared.u8 [%0], %2;\n\tst.shared.u8 [%1], %3;" ::"r"(al), "r"(ah), "r"(v), "r"(nhb) : "memory");
+    return lo | (((hb >> sh) & 3u) << 8);
 }
-__device__ __forceinline__ void tab_store(uint32_t addr, uint32_t v) {
-    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)v) : "memory");
+__device__ __forceinline__ void tab_store(uint32_t lo_s, uint32_t hi_s, uint32_t h, uint32_t v) {
+    uint32_t hb;
+    const uint32_t al = lo_s + h, ah = hi_s + (h >> 2), sh = (h & 3u) * 2u;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(hb) : "r"(ah) : "memory");
+    const uint32_t nhb = (hb & ~(3u << sh)) | ((v >> 8) << sh);
+    asm volatile("st.shared.u8 [%0], %2;\n\tst.shared.u8 [%1], %3;" ::"r"(al), "r"(ah), "r"(v), "r"(nhb) : "memory");
 }
 
-template <int TSTRIDE>
-__device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const uint32_t n, uint16_t* tab,
+__device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const uint32_t n, uint8_t* tlo, uint8_t* thi,
                                                     uint32_t* __restrict__ elist) {
-    uint32_t tab_s = smem_u32(tab);
-    asm volatile("" : "+r"(tab_s));
+    uint32_t lo_s = smem_u32(tlo), hi_s = smem_u32(thi);
+    asm volatile("" : "+r"(lo_s), "+r"(hi_s));
     uint64_t list = reinterpret_cast<uint64_t>(elist);
     asm volatile("" : "+l"(list));  // one 64-bit base: element k goes to list + 4k with a single wide multiply-add
     uint32_t ne = 0;
@@ -138,7 +149,7 @@ __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const u
             const uint32_t n0 = wn[0], n1 = wn[1], n2 = wn[2];
             const uint32_t nd0 = __funnelshift_r(n0, n1, (nxt & 3) * 8);
             const uint32_t nh = hash_bytes_s(nd0, shift);  // likewise: the next step's hash, ready if this one misses
-            const uint32_t cand = tab_swap(tab_s + h * (2 * TSTRIDE), ip);
+            const uint32_t cand = tab_swap(lo_s, hi_s, h, ip);
             const uint32_t* wa = reinterpret_cast<const uint32_t*>(in_b + (cand & ~3u));
             const uint32_t sa = (cand & 3) * 8;
             const uint32_t a0 = wa[0], a1 = wa[1];
@@ -183,7 +194,7 @@ __device__ __forceinline__ uint32_t small_find_body(const uint8_t* in_b, const u
                     const uint32_t a = w[0], b = w[1], c = w[2], e = w[3], sh = (q & 3) * 8;
                     const uint32_t p0 = __funnelshift_r(a, b, sh), p1 = __funnelshift_r(b, c, sh),
                                    p2 = __funnelshift_r(c, e, sh);  // bytes q..q+11
-                    tab_store(tab_s + hash_bytes_s(p0, shift) * (2 * TSTRIDE), q);
+                    tab_store(lo_s, hi_s, hash_bytes_s(p0, shift), q);
                     d0 = __funnelshift_r(p0, p1, 8);
                     d1 = __funnelshift_r(p1, p2, 8);
                     h = hash_bytes_s(d0, shift);
@@ -204,7 +215,7 @@ constexpr uint32_t kSmallMaxElems = kSmallMax / 4;  // copies cover >= 4 input b
 
 // Persistent CTAs of 32 bodies (LPW per warp); `elists` = gridDim.x * 32 lists of kSmallMaxElems words.
 template <int LPW>
-__global__ void __launch_bounds__(1024 / LPW, 2) snappy_compress_small2_kernel(SmallCompressParams P, uint32_t* elists) {
+__global__ void __launch_bounds__(1024 / LPW, LPW >= 4 ? 3 : 2) snappy_compress_small2_kernel(SmallCompressParams P, uint32_t* elists) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     SmallCompressSmem& sm = *reinterpret_cast<SmallCompressSmem*>(smem_raw);
     __shared__ uint64_t stage_bar;
@@ -219,8 +230,9 @@ __global__ void __launch_bounds__(1024 / LPW, 2) snappy_compress_small2_kernel(S
         const bool live = lane < LPW && idx < P.n_list;
         __syncthreads();  // previous group's tables and staged bodies are no longer in use (and stage_bar is initialised)
         {
-            uint4* t4 = reinterpret_cast<uint4*>(sm.table);
-            for (uint32_t i = threadIdx.x; i < sizeof(sm.table) / 16; i += blockDim.x) t4[i] = make_uint4(0, 0, 0, 0);
+            uint4* t4 = reinterpret_cast<uint4*>(sm.tlo);  // tlo and thi are adjacent
+            for (uint32_t i = threadIdx.x; i < (sizeof(sm.tlo) + sizeof(sm.thi)) / 16; i += blockDim.x)
+                t4[i] = make_uint4(0, 0, 0, 0);
         }
         uint32_t f = 0, n = 0;
         const uint8_t* gin = nullptr;
@@ -246,7 +258,7 @@ __global__ void __launch_bounds__(1024 / LPW, 2) snappy_compress_small2_kernel(S
         // ---- phase 1: find ----
         uint32_t* my_list = elists + ((size_t)blockIdx.x * 32 + slot) * kSmallMaxElems;
         uint32_t ne = 0;
-        if (live) ne = small_find_body<32>(in_b, n, sm.table + slot, my_list);
+        if (live) ne = small_find_body(in_b, n, sm.tlo + slot * 1024, sm.thi + slot * 256, my_list);
         __syncwarp();  // the lists written by this warp's lanes are read by all of its lanes below
         // ---- phase 2: encode, one body at a time by the whole warp ----
         uint8_t* my_out = live ? P.scratch + (P.frag_slot ? P.frag_slot[f] : (uint64_t)f * P.slot_stride) : nullptr;
@@ -489,7 +501,7 @@ int launch_compress_small(b2c_ctx* ctx, Lane& lane, const LayoutView& L, const u
     const uint32_t blocks = (P.n_list + 31) / 32;
     const size_t smem = sizeof(SmallCompressSmem);
     {  // find, then encode; persistent CTAs own their element lists
-        const uint32_t grid = std::min<uint32_t>(blocks, (uint32_t)ctx->num_sms * 2);
+        const uint32_t grid = std::min<uint32_t>(blocks, (uint32_t)ctx->num_sms * 3);
         int rc;
         if ((rc = ws_reserve(ctx, lane, lane.ws_tab, (size_t)grid * 32 * kSmallMaxElems * 4))) return rc;
         uint32_t* el = static_cast<uint32_t*>(lane.ws_tab.p);
