@@ -226,7 +226,10 @@ int b2c_snappy_uncompressed_length_dev(b2c_ctx* ctx, const b2c_layout* in_layout
  * d_out + out_layout.off[i]; out_layout.len[i] is the slot capacity.
  * d_status[i] = B2C_OK iff the reference returns true (then d_ulen[i] bytes were
  * written), B2C_CORRUPT iff it returns false, B2C_TOO_SMALL when the preamble
- * asks for more than the slot.  d_ulen may be NULL. */
+ * asks for more than the slot.  d_ulen may be NULL.
+ * Workspace (owned by the ctx, grow-only): when the batch holds slots larger than 64 KiB, their streams are cut into
+ * independently decoded 64 KiB blocks behind a table of 4 bytes per compressed byte of the batch (so about four
+ * times in_layout's payload of device memory, on top of input and output). */
 int b2c_snappy_decompress_dev(b2c_ctx* ctx, const b2c_layout* in_layout, const void* d_in,
                               const b2c_layout* out_layout, void* d_out, uint32_t* d_ulen,
                               int32_t* d_status);
