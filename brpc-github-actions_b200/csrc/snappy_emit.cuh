@@ -8,6 +8,8 @@
 namespace b2c {
 
 static constexpr uint32_t kFullMask = 0xffffffffu;
+// long literal moves noted for later (emit_elements_warp / emit_remainder_warp): list[0].x = how many, list[1..]
+static constexpr uint32_t kDeferMax = 6, kDeferMin = 512, kDeferBytes = (kDeferMax + 2) * 16;
 
 __device__ __forceinline__ uint32_t hash_w(uint32_t bytes, uint32_t shift) {  // snappy.cc:47-50
     return (bytes * 0x1e35a7bdu) >> shift;
@@ -110,7 +112,7 @@ __device__ __forceinline__ void write_copy_tail(uint8_t* o, uint32_t offset, uin
 template <class In>
 __device__ __forceinline__ uint32_t emit_elements_warp(const In& in, const bool has, const uint32_t e_ls, const uint32_t e_p,
                                                        const uint32_t off, const uint32_t mm, uint8_t* __restrict__ out,
-                                                       uint32_t op, const uint32_t lane) {
+                                                       uint32_t op, const uint32_t lane, uint4* defer = nullptr) {
     const uint32_t ll = has ? e_p - e_ls : 0u;  // literal bytes before the copy
     const uint32_t lit_sz = ll ? literal_header_bytes(ll) + ll : 0u;
     const uint32_t size = has ? lit_sz + copy_bytes(off, mm) : 0u;
@@ -138,7 +140,20 @@ __device__ __forceinline__ uint32_t emit_elements_warp(const In& in, const bool 
         const uint64_t oa = reinterpret_cast<uint64_t>(o + lit_sz - ll);
         uint8_t* d = reinterpret_cast<uint8_t*>(((uint64_t)__shfl_sync(kFullMask, (uint32_t)(oa >> 32), l) << 32) |
                                                 __shfl_sync(kFullMask, (uint32_t)oa, l));
-        for (uint32_t i = lane; i < ln; i += 32) d[i] = in.ld8(s0 + i);  // (the vector copy here costs the orbit kernel registers it has not got)
+        // Kilobytes of literal in front of a rare match (incompressible data): the vector copy costs registers the
+        // orbit kernel has not got inside its loop, so the move is only NOTED (destination, source, length) and made
+        // by emit_remainder_warp, which has that copy anyway.  The input does not change and the place is reserved.
+        if (In::kContiguous && defer && ln >= kDeferMin && defer[0].x < kDeferMax) {
+            __syncwarp();
+            if (lane == 0) {
+                const uint32_t k = ++defer[0].x;
+                const uint64_t da = reinterpret_cast<uint64_t>(d);
+                defer[k] = make_uint4((uint32_t)da, (uint32_t)(da >> 32), s0, ln);
+            }
+            __syncwarp();
+            continue;
+        }
+        for (uint32_t i = lane; i < ln; i += 32) d[i] = in.ld8(s0 + i);
     }
     if (has && mm < 68) write_copy_tail(o + lit_sz, off, mm);
     uint32_t lcopies = __ballot_sync(kFullMask, has && mm >= 68);
@@ -163,13 +178,38 @@ __device__ __forceinline__ uint32_t emit_elements_warp(const In& in, const bool 
 // emit_remainder (snappy.cc:446-450): the final literal [from, n), written by the whole warp.
 template <class In>
 __device__ __forceinline__ uint32_t emit_remainder_warp(const In& in, const uint32_t from, const uint32_t n,
-                                                        uint8_t* __restrict__ out, uint32_t op, const uint32_t lane) {
+                                                        uint8_t* __restrict__ out, uint32_t op, const uint32_t lane,
+                                                        uint4* defer = nullptr) {
+    uint32_t todo = 0;  // noted moves, the final literal among them: ONE copy loop serves all
+    if (defer) {
+        __syncwarp();
+        todo = defer[0].x;
+    }
     if (from < n) {
         const uint32_t ll = n - from;
         uint8_t* o = out + op;
         if (lane == 0) write_literal_header(o, ll);
-        copy_literal_warp(in, from, o + literal_header_bytes(ll), ll, lane);
+        uint8_t* d = o + literal_header_bytes(ll);
         op += literal_header_bytes(ll) + ll;
+        if (defer) {
+            if (lane == 0) {
+                const uint64_t da = reinterpret_cast<uint64_t>(d);
+                defer[todo + 1] = make_uint4((uint32_t)da, (uint32_t)(da >> 32), from, ll);
+            }
+            todo++;
+            __syncwarp();
+        } else {
+            copy_literal_warp(in, from, d, ll, lane);
+        }
+    }
+    for (uint32_t k = 1; k <= todo; k++) {
+        const uint4 e = defer[k];
+        copy_literal_warp(in, e.z, reinterpret_cast<uint8_t*>(((uint64_t)e.y << 32) | e.x), e.w, lane);
+    }
+    if (defer) {
+        __syncwarp();
+        if (lane == 0) defer[0].x = 0;
+        __syncwarp();
     }
     return op;
 }

@@ -27,6 +27,7 @@ namespace b2c {
 
 static constexpr uint32_t kCap = 40;    // speculative per-lane match length limit; >= 32, so a capped match leaves the window
 static constexpr uint32_t kQueue = 64;  // queued elements per warp (two words each)
+static constexpr uint32_t kWarpFixed = kQueue * sizeof(uint2) + kDeferBytes;  // per warp: the queue, then the noted literal moves
 
 // Encode the first `cnt` (<= 32) queued elements; `emitted` = end of the last element already encoded.
 template <class In>
@@ -39,7 +40,8 @@ __device__ __forceinline__ uint32_t flush_queue(const In& in, const uint2* queue
     uint32_t ls = __shfl_up_sync(kFullMask, end, 1);
     if (lane == 0) ls = emitted;
     emitted = __shfl_sync(kFullMask, end, cnt - 1);
-    return emit_elements_warp(in, has, ls, p, off, mm, out, op, lane);
+    return emit_elements_warp(in, has, ls, p, off, mm, out, op, lane,
+                              reinterpret_cast<uint4*>(const_cast<uint2*>(queue) + kQueue));
 }
 
 // CompressFragment by one warp.  `T` = `tsize` zeroed u16 slots (shared or global memory); `queue` = kQueue
@@ -50,6 +52,8 @@ __device__ uint32_t compress_fragment_orbit(const In in, const uint32_t n, uint8
     const uint32_t shift = 32 - (31 - __clz(tsize));
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t op = 0, next_emit = 0, emitted = 0, cnt = 0;
+    if (lane == 0) reinterpret_cast<uint4*>(queue + kQueue)[0].x = 0;  // no literal move noted yet
+    __syncwarp();
     if (n >= 15) {  // kInputMarginBytes, snappy.cc:344-347
         const uint32_t ip_limit = n - 15;
         // `s` is the reference's `skip` with one extra state: 31 right after a copy (the copy loop's own table
@@ -201,7 +205,7 @@ __device__ uint32_t compress_fragment_orbit(const In in, const uint32_t n, uint8
         }
     }
     if (cnt) op = flush_queue(in, queue, cnt, emitted, out, op, lane);
-    return emit_remainder_warp(in, next_emit, n, out, op, lane);  // snappy.cc:446-450
+    return emit_remainder_warp(in, next_emit, n, out, op, lane, reinterpret_cast<uint4*>(queue + kQueue));  // snappy.cc:446-450
 }
 
 // ---- kernels ------------------------------------------------------------------------------
@@ -237,11 +241,11 @@ __global__ void __launch_bounds__(256) snappy_compress_orbit_kernel(WindowParams
     const uint32_t wib = threadIdx.x >> 5;
     const uint32_t gw = blockIdx.x * (blockDim.x >> 5) + wib;
     const uint32_t total = gridDim.x * (blockDim.x >> 5);
-    const size_t per_warp = kQueue * sizeof(uint2) + (size_t)P.table_entries * 2 + P.in_stride;
+    const size_t per_warp = kWarpFixed + (size_t)P.table_entries * 2 + P.in_stride;
     uint8_t* my = smem_raw + (size_t)wib * per_warp;
     uint2* queue = reinterpret_cast<uint2*>(my);
-    uint16_t* table = P.table_entries ? reinterpret_cast<uint16_t*>(my + kQueue * sizeof(uint2)) : P.gtab + (size_t)gw * 16384;
-    uint8_t* stage = my + kQueue * sizeof(uint2) + (size_t)P.table_entries * 2;
+    uint16_t* table = P.table_entries ? reinterpret_cast<uint16_t*>(my + kWarpFixed) : P.gtab + (size_t)gw * 16384;
+    uint8_t* stage = my + kWarpFixed + (size_t)P.table_entries * 2;
     uint64_t* bar = &bars[wib];
     if (kStage && lane == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr32(bar)), "r"(1) : "memory");
@@ -357,10 +361,10 @@ int launch_compress_window(b2c_ctx* ctx, Lane& lane, const LayoutView& L, int c,
         resident = std::max(1, ctx->window_warps_per_sm / 8);
         P.table_entries = 0;
     } else {
-        const size_t pw = kQueue * sizeof(uint2) + (size_t)P.table_entries * 2 + P.in_stride;
+        const size_t pw = kWarpFixed + (size_t)P.table_entries * 2 + P.in_stride;
         resident = std::max<uint32_t>(1, (uint32_t)((220u << 10) / (pw * wpb + 1024)));
     }
-    const size_t per_warp = kQueue * sizeof(uint2) + (size_t)P.table_entries * 2 + P.in_stride;
+    const size_t per_warp = kWarpFixed + (size_t)P.table_entries * 2 + P.in_stride;
     const uint32_t want_blocks = (uint32_t)ctx->num_sms * resident;
     const uint32_t blocks = std::min<uint32_t>(want_blocks, (P.n_list + wpb - 1) / wpb);
     if (P.table_entries == 0) {
