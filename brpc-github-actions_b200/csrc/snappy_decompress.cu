@@ -289,7 +289,7 @@ __device__ int decode_message_batched(const uint8_t* __restrict__ in, const uint
             __syncwarp();
 #pragma unroll
             for (uint32_t j = 0; j < 8; j++) {
-                const uint32_t p = lane * 8 + j;
+                const uint32_t p = j * 32 + lane;
                 const uint32_t c = win[p];
                 const uint32_t kind = c & 3;
                 uint64_t L;
@@ -315,7 +315,7 @@ __device__ int decode_message_batched(const uint8_t* __restrict__ in, const uint
             for (uint32_t k = 1; k < 5; k++) {  // square the jump table: 2, 4, 8, 16 tags ahead
 #pragma unroll
                 for (uint32_t j = 0; j < 8; j++) {
-                    const uint32_t p = lane * 8 + j;
+                    const uint32_t p = j * 32 + lane;
                     const uint32_t q = sc.jmp[k - 1][p];
                     sc.jmp[k][p] = (uint16_t)(q < kWin ? sc.jmp[k - 1][q] : kStop);
                 }
